@@ -1,0 +1,231 @@
+/*
+ * libmosstts_sm100 — C ABI of the B200-native MOSS-TTS synthesis hot path.
+ *
+ * The reference (xiami2019/MOSS-TTS) is pure Python/PyTorch and has no FFI of its own
+ * (SURVEY.md §2.2, §8b): its boundary is the Python method surface
+ *     MossTTSDelayModel.generate / forward      moss_tts_delay/modeling_moss_tts.py:392-525, :225-390
+ *     inference_utils.sample_token, find_last_equal_C   moss_tts_delay/inference_utils.py:111-165
+ *     MossTTSDelayProcessor.apply_(de_)delay_pattern, decode_audio_codes
+ *                                                moss_tts_delay/processing_moss_tts.py:516-537, :880-930
+ *     MossAudioTokenizerModel.decode / batch_decode / quantizer.decode_codes
+ *                                                moss_audio_tokenizer/modeling_moss_audio_tokenizer.py:1650-1755,
+ *                                                :1431-1475, :1276-1283
+ * Each entry point below names the reference interface it stands behind.  The Python host in
+ * moss_tts_b200/ keeps those method names/arguments and calls this library through ctypes.
+ *
+ * Conventions
+ *   - plain C types only: device pointers as void*, sizes as int / long long, cudaStream_t as void*.
+ *   - every buffer is allocated by the caller (PyTorch); the library borrows and never frees it.
+ *     Opaque handles own only small host-side plans (TMA descriptors, CUDA graphs).
+ *   - return value: MT_OK (0) or a negative MT_ERR_*; mt_last_error() gives a message
+ *     (thread-local).  No exceptions cross this boundary.
+ *   - all entry points are asynchronous with respect to the host on the given stream unless noted.
+ *   - there is NO CPU fallback: without an sm_100 device every compute entry point fails.
+ */
+#ifndef MOSSTTS_H_
+#define MOSSTTS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
+
+#define MT_OK 0
+#define MT_ERR_ARG (-1)
+#define MT_ERR_CUDA (-2)
+#define MT_ERR_UNSUPPORTED (-3)
+
+#define MT_DTYPE_BF16 0
+#define MT_DTYPE_F32 1 /* as a GEMM input type: fp32 storage, TF32 tensor-core math */
+
+#define MT_GEMM_AUTO 0   /* tcgen05/TMA kernel (the product path) */
+#define MT_GEMM_SIMT 1   /* plain CUDA-core kernel, used by tests to cross-check the tcgen05 kernel */
+
+typedef void* mt_stream; /* cudaStream_t */
+
+int mt_version(void);
+const char* mt_last_error(void);
+/* Number of kernel launches issued by this library since load (bench.py's gpu_launches). */
+long long mt_launch_count(void);
+/* Debug knob for tests: force every internal GEMM to MT_GEMM_SIMT (1) or back to tcgen05 (0). */
+int mt_debug_force_simt(int on);
+
+/* ------------------------------------------------------------------------------------------
+ * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:
+ * Qwen3 q/k/v/o/gate/up/down, the 1+n_vq heads modeling_moss_tts.py:185-191,292-300, and the codec's
+ * in_proj/out_proj/linear1/linear2/input_proj/output_proj modeling_moss_audio_tokenizer.py:563-568,731-732,907-914)
+ * epilogue: v = acc (+bias[n]) ; act ; (round to bf16) ; out = residual[m,n] + (scale ? scale[n]*v : v)
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int dtype_in;          /* MT_DTYPE_BF16 | MT_DTYPE_F32 (x and w) */
+  int dtype_out;         /* MT_DTYPE_BF16 | MT_DTYPE_F32 (out and residual) */
+  int M, N, K;
+  const void* x;  long long ldx;   /* row stride in elements */
+  const void* w;  long long ldw;
+  void* out;      long long ldo;
+  const float* bias;               /* [N] or NULL */
+  int act;                         /* 0 none, 1 GELU(erf) */
+  const void* residual; long long ldr;  /* [M,N] or NULL */
+  const float* scale;              /* [N] or NULL (LayerScale) */
+  int round_bf16;                  /* round v to bf16 before the residual add */
+  float* workspace; long long workspace_bytes; /* split-K partials; may be NULL (no split-K) */
+  int impl;                        /* MT_GEMM_AUTO | MT_GEMM_SIMT */
+} mt_gemm_args;
+int mt_gemm(const mt_gemm_args* a, mt_stream s);
+
+/* ------------------------------------------------------------------------------------------
+ * MossTTSDelay language model
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  int hidden_size, intermediate_size, num_layers, num_heads, num_kv_heads, head_dim;
+  int vocab_size, n_vq, audio_head_size /* audio_vocab_size+1 */;
+  float rms_norm_eps;
+  int pad_token_id, im_start_token_id, im_end_token_id;
+  int audio_start_token_id, audio_end_token_id;
+  int audio_assistant_gen_slot_token_id, audio_assistant_delay_slot_token_id;
+  int audio_pad_code;
+  int max_batch, max_seq;       /* KV-cache capacity */
+  int max_tokens;               /* largest B*T a single forward call may see */
+} mt_lm_config;
+
+/* All weights bf16, row-major [out,in] as in nn.Linear / nn.Embedding. */
+typedef struct {
+  const void* embed_tokens;        /* [vocab, H] */
+  const void* emb_ext;             /* [n_vq, audio_head_size, H] */
+  const void* const* w_qkv;        /* per layer: rows = q | k | v, [q+2kv, H] */
+  const void* const* w_o;          /* per layer [H, q] */
+  const void* const* w_gate_up;    /* per layer: rows = gate | up, [2I, H] */
+  const void* const* w_down;       /* per layer [H, I] */
+  const void* const* ln_in;        /* per layer [H] */
+  const void* const* ln_post;      /* per layer [H] */
+  const void* const* q_norm;       /* per layer [head_dim] */
+  const void* const* k_norm;       /* per layer [head_dim] */
+  const void* final_norm;          /* [H] */
+  const void* text_head;           /* [vocab, H] */
+  const void* audio_heads;         /* [n_vq*audio_head_size, H] */
+  const void* rope_cos;            /* [max_seq, head_dim/2] bf16 (host builds it with HF's formula) */
+  const void* rope_sin;
+} mt_lm_weights;
+
+typedef struct mt_lm mt_lm;
+
+int mt_lm_query_sizes(const mt_lm_config* cfg, long long* kv_bytes, long long* workspace_bytes);
+int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, void* kv_cache, void* workspace, mt_lm** out);
+int mt_lm_destroy(mt_lm* h);
+
+/* MossTTSDelayModel.forward (modeling_moss_tts.py:225-300) without the loss branch.
+ * ids [B,T,1+n_vq] int64; attn_mask [B, mask_ld] uint8 (1 = attend) covering positions [0,past_len+T);
+ * writes K/V for positions [past_len,past_len+T).  Logit outputs are bf16 and may be NULL:
+ *   text_logits  [B, Tout, vocab]                  audio_logits [B, Tout, n_vq, audio_head_size]
+ * with Tout = T (last_only=0) or 1 (last_only=1: only the last position, what generate() consumes).
+ * audio_logits[..., audio_head_size-1] is set to -inf as the reference does (:298-299). */
+int mt_lm_forward(mt_lm* h, const int64_t* ids, const uint8_t* attn_mask, long long mask_ld,
+                  int B, int T, int past_len, int last_only,
+                  void* text_logits, void* audio_logits, mt_stream s);
+
+/* generate() (modeling_moss_tts.py:392-525). */
+typedef struct {
+  int max_new_tokens;
+  float text_temperature, text_top_p;   int text_top_k;
+  float audio_temperature, audio_top_p; int audio_top_k;
+  float audio_repetition_penalty;
+  unsigned int seed;
+  int use_cuda_graph;          /* capture the decode step once and replay it */
+  int check_stop_every;        /* host polls the all-stopped flag every this many steps (>=1) */
+} mt_gen_params;
+
+/* input_ids [B,S0,1+n_vq] int64, attention_mask [B,S0] uint8 (device).
+ * gen_ids [B, S0+max_new_tokens, 1+n_vq] int64 (device, caller-allocated) receives prompt + new rows.
+ * start_indices [B] int64 (device): last im_start index + 3 (:518).
+ * Returns through *n_steps the number of decode iterations executed (host-synchronous at the end). */
+int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
+                   const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, int* n_steps,
+                   float* step_ms /* optional [max_new_tokens] host array of per-step device ms, or NULL */,
+                   mt_stream s);
+
+/* inference_utils.sample_token (:111-145) on bf16 logits [N,V] (row stride ld elements).
+ * prev_bitmap: optional device bitmap (ceil(V/32) uint32) of ids the repetition penalty applies to
+ * (the union the reference builds with torch.unique, :78-86).  uniforms [N] float in [0,1) drive the
+ * inverse-CDF draw when do_sample=1.  out [N] int64. */
+int mt_sample_tokens(const void* logits, long long ld, int N, int V, float temperature,
+                     const uint32_t* prev_bitmap, float repetition_penalty, float top_p, int top_k,
+                     int do_sample, const float* uniforms, int64_t* out, mt_stream s);
+
+/* inference_utils.find_last_equal_C (:148-165): t [B,S] int64 -> out [B] int64 (-1 if absent). */
+int mt_find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out, mt_stream s);
+
+/* processing_moss_tts.py:516-525 / :528-537.  codes [T,n] -> out [T+n-1,n]; delayed [Td,n] -> out [Td-n+1,n]. */
+int mt_apply_delay_pattern(const int64_t* codes, int T, int n, long long pad_code, int64_t* out, mt_stream s);
+int mt_apply_de_delay_pattern(const int64_t* delayed, int Td, int n, int64_t* out, mt_stream s);
+
+/* ------------------------------------------------------------------------------------------
+ * MOSS-Audio-Tokenizer decode side
+ * ------------------------------------------------------------------------------------------ */
+#define MT_CODEC_MAX_STAGES 8
+typedef struct {
+  int num_stages;
+  int input_dim[MT_CODEC_MAX_STAGES], d_model[MT_CODEC_MAX_STAGES], num_heads[MT_CODEC_MAX_STAGES];
+  int num_layers[MT_CODEC_MAX_STAGES], dim_ff[MT_CODEC_MAX_STAGES], output_dim[MT_CODEC_MAX_STAGES];
+  int patch[MT_CODEC_MAX_STAGES], context[MT_CODEC_MAX_STAGES];
+  int code_dim, rvq_dim, num_quantizers, codebook_size, codebook_dim;
+  float max_period;
+} mt_codec_config;
+
+typedef struct {            /* one transformer layer, all fp32 */
+  const float *norm1_w, *norm1_b, *norm2_w, *norm2_b;
+  const float *in_proj;     /* [3d, d] */
+  const float *out_proj;    /* [d, d] */
+  const float *linear1;     /* [ff, d] */
+  const float *linear2;     /* [d, ff] */
+  const float *scale1, *scale2;   /* LayerScale [d] */
+} mt_codec_layer;
+
+typedef struct {
+  /* RVQ: folded per-quantizer tables, table[q][code][c] = W_out * (W_q * C_q[code] + b_q)   (see
+   * mt_rvq_fold_tables); out_bias [code_dim]. */
+  const float* rvq_table;   /* [num_quantizers, codebook_size, code_dim] */
+  const float* rvq_out_bias;
+  const float* input_proj[MT_CODEC_MAX_STAGES];   /* [d_model, input_dim] or NULL (Identity) */
+  const float* output_proj[MT_CODEC_MAX_STAGES];  /* [output_dim, d_model] or NULL */
+  const mt_codec_layer* layers[MT_CODEC_MAX_STAGES];  /* host array per stage */
+} mt_codec_weights;
+
+typedef struct mt_codec mt_codec;
+int mt_codec_create(const mt_codec_config* cfg, const mt_codec_weights* w, mt_codec** out);
+int mt_codec_destroy(mt_codec* h);
+int mt_codec_workspace_bytes(const mt_codec* h, int B, int T, long long* bytes);
+
+/* Builds the folded RVQ table from the reference's parameters (weight-norm g/v pairs, codebooks,
+ * biases; modeling_moss_audio_tokenizer.py:967-969,1046-1053,1217-1224), all fp32 on device:
+ *   codebook [nq,cs,cd], q_g [nq,rvq], q_v [nq,rvq,cd], q_b [nq,rvq], o_g [code_dim], o_v [code_dim,rvq]
+ *   -> table [nq,cs,code_dim]. */
+int mt_rvq_fold_tables(const float* codebook, const float* q_g, const float* q_v, const float* q_b,
+                       const float* o_g, const float* o_v, int nq, int cs, int cd, int rvq, int code_dim,
+                       float* table, mt_stream s);
+
+/* ResidualLFQ.decode_codes (:1276-1283): codes [nq,B,T] int64 -> fp32.
+ * channel_major=1: out [B, code_dim, T] (the reference layout); 0: out [B, T, code_dim]. */
+int mt_rvq_dequant(const mt_codec* h, const int64_t* codes, int nq, int B, int T, int channel_major,
+                   float* out, mt_stream s);
+
+/* _decode_frame (:1513-1534) for codes [nq,B,T] -> wav [B, T*downsample] fp32.
+ * chunk_frames > 0 reproduces decode(chunk_duration=...)'s streaming ring-cache visibility
+ * (:1728-1750, RingKVCache :413-480) in a single pass; 0 = unchunked.
+ * gemm_impl: MT_GEMM_AUTO | MT_GEMM_SIMT. */
+int mt_codec_decode(mt_codec* h, const int64_t* codes, int nq, int B, int T, int chunk_frames,
+                    float* wav, void* workspace, long long workspace_bytes, mt_stream s);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOSSTTS_H_ */

@@ -1,0 +1,18 @@
+// MOSS-Audio-Tokenizer decode-side kernels (codec_ops.cu).
+#pragma once
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace mt {
+int rvq_fold_tables(const float* codebook, const float* q_g, const float* q_v, const float* q_b, const float* o_g,
+                    const float* o_v, int nq, int cs, int cd, int rvq, int code_dim, float* table, cudaStream_t s);
+int rvq_dequant(const int64_t* codes, const float* table, const float* bias, int nq, int B, int T, int cs, int code_dim,
+                int channel_major, float* out, cudaStream_t s);
+int rvq_dequant_strided(const int64_t* codes, const float* table, const float* bias, int nq, long long q_stride,
+                        long long frames, int cs, int code_dim, float* out, cudaStream_t s);
+int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s);
+int codec_rope(float* qkv, long long M, int T, int d, int hd, float max_period, cudaStream_t s);
+int codec_attention(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
+                    cudaStream_t s);
+int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
+}  // namespace mt

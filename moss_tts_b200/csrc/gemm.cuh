@@ -1,0 +1,40 @@
+// Internal interface of the Linear-layer GEMMs (gemm_tc.cu).
+#pragma once
+#include <cuda.h>
+#include "common.cuh"
+
+namespace mt {
+
+// A tensor map for a row-major [rows, K] matrix with a {128 B x box_rows} box and 128B swizzle.
+int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, long long K, long long ld_elems,
+                 int box_rows);
+
+struct LinearPlan {
+  // y[M,N] = x[M,K] . w[N,K]^T
+  int dtype_in = MT_DTYPE_BF16, dtype_out = MT_DTYPE_BF16;
+  int M = 0, N = 0, K = 0;
+  const void* x = nullptr; long long ldx = 0;
+  const void* w = nullptr; long long ldw = 0;
+  void* out = nullptr; long long ldo = 0;
+  const float* bias = nullptr;
+  int act = 0;
+  const void* residual = nullptr; long long ldr = 0;
+  const float* scale = nullptr;
+  int round_bf16 = 0;
+  float* workspace = nullptr; long long workspace_bytes = 0;
+  // If non-null the kernel writes fp32 split-K partials [splits][M][N] to `workspace` and leaves the
+  // reduction + epilogue to the consumer kernel; *out_splits receives the split count (>=1).
+  int* out_splits = nullptr;
+  int impl = MT_GEMM_AUTO;
+  const CUtensorMap* w_tmap = nullptr;   // optional cached weight map (box rows 128)
+};
+
+// Launches the GEMM.  With out_splits == nullptr the result is complete in `out` on return of the
+// stream work (split-K, when chosen, is reduced by a second kernel).
+int linear(const LinearPlan& p, cudaStream_t s);
+
+extern bool g_force_simt;
+extern long long g_launches;
+inline void count_launch(int n = 1) { g_launches += n; }
+
+}  // namespace mt

@@ -1,0 +1,429 @@
+// Linear-layer GEMM for sm_100a:  y[M,N] = epilogue(x[M,K] . w[N,K]^T), bf16 (kind::f16) or fp32
+// storage with TF32 math (kind::tf32), fp32 accumulation in TMEM.
+//
+// One kernel, two orientations:
+//   normal  : TMEM lanes = rows of x (tokens, tile 128),  TMEM columns = rows of w (tile BN)
+//   swapped : TMEM lanes = rows of w (out features, 128), TMEM columns = rows of x (tokens, BN=pad16(M))
+// The swapped orientation is the decode path (M = batch <= 256): the 128-row UMMA M dimension is
+// filled by weight rows, weights stream once from HBM through a TMA ring, and split-K spreads one
+// layer over all 148 SMs.  Both operands are K-major, so the same TMA box / UMMA descriptor code
+// serves both roles.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA
+// issuer, warps 2..5 = epilogue (TMEM -> registers -> global), one TMEM lane quarter each.
+#include "gemm.cuh"
+#include "ptx.cuh"
+
+#include <mutex>
+
+namespace mt {
+
+bool g_force_simt = false;
+long long g_launches = 0;
+
+// ---------------------------------------------------------------------------------------------
+// tensor maps
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, long long K, long long ld_elems,
+                 int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return fail(MT_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+  const int esz = dtype == MT_DTYPE_BF16 ? 2 : 4;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld_elems * esz) & 15))
+    return fail(MT_ERR_ARG, "TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch (ld=%lld)", ld_elems);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld_elems) * esz};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, dtype == MT_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(MT_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", static_cast<int>(r));
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// epilogue description shared by the tcgen05 kernel, the SIMT kernel and the split-K reducer
+// ---------------------------------------------------------------------------------------------
+struct Epi {
+  void* out; long long ldo; int out_f32;
+  const float* bias; int act;
+  const void* residual; long long ldr;
+  const float* scale; int round_bf16;
+  int M, N;                       // logical output extent
+  float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+
+__device__ __forceinline__ float epi_apply(const Epi& e, int m, int n, float v) {
+  if (e.bias) v += e.bias[n];
+  if (e.act == 1) v = gelu_erf(v);
+  if (e.round_bf16) v = rbf(v);
+  if (e.residual) {
+    float r = e.out_f32 ? reinterpret_cast<const float*>(e.residual)[m * e.ldr + n]
+                        : bf2f(reinterpret_cast<const bf16*>(e.residual)[m * e.ldr + n]);
+    v = r + (e.scale ? e.scale[n] * v : v);
+  } else if (e.scale) {
+    v = e.scale[n] * v;
+  }
+  return v;
+}
+__device__ __forceinline__ void epi_store(const Epi& e, long long m, long long n, float v) {
+  if (e.out_f32) reinterpret_cast<float*>(e.out)[m * e.ldo + n] = v;
+  else reinterpret_cast<bf16*>(e.out)[m * e.ldo + n] = f2bf(v);
+}
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05 kernel
+// ---------------------------------------------------------------------------------------------
+constexpr int kTileA = 128;          // UMMA M
+constexpr int kTileKBytes = 128;     // one 128B-swizzle row of K per k-block
+constexpr int kGemmThreads = 192;
+
+template <int BN, int STAGES>
+struct GemmSmem {
+  static constexpr int kABytes = kTileA * kTileKBytes;
+  static constexpr int kBBytes = BN * kTileKBytes;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOffset = STAGES * kStageBytes;
+  static constexpr int kTotal = kBarOffset + (2 * STAGES + 1) * 8 + 16 + 1024 /* alignment slack */;
+};
+
+template <int BN, int STAGES, int KIND /*1 bf16, 2 tf32*/>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep,
+               int swapped, int rowsA, int rowsB, int k_blocks, int splits, uint64_t hintA, uint64_t hintB) {
+  using L = GemmSmem<BN, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tileA = blockIdx.x, tileB = blockIdx.y, split = blockIdx.z;
+  const int kb0 = static_cast<int>((static_cast<long long>(k_blocks) * split) / splits);
+  const int kb1 = static_cast<int>((static_cast<long long>(k_blocks) * (split + 1)) / splits);
+  constexpr int kKElems = KIND == 1 ? 64 : 32;          // elements per 128-byte k-block
+  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;     // power of two >= 32
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int i = 0; i < STAGES; ++i) {
+      ptx::mbar_init(&full[i], 1);
+      ptx::mbar_init(&empty[i], 1);
+    }
+    ptx::mbar_init(tmem_full, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_holder, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int st = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        ptx::mbar_wait(&empty[st], ph ^ 1);
+        ptx::mbar_expect_tx(&full[st], L::kStageBytes);
+        uint8_t* sa = smem + st * L::kStageBytes;
+        ptx::tma_load_2d(sa, &tmA, &full[st], kb * kKElems, tileA * kTileA, hintA);
+        ptx::tma_load_2d(sa + L::kABytes, &tmB, &full[st], kb * kKElems, tileB * BN, hintB);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc(KIND, kTileA, BN);
+      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        const int st = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        ptx::mbar_wait(&full[st], ph);
+        ptx::tc_fence_after();
+        const uint32_t sa = ptx::smem_u32(smem + st * L::kStageBytes);
+        const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
+        const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + L::kABytes);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {   // 4 x 32-byte UMMA_K slices per 128-byte row
+          if (KIND == 1) ptx::mma_bf16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+          else ptx::mma_tf32(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (it | k) != 0);
+        }
+        ptx::mma_commit(&empty[st]);    // frees the smem stage when these MMAs retire
+      }
+      ptx::mma_commit(tmem_full);       // accumulator complete
+    }
+  } else {
+    // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+    const int q = warp & 3;
+    const int a_row = tileA * kTileA + q * 32 + lane;
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    constexpr int CH = BN < 32 ? 16 : 32;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += CH) {
+      uint32_t r[CH];
+      if constexpr (CH == 32) ptx::tmem_ld32(taddr + c0, r);
+      else ptx::tmem_ld16(taddr + c0, r);
+      ptx::tmem_ld_wait();
+      const int b_row0 = tileB * BN + c0;
+      if (swapped) {
+        // lane <-> out feature n (contiguous in memory): each j is a coalesced warp store
+        const int n = a_row;
+        if (n < rowsA) {
+#pragma unroll
+          for (int j = 0; j < CH; ++j) {
+            const int m = b_row0 + j;
+            if (m < rowsB) {
+              const float v = __uint_as_float(r[j]);
+              if (ep.partial) ep.partial[(static_cast<long long>(split) * ep.M + m) * ep.N + n] = v;
+              else epi_store(ep, m, n, epi_apply(ep, m, n, v));
+            }
+          }
+        }
+      } else {
+        const int m = a_row;
+        if (m < rowsA) {
+          if (ep.partial) {
+            float* dst = ep.partial + (static_cast<long long>(split) * ep.M + m) * ep.N + b_row0;
+            if (b_row0 + CH <= rowsB && (ep.N & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < CH; j += 4)
+                *reinterpret_cast<float4*>(dst + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                                                  __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+            } else {
+              for (int j = 0; j < CH; ++j)
+                if (b_row0 + j < rowsB) dst[j] = __uint_as_float(r[j]);
+            }
+          } else {
+            float v[CH];
+#pragma unroll
+            for (int j = 0; j < CH; ++j)
+              v[j] = (b_row0 + j < rowsB) ? epi_apply(ep, m, b_row0 + j, __uint_as_float(r[j])) : 0.f;
+            const bool full_chunk = b_row0 + CH <= rowsB;
+            if (ep.out_f32) {
+              float* dst = reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + b_row0;
+              if (full_chunk && (ep.ldo & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < CH; j += 4)
+                  *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              } else {
+                for (int j = 0; j < CH; ++j)
+                  if (b_row0 + j < rowsB) dst[j] = v[j];
+              }
+            } else {
+              bf16* dst = reinterpret_cast<bf16*>(ep.out) + static_cast<long long>(m) * ep.ldo + b_row0;
+              if (full_chunk && (ep.ldo & 7) == 0) {
+#pragma unroll
+                for (int j = 0; j < CH; j += 8) {
+                  uint4 pk;
+                  pk.x = pack_bf16(v[j], v[j + 1]);
+                  pk.y = pack_bf16(v[j + 2], v[j + 3]);
+                  pk.z = pack_bf16(v[j + 4], v[j + 5]);
+                  pk.w = pack_bf16(v[j + 6], v[j + 7]);
+                  *reinterpret_cast<uint4*>(dst + j) = pk;
+                }
+              } else {
+                for (int j = 0; j < CH; ++j)
+                  if (b_row0 + j < rowsB) dst[j] = f2bf(v[j]);
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------------------------------------
+// split-K reduction + epilogue (deterministic order: split 0,1,2,...)
+// ---------------------------------------------------------------------------------------------
+__global__ void splitk_reduce_kernel(Epi ep, int splits) {
+  const long long total = static_cast<long long>(ep.M) * ep.N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = 0.f;
+    for (int s = 0; s < splits; ++s) v += ep.partial[s * total + i];
+    const int m = static_cast<int>(i / ep.N), n = static_cast<int>(i % ep.N);
+    epi_store(ep, m, n, epi_apply(ep, m, n, v));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// SIMT cross-check kernel (fp32 FMA; tests only).  One thread per output, 16x16 tiles.
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void gemm_simt_kernel(const T* __restrict__ x, long long ldx, const T* __restrict__ w, long long ldw, int K,
+                                 Epi ep) {
+  __shared__ float sx[16][17], sw[16][17];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int m = blockIdx.y * 16 + ty, n = blockIdx.x * 16 + tx;
+  float acc = 0.f;
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    const int mk = blockIdx.y * 16 + ty, nk = blockIdx.x * 16 + ty;
+    float a = 0.f, b = 0.f;
+    if (mk < ep.M && k0 + tx < K) a = static_cast<float>(x[static_cast<long long>(mk) * ldx + k0 + tx]);
+    if (nk < ep.N && k0 + tx < K) b = static_cast<float>(w[static_cast<long long>(nk) * ldw + k0 + tx]);
+    sx[ty][tx] = a;
+    sw[ty][tx] = b;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc += sx[ty][k] * sw[tx][k];
+    __syncthreads();
+  }
+  if (m < ep.M && n < ep.N) {
+    if (ep.partial) ep.partial[static_cast<long long>(m) * ep.N + n] = acc;
+    else epi_store(ep, m, n, epi_apply(ep, m, n, acc));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+template <int BN, int STAGES, int KIND>
+static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, int swapped, int rowsA, int rowsB,
+                     int k_blocks, int splits, uint64_t hintA, uint64_t hintB, cudaStream_t s) {
+  using L = GemmSmem<BN, STAGES>;
+  auto kern = gemm_tc_kernel<BN, STAGES, KIND>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal));
+    attr_set = true;
+  }
+  dim3 grid(cdiv(rowsA, kTileA), cdiv(rowsB, BN), splits);
+  kern<<<grid, kGemmThreads, L::kTotal, s>>>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hintA, hintB);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+template <int KIND>
+static int dispatch_tc(int BN, const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, int swapped, int rowsA,
+                       int rowsB, int k_blocks, int splits, uint64_t hA, uint64_t hB, cudaStream_t s) {
+  switch (BN) {
+    case 16: return launch_tc<16, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+    case 32: return launch_tc<32, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+    case 64: return launch_tc<64, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+    case 128: return launch_tc<128, 6, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+    case 256: return launch_tc<256, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+  }
+  return fail(MT_ERR_ARG, "unsupported BN %d", BN);
+}
+
+static int pick_bn_swapped(int M) {
+  if (M <= 16) return 16;
+  if (M <= 32) return 32;
+  if (M <= 64) return 64;
+  if (M <= 128) return 128;
+  return 256;
+}
+
+int linear(const LinearPlan& p, cudaStream_t s) {
+  MT_CHECK(p.M > 0 && p.N > 0 && p.K > 0, "linear: empty problem M=%d N=%d K=%d", p.M, p.N, p.K);
+  MT_CHECK(p.x && p.w, "linear: null operand");
+  Epi ep{};
+  ep.out = p.out; ep.ldo = p.ldo; ep.out_f32 = p.dtype_out == MT_DTYPE_F32;
+  ep.bias = p.bias; ep.act = p.act; ep.residual = p.residual; ep.ldr = p.ldr; ep.scale = p.scale;
+  ep.round_bf16 = p.round_bf16; ep.M = p.M; ep.N = p.N; ep.partial = nullptr;
+
+  if (p.impl == MT_GEMM_SIMT || g_force_simt) {
+    if (p.out_splits) { *p.out_splits = 1; ep.partial = p.workspace; }
+    dim3 grid(cdiv(p.N, 16), cdiv(p.M, 16)), block(16, 16);
+    if (p.dtype_in == MT_DTYPE_BF16)
+      gemm_simt_kernel<bf16><<<grid, block, 0, s>>>(reinterpret_cast<const bf16*>(p.x), p.ldx,
+                                                    reinterpret_cast<const bf16*>(p.w), p.ldw, p.K, ep);
+    else
+      gemm_simt_kernel<float><<<grid, block, 0, s>>>(reinterpret_cast<const float*>(p.x), p.ldx,
+                                                     reinterpret_cast<const float*>(p.w), p.ldw, p.K, ep);
+    count_launch();
+    MT_LAUNCH_CHECK();
+    return MT_OK;
+  }
+
+  const int esz = p.dtype_in == MT_DTYPE_BF16 ? 2 : 4;
+  const int k_elems = 128 / esz;
+  const int k_blocks = cdiv(p.K, k_elems);
+  const bool swapped = p.M <= 256;
+  int BN, rowsA, rowsB;
+  CUtensorMap tmA, tmB;
+  if (swapped) {
+    BN = pick_bn_swapped(p.M);
+    rowsA = p.N; rowsB = p.M;
+    if (p.w_tmap) tmA = *p.w_tmap;
+    else MT_TRY(make_tmap_2d(&tmA, p.w, p.dtype_in, p.N, p.K, p.ldw, kTileA));
+    MT_TRY(make_tmap_2d(&tmB, p.x, p.dtype_in, p.M, p.K, p.ldx, BN));
+  } else {
+    BN = 128;
+    rowsA = p.M; rowsB = p.N;
+    MT_TRY(make_tmap_2d(&tmA, p.x, p.dtype_in, p.M, p.K, p.ldx, kTileA));
+    if (p.w_tmap) tmB = *p.w_tmap;
+    else MT_TRY(make_tmap_2d(&tmB, p.w, p.dtype_in, p.N, p.K, p.ldw, BN));
+  }
+  // split-K: fill ~2 CTAs per SM when the tile grid alone cannot (decode-sized problems)
+  const int tiles = cdiv(rowsA, kTileA) * cdiv(rowsB, BN);
+  int splits = 1;
+  const long long per_split = static_cast<long long>(p.M) * p.N * 4;
+  if (p.workspace && tiles < 2 * kNumSMs) {
+    splits = (2 * kNumSMs) / tiles;
+    if (splits > k_blocks / 4) splits = k_blocks / 4;     // keep >= 4 k-blocks per CTA
+    if (splits > 16) splits = 16;
+    if (splits < 1) splits = 1;
+    while (splits > 1 && per_split * splits > p.workspace_bytes) --splits;
+  }
+  if (p.out_splits) {
+    MT_CHECK(p.workspace && per_split <= p.workspace_bytes, "linear: workspace too small for partial output");
+    *p.out_splits = splits;
+    ep.partial = p.workspace;
+  } else if (splits > 1) {
+    ep.partial = p.workspace;
+  }
+  // weights are streamed once in decode (evict-first); activations are re-read by every tile (evict-last)
+  const uint64_t hint_w = swapped ? ptx::kEvictFirst : ptx::kEvictNormal;
+  const uint64_t hint_x = ptx::kEvictLast;
+  const uint64_t hA = swapped ? hint_w : hint_x, hB = swapped ? hint_x : hint_w;
+  if (p.dtype_in == MT_DTYPE_BF16)
+    MT_TRY(dispatch_tc<1>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s));
+  else
+    MT_TRY(dispatch_tc<2>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s));
+  if (ep.partial && !p.out_splits) {
+    const long long total = static_cast<long long>(p.M) * p.N;
+    int blocks = static_cast<int>(cdivll(total, 256));
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ep, splits);
+    count_launch();
+    MT_LAUNCH_CHECK();
+  }
+  return MT_OK;
+}
+
+}  // namespace mt

@@ -1,0 +1,391 @@
+// Non-GEMM kernels of the MossTTSDelay decode/prefill step.  Every kernel rounds to bf16 exactly
+// where the reference's PyTorch ops return bf16 tensors (see oracle/lm.py), so greedy ids can match.
+//   a1  embed_sum            modeling_moss_tts.py:196-213
+//   a2  add_rmsnorm          Qwen3RMSNorm modeling_qwen3.py:59-64 + residual adds :305-335
+//       qkv_post             q/k RMSNorm + RoPE :263-268,:160-181 + KV append cache_utils.py:102-121
+//       attention            eager_attention_forward :196-217 (GQA, additive mask, fp32 softmax)
+//       silu_mul             Qwen3MLP :81-83
+#include "lm_ops.cuh"
+
+namespace mt {
+
+// ---------------------------------------------------------------------------------------------
+// a1: x[m,:] = E_text[id0] + sum_i emb_ext[i][id_{i+1}]   (left-to-right, bf16 after every add)
+// ---------------------------------------------------------------------------------------------
+__global__ void embed_sum_kernel(const int64_t* __restrict__ ids, const bf16* __restrict__ emb_text,
+                                 const bf16* __restrict__ emb_ext, bf16* __restrict__ out, int H, int n_vq,
+                                 int audio_rows, int vocab) {
+  const int m = blockIdx.x;
+  const int64_t* row = ids + static_cast<long long>(m) * (1 + n_vq);
+  for (int c = threadIdx.x * 8; c < H; c += blockDim.x * 8) {
+    long long t0 = row[0];
+    t0 = t0 < 0 ? 0 : (t0 >= vocab ? vocab - 1 : t0);
+    uint4 a = *reinterpret_cast<const uint4*>(emb_text + t0 * H + c);
+    float acc[8] = {bits_lo(a.x), bits_hi(a.x), bits_lo(a.y), bits_hi(a.y),
+                    bits_lo(a.z), bits_hi(a.z), bits_lo(a.w), bits_hi(a.w)};
+    for (int i = 0; i < n_vq; ++i) {
+      long long t = row[1 + i];
+      t = t < 0 ? 0 : (t >= audio_rows ? audio_rows - 1 : t);
+      uint4 b = *reinterpret_cast<const uint4*>(emb_ext + (static_cast<long long>(i) * audio_rows + t) * H + c);
+      const float e[8] = {bits_lo(b.x), bits_hi(b.x), bits_lo(b.y), bits_hi(b.y),
+                          bits_lo(b.z), bits_hi(b.z), bits_lo(b.w), bits_hi(b.w)};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = rbf(acc[j] + e[j]);
+    }
+    uint4 o;
+    o.x = pack_bf16(acc[0], acc[1]); o.y = pack_bf16(acc[2], acc[3]);
+    o.z = pack_bf16(acc[4], acc[5]); o.w = pack_bf16(acc[6], acc[7]);
+    *reinterpret_cast<uint4*>(out + static_cast<long long>(m) * H + c) = o;
+  }
+}
+
+int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf16* out, int M, int H, int n_vq,
+              int audio_rows, int vocab, cudaStream_t s) {
+  MT_CHECK(H % 8 == 0, "hidden size must be a multiple of 8");
+  int threads = H / 8 < 256 ? ((H / 8 + 31) / 32) * 32 : 256;
+  embed_sum_kernel<<<M, threads, 0, s>>>(ids, emb_text, emb_ext, out, H, n_vq, audio_rows, vocab);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// x_new = residual + bf16(delta)      (delta = bf16 tensor, or the sum of fp32 split-K partials)
+// normed = gain * bf16(x_new * rsqrt(mean(x_new^2) + eps))
+// One block per token row.
+// ---------------------------------------------------------------------------------------------
+__global__ void add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
+                                   const float* __restrict__ partials, int nsplit, long long split_stride,
+                                   bf16* __restrict__ x_out, const bf16* __restrict__ gain,
+                                   bf16* __restrict__ normed, int H, float eps) {
+  extern __shared__ float srow[];            // H floats + 33 scratch
+  float* scratch = srow + H;
+  const long long m = blockIdx.x;
+  float ss = 0.f;
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    float v;
+    if (partials) {
+      float a = 0.f;
+      for (int s = 0; s < nsplit; ++s) a += partials[s * split_stride + m * H + c];
+      v = rbf(a);
+    } else if (delta) {
+      v = bf2f(delta[m * H + c]);
+    } else {
+      v = 0.f;
+    }
+    if (residual) v = rbf(bf2f(residual[m * H + c]) + v);
+    if (x_out) x_out[m * H + c] = f2bf(v);
+    srow[c] = v;
+    ss += v * v;
+  }
+  ss = block_sum(ss, scratch);
+  const float inv = rsqrtf(ss / static_cast<float>(H) + eps);
+  if (normed) {
+    for (int c = threadIdx.x; c < H; c += blockDim.x)
+      normed[m * H + c] = f2bf(bf2f(gain[c]) * rbf(srow[c] * inv));
+  }
+}
+
+int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
+                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s) {
+  const size_t smem = (H + 40) * sizeof(float);
+  add_rmsnorm_kernel<<<M, 256, smem, s>>>(residual, delta, partials, nsplit, split_stride, x_out, gain, normed, H, eps);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// qkv_post: one warp per (token, head).  Input row layout [q heads | k heads | v heads] x D.
+//   q,k: RMSNorm over D with gain, then RoPE:  out = bf16(bf16(x*cos) + bf16(rot_half(x)*sin))
+//   q -> q_out[m, head, :];  k,v -> cache[(b, kvh, pos, :)]
+// Lane l owns elements {l, l+32, ...}; the RoPE partner of element j is j +- D/2, which is the
+// same lane for D = 64 and D = 128.
+// ---------------------------------------------------------------------------------------------
+template <int D>
+__global__ void qkv_post_kernel(const bf16* __restrict__ qkv, const float* __restrict__ partials, int nsplit,
+                                long long split_stride, const bf16* __restrict__ q_gain,
+                                const bf16* __restrict__ k_gain, const bf16* __restrict__ rope_cos,
+                                const bf16* __restrict__ rope_sin, bf16* __restrict__ q_out,
+                                bf16* __restrict__ k_cache, bf16* __restrict__ v_cache, int M, int T, int n_heads,
+                                int n_kv, int past_len, const int* __restrict__ past_len_dev, int max_seq,
+                                float eps) {
+  constexpr int E = D / 32;
+  const long long warp = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int heads_total = n_heads + 2 * n_kv;
+  const long long m = warp / heads_total;
+  const int hh = static_cast<int>(warp % heads_total);
+  if (m >= M) return;
+  const int b = static_cast<int>(m / T), t = static_cast<int>(m % T);
+  if (past_len_dev) past_len = *past_len_dev;
+  const int pos = past_len + t;
+  const long long row_w = static_cast<long long>(heads_total) * D;
+  float x[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    const long long idx = m * row_w + hh * D + lane + 32 * e;
+    if (partials) {
+      float a = 0.f;
+      for (int s = 0; s < nsplit; ++s) a += partials[s * split_stride + idx];
+      x[e] = rbf(a);
+    } else {
+      x[e] = bf2f(qkv[idx]);
+    }
+  }
+  if (hh < n_heads + n_kv) {
+    const bf16* gain = hh < n_heads ? q_gain : k_gain;
+    float ss = 0.f;
+#pragma unroll
+    for (int e = 0; e < E; ++e) ss += x[e] * x[e];
+    ss = warp_sum(ss);
+    const float inv = rsqrtf(ss / static_cast<float>(D) + eps);
+#pragma unroll
+    for (int e = 0; e < E; ++e) x[e] = rbf(bf2f(gain[lane + 32 * e]) * rbf(x[e] * inv));
+    float y[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      const int j = lane + 32 * e;
+      const int jh = j % (D / 2);
+      const float c = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
+      const float sn = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
+      const float partner = x[(e + E / 2) % E];
+      const float rot = j < D / 2 ? -partner : partner;
+      y[e] = rbf(rbf(x[e] * c) + rbf(rot * sn));
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) x[e] = y[e];
+  }
+  if (hh < n_heads) {
+#pragma unroll
+    for (int e = 0; e < E; ++e) q_out[(m * n_heads + hh) * D + lane + 32 * e] = f2bf(x[e]);
+  } else {
+    const bool is_k = hh < n_heads + n_kv;
+    const int kvh = is_k ? hh - n_heads : hh - n_heads - n_kv;
+    bf16* dst = (is_k ? k_cache : v_cache) + ((static_cast<long long>(b) * n_kv + kvh) * max_seq + pos) * D;
+#pragma unroll
+    for (int e = 0; e < E; ++e) dst[lane + 32 * e] = f2bf(x[e]);
+  }
+}
+
+int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
+             const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* q_out, bf16* k_cache,
+             bf16* v_cache, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
+             int max_seq, float eps, cudaStream_t s) {
+  const int heads_total = n_heads + 2 * n_kv;
+  const int M = B * T;
+  const long long warps = static_cast<long long>(M) * heads_total;
+  const int threads = 128;
+  const unsigned grid = static_cast<unsigned>(cdivll(warps * 32, threads));
+  if (D == 128)
+    qkv_post_kernel<128><<<grid, threads, 0, s>>>(qkv, partials, nsplit, split_stride, q_gain, k_gain, rope_cos,
+        rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev, max_seq, eps);
+  else if (D == 64)
+    qkv_post_kernel<64><<<grid, threads, 0, s>>>(qkv, partials, nsplit, split_stride, q_gain, k_gain, rope_cos,
+        rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev, max_seq, eps);
+  else
+    return fail(MT_ERR_UNSUPPORTED, "head_dim %d not supported (64 or 128)", D);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// GQA attention with the reference's eager rounding points.  One block per (query token, kv head,
+// batch row); the G = n_heads/n_kv query heads of the group share every K/V row read.
+//   s   = bf16(bf16(q.k) * scale)                     (matmul -> bf16, then * scaling -> bf16)
+//   p   = bf16(softmax_fp32(s over visible keys))     (masked keys get exactly 0)
+//   out = bf16(sum_k p_k * v_k)                        (fp32 accumulate)
+// visible(k) = k <= pos(query) and attn_mask[b,k].  A query with no visible key (left padding)
+// writes zeros.  Phase 1: one thread per key; phase 2: one thread per output dim.
+// ---------------------------------------------------------------------------------------------
+template <int D, int G>
+__global__ void attention_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_cache,
+                                 const bf16* __restrict__ v_cache, const uint8_t* __restrict__ mask,
+                                 long long mask_ld, bf16* __restrict__ out, int T, int n_heads, int n_kv,
+                                 int past_len, const int* __restrict__ past_len_dev, int max_seq, float scale) {
+  extern __shared__ float sm[];
+  const int t = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  if (past_len_dev) past_len = *past_len_dev;
+  const int nkeys = past_len + t + 1;
+  float* sq = sm;                       // [G][D]
+  float* sc = sm + G * D;               // [G][nkeys_pad]
+  const int npad = (nkeys + 3) & ~3;
+  float* scratch = sc + G * npad;       // 33
+  const long long m = static_cast<long long>(b) * T + t;
+  for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
+    const int g = i / D, d = i % D;
+    sq[i] = bf2f(q[(m * n_heads + kvh * G + g) * D + d]);
+  }
+  __syncthreads();
+  const bf16* kbase = k_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
+  const bf16* vbase = v_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
+  const uint8_t* mrow = mask + b * mask_ld;
+  float lmax[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) lmax[g] = -INFINITY;
+  for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
+    if (mrow[k]) {
+      float acc[G];
+#pragma unroll
+      for (int g = 0; g < G; ++g) acc[g] = 0.f;
+      const uint4* kr = reinterpret_cast<const uint4*>(kbase + static_cast<long long>(k) * D);
+#pragma unroll 4
+      for (int d8 = 0; d8 < D / 8; ++d8) {
+        const uint4 u = kr[d8];
+        const float kv[8] = {bits_lo(u.x), bits_hi(u.x), bits_lo(u.y), bits_hi(u.y),
+                             bits_lo(u.z), bits_hi(u.z), bits_lo(u.w), bits_hi(u.w)};
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[g] = fmaf(sq[g * D + d8 * 8 + j], kv[j], acc[g]);
+        }
+      }
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float sv = rbf(rbf(acc[g]) * scale);
+        sc[g * npad + k] = sv;
+        lmax[g] = fmaxf(lmax[g], sv);
+      }
+    } else {
+#pragma unroll
+      for (int g = 0; g < G; ++g) sc[g * npad + k] = -INFINITY;
+    }
+  }
+  float gmax[G], gsum[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) gmax[g] = block_max(lmax[g], scratch);
+  float lsum[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) lsum[g] = 0.f;
+  for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float sv = sc[g * npad + k];
+      const float e = (sv == -INFINITY) ? 0.f : __expf(sv - gmax[g]);
+      sc[g * npad + k] = e;
+      lsum[g] += e;
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g) gsum[g] = block_sum(lsum[g], scratch);
+  // normalise + round the probabilities to bf16 (the reference casts softmax output to q.dtype)
+  for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
+#pragma unroll
+    for (int g = 0; g < G; ++g) sc[g * npad + k] = gsum[g] > 0.f ? rbf(sc[g * npad + k] / gsum[g]) : 0.f;
+  }
+  __syncthreads();
+  // phase 2: thread d accumulates out[g][d] over keys
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float acc[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) acc[g] = 0.f;
+    for (int k = 0; k < nkeys; ++k) {
+      const float vv = bf2f(vbase[static_cast<long long>(k) * D + d]);
+#pragma unroll
+      for (int g = 0; g < G; ++g) acc[g] = fmaf(sc[g * npad + k], vv, acc[g]);
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) out[(m * n_heads + kvh * G + g) * D + d] = f2bf(acc[g]);
+  }
+}
+
+template <int D, int G>
+static int launch_attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask,
+                            long long mask_ld, bf16* out, int B, int T, int n_heads, int n_kv, int past_len,
+                            const int* past_len_dev, int max_keys, int max_seq, cudaStream_t s) {
+  const int npad = (max_keys + 3) & ~3;
+  const size_t smem = (static_cast<size_t>(G) * D + static_cast<size_t>(G) * npad + 40) * sizeof(float);
+  MT_CHECK(smem <= 200 * 1024, "attention: %d keys exceed the single-pass shared-memory budget", max_keys);
+  auto kern = attention_kernel<D, G>;
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    MT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    smem_set = 200 * 1024;
+  }
+  dim3 grid(T, n_kv, B);
+  kern<<<grid, 128, smem, s>>>(q, k_cache, v_cache, mask, mask_ld, out, T, n_heads, n_kv, past_len, past_len_dev,
+                               max_seq, 1.0f / sqrtf(static_cast<float>(D)));
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld,
+              bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
+              int max_keys, int max_seq, cudaStream_t s) {
+  const int G = n_heads / n_kv;
+#define MT_ATT(DD, GG)                                                                                   \
+  if (D == DD && G == GG)                                                                                \
+    return launch_attention<DD, GG>(q, k_cache, v_cache, mask, mask_ld, out, B, T, n_heads, n_kv, past_len, \
+                                    past_len_dev, max_keys, max_seq, s);
+  MT_ATT(128, 1) MT_ATT(128, 2) MT_ATT(128, 4) MT_ATT(128, 8)
+  MT_ATT(64, 1) MT_ATT(64, 2) MT_ATT(64, 4) MT_ATT(64, 8)
+#undef MT_ATT
+  return fail(MT_ERR_UNSUPPORTED, "attention: head_dim %d with group size %d not supported", D, G);
+}
+
+// ---------------------------------------------------------------------------------------------
+// act[m,i] = bf16(bf16(silu(gate)) * up),  gate/up = columns [0,I) / [I,2I) of the fused GEMM output
+// ---------------------------------------------------------------------------------------------
+__global__ void silu_mul_kernel(const bf16* __restrict__ gu, const float* __restrict__ partials, int nsplit,
+                                long long split_stride, bf16* __restrict__ act, long long M, int I) {
+  const long long total = M * I;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long m = idx / I;
+    const int i = static_cast<int>(idx % I);
+    float g, u;
+    if (partials) {
+      float a = 0.f, c = 0.f;
+      for (int s = 0; s < nsplit; ++s) {
+        a += partials[s * split_stride + m * 2 * I + i];
+        c += partials[s * split_stride + m * 2 * I + I + i];
+      }
+      g = rbf(a); u = rbf(c);
+    } else {
+      g = bf2f(gu[m * 2 * I + i]);
+      u = bf2f(gu[m * 2 * I + I + i]);
+    }
+    const float sg = rbf(g / (1.f + expf(-g)));
+    act[idx] = f2bf(sg * u);
+  }
+}
+
+int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
+             cudaStream_t s) {
+  const long long total = static_cast<long long>(M) * I;
+  int blocks = static_cast<int>(cdivll(total, 256));
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  silu_mul_kernel<<<blocks, 256, 0, s>>>(gu, partials, nsplit, split_stride, act, M, I);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// audio_logits[..., last] = -inf  (modeling_moss_tts.py:298-299)
+__global__ void fill_audio_pad_kernel(bf16* logits, long long rows, int head_size) {
+  const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < rows) logits[i * head_size + head_size - 1] = f2bf(-INFINITY);
+}
+int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s) {
+  fill_audio_pad_kernel<<<static_cast<unsigned>(cdivll(rows, 256)), 256, 0, s>>>(logits, rows, head_size);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// gather the last token of every batch row: dst[b,:] = src[b*T + T-1, :]
+__global__ void gather_last_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, int T, int H) {
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < H; c += blockDim.x)
+    dst[static_cast<long long>(b) * H + c] = src[(static_cast<long long>(b) * T + T - 1) * H + c];
+}
+int gather_last(const bf16* src, bf16* dst, int B, int T, int H, cudaStream_t s) {
+  gather_last_kernel<<<B, 256, 0, s>>>(src, dst, T, H);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+}  // namespace mt

@@ -1,0 +1,24 @@
+// Non-GEMM kernels of the MossTTSDelay step (lm_ops.cu) and the sampler (sampling.cu).
+#pragma once
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace mt {
+
+int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf16* out, int M, int H, int n_vq,
+              int audio_rows, int vocab, cudaStream_t s);
+int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
+                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s);
+int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
+             const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* q_out, bf16* k_cache,
+             bf16* v_cache, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
+             int max_seq, float eps, cudaStream_t s);
+int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld,
+              bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
+              int max_keys, int max_seq, cudaStream_t s);
+int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
+             cudaStream_t s);
+int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s);
+int gather_last(const bf16* src, bf16* dst, int B, int T, int H, cudaStream_t s);
+
+}  // namespace mt

@@ -1,0 +1,506 @@
+// Fused sampling + delay-pattern state machine: one launch samples every (row, channel) of a step,
+// a second tiny launch commits the state.  No host synchronisation inside a step.
+//   a4  text-logit masking / forced tokens     modeling_moss_tts.py:451-464
+//   a5  sample_token                           inference_utils.py:111-145 (penalty -> argmax | top-k -> top-p -> draw)
+//   a6  audio active mask + scatter            modeling_moss_tts.py:475-503
+//   a7  state update / history append          modeling_moss_tts.py:472-473,505-516
+//   a8  find_last_equal_C                      inference_utils.py:148-165
+//   a9  (de-)delay pattern                     processing_moss_tts.py:516-537
+// Logits are bf16; every transform returns the value a bf16 PyTorch tensor would hold.
+#include "sampling.cuh"
+
+namespace mt {
+
+constexpr int kSampThreads = 256;
+
+// ---- uniform hash shared with oracle/sampling.py::uniform_u ----------------------------------
+__host__ __device__ inline uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+  return x;
+}
+__host__ __device__ inline float mt_uniform(uint32_t seed, uint32_t step, uint32_t row, uint32_t channel) {
+  uint32_t h = mix32(seed ^ 0x9E3779B9u);
+  h = mix32(h ^ (step * 0x85EBCA6Bu));
+  h = mix32(h ^ (row * 0xC2B2AE35u));
+  h = mix32(h ^ (channel * 0x27D4EB2Fu));
+  return static_cast<float>(h >> 8) * (1.0f / 16777216.0f);
+}
+
+// ---- per-row logit transform -----------------------------------------------------------------
+struct RowXform {
+  const bf16* row; int V;
+  float temp;                 // value = bf16(l / temp)
+  int mode;                   // 0 plain, 1 text outside audio, 2 text inside audio
+  int ban[6]; int nban;       // ids forced to -inf (all modes)
+  int keep0, keep1;           // mode 2: everything else is -inf
+  const uint32_t* bitmap; float penalty;   // repetition penalty on ids whose bit is set
+  __device__ __forceinline__ float get(int i) const {
+    float v = bf2f(row[i]);
+    v = rbf(v / temp);
+    if (mode == 2 && i != keep0 && i != keep1) return -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 6; ++j)
+      if (j < nban && i == ban[j]) return -INFINITY;
+    if (bitmap && (bitmap[i >> 5] >> (i & 31) & 1u)) v = v > 0.f ? rbf(v / penalty) : rbf(v * penalty);
+    return v;
+  }
+};
+
+__device__ __forceinline__ uint32_t key16(float v) {
+  if (v != v) return 0u;                                  // NaN sorts below everything
+  const uint32_t b = __float_as_uint(v) >> 16;            // v is bf16-representable
+  return (b & 0x8000u) ? (~b & 0xFFFFu) : (b | 0x8000u);
+}
+__device__ __forceinline__ float unkey16(uint32_t k) {
+  const uint32_t b = (k & 0x8000u) ? (k & 0x7FFFu) : (~k & 0xFFFFu);
+  return __uint_as_float(b << 16);
+}
+constexpr uint32_t kKeyNegInf = 0x007Fu;
+
+// ---- greedy: first index of the maximum ------------------------------------------------------
+__device__ int row_argmax(const RowXform& x, uint32_t* s_u32) {
+  uint32_t best_k = 0; int best_i = 0x7fffffff;
+  for (int i = threadIdx.x; i < x.V; i += blockDim.x) {
+    const uint32_t k = key16(x.get(i));
+    if (k > best_k || (k == best_k && i < best_i)) { best_k = k; best_i = i; }
+  }
+  // pack (key, ~index) so that max() prefers the larger key, then the smaller index
+  unsigned long long p = (static_cast<unsigned long long>(best_k) << 32) | (0xFFFFFFFFu - static_cast<uint32_t>(best_i));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long q = __shfl_xor_sync(0xffffffffu, p, o);
+    p = q > p ? q : p;
+  }
+  unsigned long long* s64 = reinterpret_cast<unsigned long long*>(s_u32);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) s64[warp] = p;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long v = lane < (blockDim.x >> 5) ? s64[lane] : 0ull;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long q = __shfl_xor_sync(0xffffffffu, v, o);
+      v = q > v ? q : v;
+    }
+    if (lane == 0) s64[32] = v;
+  }
+  __syncthreads();
+  const unsigned long long r = s64[32];
+  __syncthreads();
+  return static_cast<int>(0xFFFFFFFFu - static_cast<uint32_t>(r & 0xFFFFFFFFu));
+}
+
+// ---- sampling: radix-select the k-th largest 16-bit key, collect, sort, top-p, draw ----------
+struct SampSmem {
+  int hist[256];
+  int scan[kSampThreads + 1];
+  unsigned long long cand[kMaxTopK];
+  int misc[8];
+  unsigned long long red[34];
+};
+
+// from the top bin down, find the bin where the running count reaches `need`
+__device__ void find_bin(const int* hist, int need, int* out_bin, int* out_above) {
+  int acc = 0;
+  for (int b = 255; b >= 0; --b) {
+    if (acc + hist[b] >= need) { *out_bin = b; *out_above = acc; return; }
+    acc += hist[b];
+  }
+  *out_bin = 0; *out_above = acc - hist[0];
+}
+
+__device__ int row_sample(const RowXform& x, int top_k, float top_p, float u, SampSmem& sm) {
+  const int tid = threadIdx.x;
+  const int k = top_k < x.V ? top_k : x.V;
+  // pass 1: high byte
+  for (int i = tid; i < 256; i += blockDim.x) sm.hist[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < x.V; i += blockDim.x) atomicAdd(&sm.hist[key16(x.get(i)) >> 8], 1);
+  __syncthreads();
+  if (tid == 0) find_bin(sm.hist, k, &sm.misc[0], &sm.misc[1]);
+  __syncthreads();
+  const int hi = sm.misc[0], above_hi = sm.misc[1];
+  // pass 2: low byte inside the selected high bin
+  for (int i = tid; i < 256; i += blockDim.x) sm.hist[i] = 0;
+  __syncthreads();
+  for (int i = tid; i < x.V; i += blockDim.x) {
+    const uint32_t kk = key16(x.get(i));
+    if (static_cast<int>(kk >> 8) == hi) atomicAdd(&sm.hist[kk & 255], 1);
+  }
+  __syncthreads();
+  if (tid == 0) find_bin(sm.hist, k - above_hi, &sm.misc[2], &sm.misc[3]);
+  __syncthreads();
+  const uint32_t thr = (static_cast<uint32_t>(hi) << 8) | static_cast<uint32_t>(sm.misc[2]);
+  const int need_eq = k - above_hi - sm.misc[3];
+  // pass 3: ordered collection.  Thread t owns the contiguous index segment [t*seg,(t+1)*seg) so a
+  // single block scan ranks ties by index (lowest index wins, as in the oracle).
+  const int seg = (x.V + blockDim.x - 1) / blockDim.x;
+  const int i0 = tid * seg, i1 = min(x.V, i0 + seg);
+  int n_gt = 0, n_eq = 0;
+  for (int i = i0; i < i1; ++i) {
+    const uint32_t kk = key16(x.get(i));
+    n_gt += kk > thr;
+    n_eq += kk == thr;
+  }
+  // exclusive scans of n_gt and n_eq over threads (packed: eq in the high half)
+  sm.scan[tid] = n_gt | (n_eq << 16);
+  __syncthreads();
+  if (tid == 0) {
+    int g = 0, e = 0;
+    for (int t = 0; t < static_cast<int>(blockDim.x); ++t) {
+      const int v = sm.scan[t];
+      sm.scan[t] = g | (e << 16);
+      g += v & 0xFFFF;
+      e = min(e + (v >> 16), 32767);     // only "rank < need_eq (<=1024)" matters; clamp to stay in 15 bits
+    }
+    sm.misc[4] = g;
+  }
+  __syncthreads();
+  const int total_gt = sm.misc[4];
+  int off_gt = sm.scan[tid] & 0xFFFF, off_eq = sm.scan[tid] >> 16;
+  for (int i = tid; i < kMaxTopK; i += blockDim.x) sm.cand[i] = ~0ull;
+  __syncthreads();
+  for (int i = i0; i < i1; ++i) {
+    const uint32_t kk = key16(x.get(i));
+    int slot = -1;
+    if (kk > thr) slot = off_gt++;
+    else if (kk == thr) { if (off_eq < need_eq) slot = total_gt + off_eq; off_eq++; }
+    if (slot >= 0 && slot < kMaxTopK && kk != kKeyNegInf && kk != 0u)
+      sm.cand[slot] = (static_cast<unsigned long long>(0xFFFFu - kk) << 32) | static_cast<uint32_t>(i);
+  }
+  __syncthreads();
+  // bitonic sort ascending on (0xFFFF-key, index)  ==  value descending, index ascending
+  int n2 = 1;
+  while (n2 < k) n2 <<= 1;
+  for (int size = 2; size <= n2; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = tid; i < n2; i += blockDim.x) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const unsigned long long a = sm.cand[i], b = sm.cand[j];
+          const bool up = (i & size) == 0;
+          if ((a > b) == up) { sm.cand[i] = b; sm.cand[j] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  // sequential tail on one thread: softmax -> top-p cut -> softmax -> inverse-CDF draw
+  if (tid == 0) {
+    int n = 0;
+    while (n < k && sm.cand[n] != ~0ull) ++n;
+    int result = 0;
+    if (n > 0) {
+      const float mx = unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[0] >> 32));
+      int keep = n;
+      if (top_p < 1.0f) {
+        float sum = 0.f;
+        for (int j = 0; j < n; ++j) sum += expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx);
+        const float thr_p = rbf(top_p);
+        float run = 0.f;
+        keep = 0;
+        for (int j = 0; j < n; ++j) {
+          // entry j is removed when the rounded cumulative sum of entries < j exceeds top_p
+          if (j > 0 && rbf(run) > thr_p) break;
+          ++keep;
+          run += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum);
+        }
+      }
+      float sum2 = 0.f;
+      for (int j = 0; j < keep; ++j) sum2 += expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx);
+      float total = 0.f;
+      for (int j = 0; j < keep; ++j)
+        total += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum2);
+      const float target = u * total;
+      float run2 = 0.f;
+      result = static_cast<int>(sm.cand[keep - 1] & 0xFFFFFFFFu);
+      for (int j = 0; j < keep; ++j) {
+        run2 += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum2);
+        if (run2 > target) { result = static_cast<int>(sm.cand[j] & 0xFFFFFFFFu); break; }
+      }
+    }
+    sm.misc[5] = result;
+  }
+  __syncthreads();
+  const int r = sm.misc[5];
+  __syncthreads();
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// one block per (channel, row)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSampThreads)
+gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
+                  const bf16* __restrict__ audio_logits, int audio_head, SampleCfg sc, TokenIds tk) {
+  __shared__ SampSmem sm;
+  if (*st.done) return;
+  const int ch = blockIdx.x, b = blockIdx.y;
+  const int n_vq = st.C - 1;
+  const int step = *st.step;
+  const int delayed = st.delayed[b];
+  int64_t* dst = st.next_ids + static_cast<long long>(b) * st.C + ch;
+  RowXform x;
+  x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1; x.bitmap = nullptr; x.penalty = 1.f;
+  if (ch == 0) {
+    // ---- text channel: forced tokens first (modeling_moss_tts.py:453-458)
+    int forced = -1;
+    if (st.stopping[b]) forced = tk.pad;
+    else if (delayed >= 0 && delayed < n_vq) forced = tk.delay_slot;
+    else if (delayed == n_vq) forced = tk.audio_end;
+    if (forced >= 0) { if (threadIdx.x == 0) *dst = forced; return; }
+    x.row = text_logits + static_cast<long long>(b) * vocab; x.V = vocab; x.temp = sc.text_temperature;
+    if (st.is_audio[b]) {
+      x.mode = 2; x.keep0 = tk.gen_slot; x.keep1 = tk.delay_slot;
+    } else {
+      x.mode = 1;
+      x.ban[0] = tk.pad; x.ban[1] = tk.gen_slot; x.ban[2] = tk.delay_slot; x.ban[3] = tk.audio_end; x.nban = 4;
+    }
+    if (step == 0) x.ban[x.nban++] = 151662;              // hard-coded id in the reference (:462)
+    if (step <= n_vq) x.ban[x.nban++] = tk.im_end;
+    int tok;
+    if (!sc.text_do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
+    else tok = row_sample(x, sc.text_top_k, sc.text_top_p, mt_uniform(sc.seed, step, b, 0), sm);
+    if (threadIdx.x == 0) *dst = tok;
+  } else {
+    // ---- audio channel i = ch-1 (modeling_moss_tts.py:475-503); lengths are the pre-update ones
+    const int i = ch - 1;
+    const bool active = st.audio_len[b] > i && (delayed < 0 || i > delayed - 1);
+    if (!active) { if (threadIdx.x == 0) *dst = tk.audio_pad_code; return; }
+    x.row = audio_logits + (static_cast<long long>(b) * n_vq + i) * audio_head; x.V = audio_head;
+    x.temp = sc.audio_temperature;
+    x.ban[0] = tk.audio_pad_code; x.nban = 1;
+    if (sc.penalty != 1.0f) { x.bitmap = i == 0 ? st.seen0 : st.seen_rest; x.penalty = sc.penalty; }
+    int tok;
+    if (!sc.audio_do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
+    else tok = row_sample(x, sc.audio_top_k, sc.audio_top_p, mt_uniform(sc.seed, step, b, ch), sm);
+    if (threadIdx.x == 0) *dst = tok;
+  }
+}
+
+// state update + history append (:472-473,505-516); a single block
+__global__ void gen_commit_kernel(GenState st, TokenIds tk) {
+  if (*st.done) return;
+  const int n_vq = st.C - 1;
+  const int len = *st.len;
+  int all_stopped = 1;
+  for (int b = threadIdx.x; b < st.B; b += blockDim.x) {
+    const int64_t* nx = st.next_ids + static_cast<long long>(b) * st.C;
+    const int tok = static_cast<int>(nx[0]);
+    int delayed = st.delayed[b];
+    uint8_t stopping = st.stopping[b], is_audio = st.is_audio[b];
+    if (!stopping && delayed == n_vq) is_audio = 0;          // is_audio[is_audio_eos] = False (:457)
+    if (tok == tk.audio_start) is_audio = 1;
+    if (tok == tk.im_end) stopping = 1;
+    int al = st.audio_len[b];
+    if (tok == tk.audio_start || tok == tk.gen_slot || tok == tk.delay_slot) al += 1;
+    if (tok == tk.audio_end) al = 0;
+    if (delayed < 0 && tok == tk.delay_slot) delayed = 0;
+    if (delayed >= 0) delayed += 1;
+    if (delayed > n_vq) delayed = -1;
+    st.audio_len[b] = al; st.delayed[b] = delayed; st.stopping[b] = stopping; st.is_audio[b] = is_audio;
+    if (len < st.max_len) {
+      int64_t* g = st.gen_ids + (static_cast<long long>(b) * st.max_len + len) * st.C;
+      for (int c = 0; c < st.C; ++c) g[c] = nx[c];
+      st.mask[static_cast<long long>(b) * st.max_len + len] = !stopping;
+    }
+    // repetition-penalty id sets grow with every appended row (pad code included, as torch.unique sees it)
+    const long long a0 = nx[1];
+    if (a0 >= 0 && a0 < st.bitmap_words * 32) atomicOr(&st.seen0[a0 >> 5], 1u << (a0 & 31));
+    for (int c = 2; c < st.C; ++c) {
+      const long long a = nx[c];
+      if (a >= 0 && a < st.bitmap_words * 32) atomicOr(&st.seen_rest[a >> 5], 1u << (a & 31));
+    }
+    all_stopped &= stopping;
+  }
+  all_stopped = __syncthreads_and(all_stopped);
+  if (threadIdx.x == 0) {
+    *st.len = len + 1;
+    *st.pos = len;
+    *st.step = *st.step + 1;
+    if (all_stopped) *st.done = 1;
+  }
+}
+
+// prologue of generate(): continuation detection, history/mask copy, penalty sets (:417-436,518)
+__global__ void gen_init_kernel(GenState st, const int64_t* __restrict__ input_ids,
+                                const uint8_t* __restrict__ attn_mask, int S0, TokenIds tk,
+                                int64_t* __restrict__ start_indices) {
+  const int b = blockIdx.x;
+  const int64_t* src = input_ids + static_cast<long long>(b) * S0 * st.C;
+  int64_t* g = st.gen_ids + static_cast<long long>(b) * st.max_len * st.C;
+  __shared__ int s_last_start, s_last_im;
+  if (threadIdx.x == 0) { s_last_start = -1; s_last_im = -1; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < S0 * st.C; i += blockDim.x) {
+    const int64_t v = src[i];
+    g[i] = v;
+    const int t = i / st.C, c = i % st.C;
+    if (c == 0) {
+      if (v == tk.audio_start) atomicMax(&s_last_start, t);
+      if (v == tk.im_start) atomicMax(&s_last_im, t);
+    } else if (v >= 0 && v < st.bitmap_words * 32) {
+      atomicOr(c == 1 ? &st.seen0[v >> 5] : &st.seen_rest[v >> 5], 1u << (v & 31));
+    }
+  }
+  for (int t = threadIdx.x; t < st.max_len; t += blockDim.x)
+    st.mask[static_cast<long long>(b) * st.max_len + t] = t < S0 ? (attn_mask ? attn_mask[static_cast<long long>(b) * S0 + t] : 1) : 0;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int64_t last = src[static_cast<long long>(S0 - 1) * st.C];
+    const bool cont = (last == tk.audio_start || last == tk.gen_slot) && s_last_start >= 0;
+    st.audio_len[b] = cont ? S0 - s_last_start : 0;
+    st.is_audio[b] = cont;
+    st.stopping[b] = 0;
+    st.delayed[b] = -1;
+    start_indices[b] = s_last_im + 3;
+    if (b == 0) { *st.len = S0; *st.step = 0; *st.done = 0; *st.pos = S0 - 1; }
+  }
+}
+
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+size_t gen_state_bytes(int B, int C, int max_len, int audio_head) {
+  const int words = (audio_head + 31) / 32;
+  size_t n = 256;                                       // scalars
+  n += align_up(B, 256) * 2;                            // stopping, is_audio
+  n += align_up(B * sizeof(int), 256) * 2;              // audio_len, delayed
+  n += align_up(static_cast<size_t>(B) * C * 8, 256);   // next_ids
+  n += align_up(static_cast<size_t>(B) * max_len, 256); // mask
+  n += align_up(words * 4, 256) * 2;
+  return n;
+}
+
+GenState gen_state_carve(void* buf, int B, int C, int max_len, int audio_head, int64_t* gen_ids) {
+  GenState st{};
+  uint8_t* p = reinterpret_cast<uint8_t*>(buf);
+  const int words = (audio_head + 31) / 32;
+  st.len = reinterpret_cast<int*>(p); st.step = st.len + 1; st.done = st.len + 2; st.pos = st.len + 3; p += 256;
+  st.stopping = p; p += align_up(B, 256);
+  st.is_audio = p; p += align_up(B, 256);
+  st.audio_len = reinterpret_cast<int*>(p); p += align_up(B * sizeof(int), 256);
+  st.delayed = reinterpret_cast<int*>(p); p += align_up(B * sizeof(int), 256);
+  st.next_ids = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * C * 8, 256);
+  st.mask = p; p += align_up(static_cast<size_t>(B) * max_len, 256);
+  st.seen0 = reinterpret_cast<uint32_t*>(p); p += align_up(words * 4, 256);
+  st.seen_rest = reinterpret_cast<uint32_t*>(p);
+  st.gen_ids = gen_ids; st.B = B; st.C = C; st.max_len = max_len; st.bitmap_words = words;
+  return st;
+}
+
+int gen_init(const GenState& st, const int64_t* input_ids, const uint8_t* attn_mask, int S0, const TokenIds& tk,
+             int64_t* start_indices, cudaStream_t s) {
+  MT_CUDA(cudaMemsetAsync(st.seen0, 0, st.bitmap_words * 4, s));
+  MT_CUDA(cudaMemsetAsync(st.seen_rest, 0, st.bitmap_words * 4, s));
+  gen_init_kernel<<<st.B, 256, 0, s>>>(st, input_ids, attn_mask, S0, tk, start_indices);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, const bf16* audio_logits, int audio_head,
+                    const SampleCfg& sc, const TokenIds& tk, cudaStream_t s) {
+  dim3 grid(st.C, st.B);
+  gen_sample_kernel<<<grid, kSampThreads, 0, s>>>(st, text_logits, vocab, audio_logits, audio_head, sc, tk);
+  gen_commit_kernel<<<1, 256, 0, s>>>(st, tk);
+  count_launch(2);
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// standalone sample_token (inference_utils.py:111-145) on [N,V] bf16 logits
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSampThreads)
+sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int V, float temperature,
+                     const uint32_t* __restrict__ bitmap, float penalty, float top_p, int top_k, int do_sample,
+                     const float* __restrict__ uniforms, int64_t* __restrict__ out) {
+  __shared__ SampSmem sm;
+  const int r = blockIdx.x;
+  RowXform x;
+  x.row = logits + r * ld; x.V = V; x.temp = temperature; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
+  x.bitmap = penalty != 1.0f ? bitmap : nullptr; x.penalty = penalty;
+  int tok;
+  if (!do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
+  else tok = row_sample(x, top_k, top_p, uniforms ? uniforms[r] : 0.f, sm);
+  if (threadIdx.x == 0) out[r] = tok;
+}
+
+int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
+                  float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
+                  cudaStream_t s) {
+  MT_CHECK(N > 0 && V > 0, "sample_tokens: empty input");
+  if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
+    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
+  MT_CHECK(temperature > 0.f, "temperature must be > 0");
+  sample_tokens_kernel<<<N, kSampThreads, 0, s>>>(logits, ld, V, temperature, prev_bitmap, penalty, top_p, top_k,
+                                                  do_sample, uniforms, out);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// find_last_equal_C: one warp per row, scanning from the end
+// ---------------------------------------------------------------------------------------------
+__global__ void find_last_equal_kernel(const int64_t* __restrict__ t, int B, int S, long long ld, long long value,
+                                       int64_t* __restrict__ out) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= B) return;
+  int best = -1;
+  for (int i = lane; i < S; i += 32)
+    if (t[row * ld + i] == value) best = i;       // ascending per lane: the last hit survives
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+  if (lane == 0) out[row] = best;
+}
+int find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out, cudaStream_t s) {
+  MT_CHECK(B > 0, "find_last_equal: empty batch");
+  find_last_equal_kernel<<<cdiv(B * 32, 128), 128, 0, s>>>(t, B, S, ld, value, out);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// delay pattern: out[t+i, i] = codes[t, i], pad elsewhere; de-delay: out[t, i] = in[t+i, i]
+// ---------------------------------------------------------------------------------------------
+__global__ void delay_kernel(const int64_t* __restrict__ codes, int T, int n, long long pad, int64_t* __restrict__ out) {
+  const long long total = static_cast<long long>(T + n - 1) * n;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int r = static_cast<int>(idx / n), i = static_cast<int>(idx % n);
+    const int t = r - i;
+    out[idx] = (t >= 0 && t < T) ? codes[static_cast<long long>(t) * n + i] : pad;
+  }
+}
+__global__ void dedelay_kernel(const int64_t* __restrict__ in, int T, int n, int64_t* __restrict__ out) {
+  const long long total = static_cast<long long>(T) * n;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(idx / n), i = static_cast<int>(idx % n);
+    out[idx] = in[static_cast<long long>(t + i) * n + i];
+  }
+}
+int apply_delay_pattern(const int64_t* codes, int T, int n, long long pad, int64_t* out, cudaStream_t s) {
+  MT_CHECK(T >= 0 && n > 0, "apply_delay_pattern: bad shape");
+  const long long total = static_cast<long long>(T + n - 1) * n;
+  if (total <= 0) return MT_OK;
+  delay_kernel<<<static_cast<unsigned>(min(cdivll(total, 256), 4096LL)), 256, 0, s>>>(codes, T, n, pad, out);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+int apply_de_delay_pattern(const int64_t* delayed, int Td, int n, int64_t* out, cudaStream_t s) {
+  const int T = Td - n + 1;
+  MT_CHECK(n > 0, "apply_de_delay_pattern: bad shape");
+  if (T <= 0) return MT_OK;
+  const long long total = static_cast<long long>(T) * n;
+  dedelay_kernel<<<static_cast<unsigned>(min(cdivll(total, 256), 4096LL)), 256, 0, s>>>(delayed, T, n, out);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+}  // namespace mt

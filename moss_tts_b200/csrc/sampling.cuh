@@ -1,0 +1,59 @@
+// Fused per-step sampler + delay-pattern state machine (sampling.cu).
+#pragma once
+#include "common.cuh"
+#include "gemm.cuh"
+
+namespace mt {
+
+constexpr int kMaxTopK = 1024;
+
+// Device-resident generation state of one generate() call (reference modeling_moss_tts.py:417-440).
+struct GenState {
+  // scalars (device)
+  int* len;          // filled sequence positions (prompt + generated) == past_len of the next forward
+  int* step;         // time_step
+  int* done;         // all rows stopped
+  int* pos;          // index of the row appended by the last commit (= KV position of the next decode input)
+  // per row
+  uint8_t* stopping;
+  uint8_t* is_audio;
+  int* audio_len;
+  int* delayed;      // -1 encodes the reference's INT64_MAX sentinel
+  // token buffers
+  int64_t* next_ids; // [B, C] tokens chosen this step == input of the next forward
+  int64_t* gen_ids;  // [B, max_len, C]
+  uint8_t* mask;     // [B, max_len]
+  uint32_t* seen0;   // repetition-penalty bitmaps over audio ids: channel 1 / channels 2..n_vq
+  uint32_t* seen_rest;
+  int B, C, max_len, bitmap_words;
+};
+
+struct SampleCfg {
+  float text_temperature, text_top_p; int text_top_k, text_do_sample;
+  float audio_temperature, audio_top_p; int audio_top_k, audio_do_sample;
+  float penalty;
+  unsigned seed;
+};
+
+struct TokenIds {
+  int pad, im_start, im_end, audio_start, audio_end, gen_slot, delay_slot, audio_pad_code;
+};
+
+size_t gen_state_bytes(int B, int C, int max_len, int audio_head);
+// carve `buf` (device) into a GenState; gen_ids is caller-provided
+GenState gen_state_carve(void* buf, int B, int C, int max_len, int audio_head, int64_t* gen_ids);
+
+int gen_init(const GenState& st, const int64_t* input_ids, const uint8_t* attn_mask, int S0, const TokenIds& tk,
+             int64_t* start_indices, cudaStream_t s);
+// text_logits [B, vocab] bf16, audio_logits [B, n_vq, audio_head] bf16 (last position of this step)
+int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, const bf16* audio_logits, int audio_head,
+                    const SampleCfg& sc, const TokenIds& tk, cudaStream_t s);
+
+int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
+                  float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
+                  cudaStream_t s);
+int find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out, cudaStream_t s);
+int apply_delay_pattern(const int64_t* codes, int T, int n, long long pad, int64_t* out, cudaStream_t s);
+int apply_de_delay_pattern(const int64_t* delayed, int Td, int n, int64_t* out, cudaStream_t s);
+
+}  // namespace mt
