@@ -1,0 +1,92 @@
+"""tcgen05/TMA GEMM vs a plain torch fp32 reference (and the SIMT cross-check kernel), through mt_gemm."""
+import pytest
+import torch
+
+from moss_tts_b200 import _lib as L
+from gpu_util import DEV, gemm
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(x, w, bias=None, act=0, residual=None, scale=None, round_bf16=0, out_dtype=None):
+    v = x.float() @ w.float().T
+    if bias is not None:
+        v = v + bias
+    if act == 1:
+        v = torch.nn.functional.gelu(v)
+    if round_bf16:
+        v = v.to(torch.bfloat16).float()
+    if residual is not None:
+        v = residual.float() + (scale * v if scale is not None else v)
+    elif scale is not None:
+        v = scale * v
+    return v
+
+
+SHAPES = [(1, 256, 128), (16, 384, 256), (64, 1024, 512), (64, 1025 * 4, 256), (200, 512, 192), (256, 640, 1280),
+          (300, 512, 256), (1000, 1536, 512), (130, 240, 768), (4096, 1024, 1024)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
+def test_gemm_bf16(M, N, K, impl):
+    g = torch.Generator(device=DEV).manual_seed(M * 7 + N)
+    x = torch.randn(M, K, device=DEV, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(torch.bfloat16)
+    out = gemm(x, w, impl=impl)
+    ref = _ref(x, w)
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 2e-2 * max(1.0, ref.abs().max().item()), err
+    # fp32 output exposes accumulation differences without the bf16 rounding
+    out32 = gemm(x, w, out_dtype=torch.float32, impl=impl)
+    assert (out32 - ref).abs().max().item() <= 2e-3, (out32 - ref).abs().max().item()
+
+
+@pytest.mark.parametrize("M,N,K", [(64, 512, 4096), (8, 4096, 12288)])
+def test_gemm_bf16_splitk_matches_unsplit(M, N, K):
+    g = torch.Generator(device=DEV).manual_seed(3)
+    x = torch.randn(M, K, device=DEV, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(torch.bfloat16)
+    a = gemm(x, w, out_dtype=torch.float32, workspace_mb=64)
+    b = gemm(x, w, out_dtype=torch.float32, workspace_mb=0)
+    ref = _ref(x, w)
+    assert (a - ref).abs().max().item() <= 2e-3
+    assert (b - ref).abs().max().item() <= 2e-3
+
+
+@pytest.mark.parametrize("M,N,K", [(32, 768, 512), (250, 1280, 768), (1000, 3072, 768), (700, 240, 768)])
+@pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
+def test_gemm_tf32_epilogues(M, N, K, impl):
+    g = torch.Generator(device=DEV).manual_seed(N)
+    x = torch.randn(M, K, device=DEV, generator=g)
+    w = torch.randn(N, K, device=DEV, generator=g) * K ** -0.5
+    bias = torch.randn(N, device=DEV, generator=g)
+    scale = torch.randn(N, device=DEV, generator=g)
+    res = torch.randn(M, N, device=DEV, generator=g)
+    tol = 1e-4 if impl == L.MT_GEMM_SIMT else 1e-2      # TF32 inputs keep 10 mantissa bits
+    for kw in (dict(), dict(bias=bias), dict(act=1), dict(residual=res, scale=scale), dict(bias=bias, act=1, residual=res)):
+        out = gemm(x, w, impl=impl, **kw)
+        ref = _ref(x, w, **kw)
+        err = (out - ref).abs().max().item()
+        assert err <= tol * max(1.0, ref.abs().max().item()), (kw.keys(), err)
+
+
+def test_gemm_bf16_lm_epilogue():
+    g = torch.Generator(device=DEV).manual_seed(11)
+    M, N, K = 48, 512, 256
+    x = torch.randn(M, K, device=DEV, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(torch.bfloat16)
+    res = torch.randn(M, N, device=DEV, generator=g).to(torch.bfloat16)
+    out = gemm(x, w, residual=res, round_bf16=1)
+    ref = _ref(x, w, residual=res, round_bf16=1).to(torch.bfloat16)
+    # identical rounding points: at most 1 bf16 ulp apart, and almost everywhere identical
+    diff = (out.float() - ref.float()).abs()
+    assert diff.max().item() <= 2e-2
+    assert (diff > 0).float().mean().item() < 0.02
+
+
+def test_gemm_rejects_bad_args():
+    x = torch.zeros(4, 100, device=DEV, dtype=torch.bfloat16)     # K*2 bytes not a multiple of 16
+    w = torch.zeros(8, 100, device=DEV, dtype=torch.bfloat16)
+    with pytest.raises(ValueError):
+        gemm(x, w)
