@@ -37,6 +37,7 @@ struct mt_lm {
   size_t ws_bytes;
   // graph
   cudaGraphExec_t graph_exec = nullptr;
+  cudaStream_t cap_stream = nullptr;   // capture-only stream (the caller's stream may be the legacy default stream)
   int graph_B = 0; long long graph_key = 0;
 };
 
@@ -203,6 +204,7 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
 extern "C" int mt_lm_destroy(mt_lm* h) {
   if (!h) return MT_OK;
   if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+  if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   delete h;
   return MT_OK;
 }
@@ -284,10 +286,12 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
       if (!exec) {
         // capture one decode step (step 1 ran eagerly so every lazy attribute/JIT path is warm)
         cudaGraph_t graph = nullptr;
-        if (cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { status = fail(MT_ERR_CUDA, "begin capture failed"); break; }
+        if (!h->cap_stream && cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking) != cudaSuccess) { status = fail(MT_ERR_CUDA, "capture stream creation failed"); break; }
+        cudaError_t be = cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal);
+        if (be != cudaSuccess) { status = fail(MT_ERR_CUDA, "begin capture failed: %s", cudaGetErrorString(be)); break; }
         const long long before = g_launches;
-        status = decode_step(s);
-        cudaError_t ce = cudaStreamEndCapture(s, &graph);
+        status = decode_step(h->cap_stream);
+        cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
         if (status == MT_OK && ce != cudaSuccess) status = fail(MT_ERR_CUDA, "end capture: %s", cudaGetErrorString(ce));
         if (status == MT_OK && cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) status = fail(MT_ERR_CUDA, "graph instantiate failed");
         if (graph) cudaGraphDestroy(graph);

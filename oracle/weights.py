@@ -51,10 +51,11 @@ def make_lm_weights(cfg: LMConfig, seed: int = 0, never_stop: bool = False,
     w["language_model.norm.weight"] = _normal(seed, "norm", (H,), 0.1, 1.0)
     for i in range(cfg.n_vq):
         w[f"emb_ext.{i}.weight"] = _normal(seed, f"emb_ext{i}", (cfg.audio_head_size, H), std)
-    # heads get a larger std so that greedy argmax margins are not all sub-ulp
-    w["lm_heads.0.weight"] = _normal(seed, "head0", (cfg.vocab_size, H), 4 * std)
+    # heads keep the HF init scale: |logits| stays below 4, where one bf16 ulp (<= 1.6e-2) is inside the
+    # 2e-2 absolute logit tolerance of the north star
+    w["lm_heads.0.weight"] = _normal(seed, "head0", (cfg.vocab_size, H), std)
     for i in range(cfg.n_vq):
-        w[f"lm_heads.{i + 1}.weight"] = _normal(seed, f"head{i + 1}", (cfg.audio_head_size, H), 4 * std)
+        w[f"lm_heads.{i + 1}.weight"] = _normal(seed, f"head{i + 1}", (cfg.audio_head_size, H), std)
     if never_stop:
         w["lm_heads.0.weight"][cfg.audio_assistant_delay_slot_token_id] = \
             w["lm_heads.0.weight"][cfg.audio_assistant_gen_slot_token_id]

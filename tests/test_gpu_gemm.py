@@ -85,6 +85,7 @@ def test_gemm_bf16_lm_epilogue():
     assert (diff > 0).float().mean().item() < 0.02
 
 
+@pytest.mark.skipif(__import__("os").environ.get("MT_FORCE_SIMT") == "1", reason="TMA alignment only applies to the tcgen05 path")
 def test_gemm_rejects_bad_args():
     x = torch.zeros(4, 100, device=DEV, dtype=torch.bfloat16)     # K*2 bytes not a multiple of 16
     w = torch.zeros(8, 100, device=DEV, dtype=torch.bfloat16)

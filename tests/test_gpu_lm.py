@@ -79,14 +79,18 @@ def test_teacher_forced_logits(name):
     logits = model.forward(ids, mask).logits
     oracle = OracleLM(cfg, w, torch.bfloat16).forward(ids, mask)
     valid = mask.bool()
-    worst = 0.0
+    worst, ndiff, ntot, big = 0.0, 0, 0, 0.0
     for i, (mine, ref) in enumerate(zip(logits, oracle)):
         mine = mine.float().cpu()[valid]
         ref = ref.float()[valid]
         assert torch.equal(torch.isinf(mine), torch.isinf(ref)), f"head {i}: -inf pattern differs"
         fin = torch.isfinite(ref)
-        worst = max(worst, (mine[fin] - ref[fin]).abs().max().item())
-    print(f"[{name}] teacher-forced logits max-abs vs oracle: {worst:.4g}")
+        d = (mine[fin] - ref[fin]).abs()
+        worst = max(worst, d.max().item())
+        ndiff += int((d > 0).sum()); ntot += d.numel()
+        big = max(big, ref[fin].abs().max().item())
+    print(f"[{name}] teacher-forced logits max-abs vs oracle: {worst:.4g}; {ndiff}/{ntot} logits differ "
+          f"({100.0 * ndiff / ntot:.3f}%), max |logit| {big:.3g}")
     assert worst <= LOGIT_TOL
     # and against the reference-minted digest
     pos = g["tf_positions"].tolist()
