@@ -393,12 +393,18 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const int tiles = cdiv(rowsA, kTileA) * cdiv(rowsB, BN);
   int splits = 1;
   const long long per_split = static_cast<long long>(p.M) * p.N * 4;
-  if (p.workspace && tiles < 2 * kNumSMs) {
-    splits = (2 * kNumSMs) / tiles;
-    if (splits > k_blocks / 4) splits = k_blocks / 4;     // keep >= 4 k-blocks per CTA
-    if (splits > 16) splits = 16;
-    if (splits < 1) splits = 1;
-    while (splits > 1 && per_split * splits > p.workspace_bytes) --splits;
+  if (p.workspace && tiles < 4 * kNumSMs) {
+    // pick the split count whose CTA total fills whole waves of 2 CTAs/SM best; ties -> fewer splits
+    const int slots = 2 * kNumSMs;
+    double best_eff = 0.0;
+    for (int sp = 1; sp <= 16; ++sp) {
+      if (sp > 1 && k_blocks / sp < 4) break;                       // keep >= 4 k-blocks per CTA
+      if (per_split * sp > p.workspace_bytes) break;
+      const int ctas = tiles * sp;
+      const int waves = (ctas + slots - 1) / slots;
+      const double eff = static_cast<double>(ctas) / (static_cast<double>(waves) * slots);
+      if (eff > best_eff + 0.02) { best_eff = eff; splits = sp; }
+    }
   }
   if (p.out_splits) {
     MT_CHECK(p.workspace && per_split <= p.workspace_bytes, "linear: workspace too small for partial output");

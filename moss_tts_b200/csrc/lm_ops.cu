@@ -54,42 +54,64 @@ int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf1
 // normed = gain * bf16(x_new * rsqrt(mean(x_new^2) + eps))
 // One block per token row.
 // ---------------------------------------------------------------------------------------------
-__global__ void add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
-                                   const float* __restrict__ partials, int nsplit, long long split_stride,
-                                   bf16* __restrict__ x_out, const bf16* __restrict__ gain,
-                                   bf16* __restrict__ normed, int H, float eps) {
+__global__ void __launch_bounds__(1024)
+add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
+                   const float* __restrict__ partials, int nsplit, long long split_stride,
+                   bf16* __restrict__ x_out, const bf16* __restrict__ gain, bf16* __restrict__ normed, int H,
+                   float eps) {
   extern __shared__ float srow[];            // H floats + 33 scratch
   float* scratch = srow + H;
   const long long m = blockIdx.x;
   float ss = 0.f;
-  for (int c = threadIdx.x; c < H; c += blockDim.x) {
-    float v;
+  // 4 elements per thread and iteration: every split's float4 is an independent 16-byte load
+  for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
     if (partials) {
-      float a = 0.f;
-      for (int s = 0; s < nsplit; ++s) a += partials[s * split_stride + m * H + c];
-      v = rbf(a);
+      const float* p = partials + m * H + c;
+#pragma unroll 4
+      for (int s = 0; s < nsplit; ++s) {
+        const float4 t = *reinterpret_cast<const float4*>(p + s * split_stride);
+        v[0] += t.x; v[1] += t.y; v[2] += t.z; v[3] += t.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = rbf(v[j]);
     } else if (delta) {
-      v = bf2f(delta[m * H + c]);
-    } else {
-      v = 0.f;
+      const uint2 d = *reinterpret_cast<const uint2*>(delta + m * H + c);
+      v[0] = bits_lo(d.x); v[1] = bits_hi(d.x); v[2] = bits_lo(d.y); v[3] = bits_hi(d.y);
     }
-    if (residual) v = rbf(bf2f(residual[m * H + c]) + v);
-    if (x_out) x_out[m * H + c] = f2bf(v);
-    srow[c] = v;
-    ss += v * v;
+    if (residual) {
+      const uint2 r = *reinterpret_cast<const uint2*>(residual + m * H + c);
+      v[0] = rbf(bits_lo(r.x) + v[0]); v[1] = rbf(bits_hi(r.x) + v[1]);
+      v[2] = rbf(bits_lo(r.y) + v[2]); v[3] = rbf(bits_hi(r.y) + v[3]);
+    }
+    if (x_out) {
+      uint2 o; o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
+      *reinterpret_cast<uint2*>(x_out + m * H + c) = o;
+    }
+    *reinterpret_cast<float4*>(srow + c) = make_float4(v[0], v[1], v[2], v[3]);
+    ss += v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
   }
   ss = block_sum(ss, scratch);
   const float inv = rsqrtf(ss / static_cast<float>(H) + eps);
   if (normed) {
-    for (int c = threadIdx.x; c < H; c += blockDim.x)
-      normed[m * H + c] = f2bf(bf2f(gain[c]) * rbf(srow[c] * inv));
+    for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+      const float4 x = *reinterpret_cast<const float4*>(srow + c);
+      const uint2 g = *reinterpret_cast<const uint2*>(gain + c);
+      uint2 o;
+      o.x = pack_bf16(bits_lo(g.x) * rbf(x.x * inv), bits_hi(g.x) * rbf(x.y * inv));
+      o.y = pack_bf16(bits_lo(g.y) * rbf(x.z * inv), bits_hi(g.y) * rbf(x.w * inv));
+      *reinterpret_cast<uint2*>(normed + m * H + c) = o;
+    }
   }
 }
 
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
                 bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s) {
+  MT_CHECK(H % 4 == 0, "hidden size must be a multiple of 4");
   const size_t smem = (H + 40) * sizeof(float);
-  add_rmsnorm_kernel<<<M, 256, smem, s>>>(residual, delta, partials, nsplit, split_stride, x_out, gain, normed, H, eps);
+  int threads = ((H / 4 + 31) / 32) * 32;
+  if (threads > 1024) threads = 1024;
+  add_rmsnorm_kernel<<<M, threads, smem, s>>>(residual, delta, partials, nsplit, split_stride, x_out, gain, normed, H, eps);
   count_launch();
   MT_LAUNCH_CHECK();
   return MT_OK;
@@ -199,19 +221,24 @@ int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split
 // visible(k) = k <= pos(query) and attn_mask[b,k].  A query with no visible key (left padding)
 // writes zeros.  Phase 1: one thread per key; phase 2: one thread per output dim.
 // ---------------------------------------------------------------------------------------------
+constexpr int kAttThreads = 256;
+
 template <int D, int G>
-__global__ void attention_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_cache,
-                                 const bf16* __restrict__ v_cache, const uint8_t* __restrict__ mask,
-                                 long long mask_ld, bf16* __restrict__ out, int T, int n_heads, int n_kv,
-                                 int past_len, const int* __restrict__ past_len_dev, int max_seq, float scale) {
+__global__ void __launch_bounds__(kAttThreads)
+attention_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
+                 const uint8_t* __restrict__ mask, long long mask_ld, bf16* __restrict__ out, int T, int n_heads,
+                 int n_kv, int past_len, const int* __restrict__ past_len_dev, int max_seq, float scale) {
   extern __shared__ float sm[];
+  constexpr int NW = kAttThreads / 32;
+  constexpr int E = D / 32;               // output dims per lane in phase 2
   const int t = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   if (past_len_dev) past_len = *past_len_dev;
   const int nkeys = past_len + t + 1;
-  float* sq = sm;                       // [G][D]
-  float* sc = sm + G * D;               // [G][nkeys_pad]
   const int npad = (nkeys + 3) & ~3;
-  float* scratch = sc + G * npad;       // 33
+  float* sq = sm;                         // [G][D]
+  float* red = sm + G * D;                // [NW][G][D] partial outputs
+  float* sc = red + NW * G * D;           // [G][npad] scores / probabilities
+  float* scratch = sc + G * npad;         // 33
   const long long m = static_cast<long long>(b) * T + t;
   for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
     const int g = i / D, d = i % D;
@@ -224,6 +251,7 @@ __global__ void attention_kernel(const bf16* __restrict__ q, const bf16* __restr
   float lmax[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) lmax[g] = -INFINITY;
+  // phase 1: one thread per key, 16-byte loads along the K row
   for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
     if (mrow[k]) {
       float acc[G];
@@ -269,24 +297,46 @@ __global__ void attention_kernel(const bf16* __restrict__ q, const bf16* __restr
   }
 #pragma unroll
   for (int g = 0; g < G; ++g) gsum[g] = block_sum(lsum[g], scratch);
-  // normalise + round the probabilities to bf16 (the reference casts softmax output to q.dtype)
   for (int k = threadIdx.x; k < nkeys; k += blockDim.x) {
 #pragma unroll
     for (int g = 0; g < G; ++g) sc[g * npad + k] = gsum[g] > 0.f ? rbf(sc[g * npad + k] / gsum[g]) : 0.f;
   }
   __syncthreads();
-  // phase 2: thread d accumulates out[g][d] over keys
-  for (int d = threadIdx.x; d < D; d += blockDim.x) {
-    float acc[G];
+  // phase 2: warp w takes keys w, w+NW, ...; lane owns E consecutive dims (one 4/8-byte load per V row)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc[G][E];
 #pragma unroll
-    for (int g = 0; g < G; ++g) acc[g] = 0.f;
-    for (int k = 0; k < nkeys; ++k) {
-      const float vv = bf2f(vbase[static_cast<long long>(k) * D + d]);
+  for (int g = 0; g < G; ++g)
 #pragma unroll
-      for (int g = 0; g < G; ++g) acc[g] = fmaf(sc[g * npad + k], vv, acc[g]);
+    for (int e = 0; e < E; ++e) acc[g][e] = 0.f;
+#pragma unroll 4
+  for (int k = warp; k < nkeys; k += NW) {
+    float vv[E];
+    if constexpr (E == 4) {
+      const uint2 u = *reinterpret_cast<const uint2*>(vbase + static_cast<long long>(k) * D + lane * 4);
+      vv[0] = bits_lo(u.x); vv[1] = bits_hi(u.x); vv[2] = bits_lo(u.y); vv[3] = bits_hi(u.y);
+    } else {
+      const uint32_t u = *reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(k) * D + lane * 2);
+      vv[0] = bits_lo(u); vv[1] = bits_hi(u);
     }
 #pragma unroll
-    for (int g = 0; g < G; ++g) out[(m * n_heads + kvh * G + g) * D + d] = f2bf(acc[g]);
+    for (int g = 0; g < G; ++g) {
+      const float p = sc[g * npad + k];
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[g][e] = fmaf(p, vv[e], acc[g][e]);
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+#pragma unroll
+    for (int e = 0; e < E; ++e) red[(warp * G + g) * D + lane * E + e] = acc[g][e];
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) v += red[w * G * D + i];
+    const int g = i / D, d = i % D;
+    out[(m * n_heads + kvh * G + g) * D + d] = f2bf(v);
   }
 }
 
@@ -295,7 +345,7 @@ static int launch_attention(const bf16* q, const bf16* k_cache, const bf16* v_ca
                             long long mask_ld, bf16* out, int B, int T, int n_heads, int n_kv, int past_len,
                             const int* past_len_dev, int max_keys, int max_seq, cudaStream_t s) {
   const int npad = (max_keys + 3) & ~3;
-  const size_t smem = (static_cast<size_t>(G) * D + static_cast<size_t>(G) * npad + 40) * sizeof(float);
+  const size_t smem = (static_cast<size_t>(G) * D * (1 + kAttThreads / 32) + static_cast<size_t>(G) * npad + 40) * sizeof(float);
   MT_CHECK(smem <= 200 * 1024, "attention: %d keys exceed the single-pass shared-memory budget", max_keys);
   auto kern = attention_kernel<D, G>;
   static size_t smem_set = 0;
@@ -304,7 +354,7 @@ static int launch_attention(const bf16* q, const bf16* k_cache, const bf16* v_ca
     smem_set = 200 * 1024;
   }
   dim3 grid(T, n_kv, B);
-  kern<<<grid, 128, smem, s>>>(q, k_cache, v_cache, mask, mask_ld, out, T, n_heads, n_kv, past_len, past_len_dev,
+  kern<<<grid, kAttThreads, smem, s>>>(q, k_cache, v_cache, mask, mask_ld, out, T, n_heads, n_kv, past_len, past_len_dev,
                                max_seq, 1.0f / sqrtf(static_cast<float>(D)));
   count_launch();
   MT_LAUNCH_CHECK();
@@ -330,31 +380,43 @@ int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uin
 // ---------------------------------------------------------------------------------------------
 __global__ void silu_mul_kernel(const bf16* __restrict__ gu, const float* __restrict__ partials, int nsplit,
                                 long long split_stride, bf16* __restrict__ act, long long M, int I) {
-  const long long total = M * I;
+  const int I4 = I / 4;
+  const long long total = M * I4;
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long m = idx / I;
-    const int i = static_cast<int>(idx % I);
-    float g, u;
+    const long long m = idx / I4;
+    const int i = static_cast<int>(idx % I4) * 4;
+    float g[4], u[4];
     if (partials) {
-      float a = 0.f, c = 0.f;
+      float a[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
+      const float* p = partials + m * 2 * I + i;
+#pragma unroll 4
       for (int s = 0; s < nsplit; ++s) {
-        a += partials[s * split_stride + m * 2 * I + i];
-        c += partials[s * split_stride + m * 2 * I + I + i];
+        const float4 x = *reinterpret_cast<const float4*>(p + s * split_stride);
+        const float4 y = *reinterpret_cast<const float4*>(p + s * split_stride + I);
+        a[0] += x.x; a[1] += x.y; a[2] += x.z; a[3] += x.w;
+        c[0] += y.x; c[1] += y.y; c[2] += y.z; c[3] += y.w;
       }
-      g = rbf(a); u = rbf(c);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { g[j] = rbf(a[j]); u[j] = rbf(c[j]); }
     } else {
-      g = bf2f(gu[m * 2 * I + i]);
-      u = bf2f(gu[m * 2 * I + I + i]);
+      const uint2 x = *reinterpret_cast<const uint2*>(gu + m * 2 * I + i);
+      const uint2 y = *reinterpret_cast<const uint2*>(gu + m * 2 * I + I + i);
+      g[0] = bits_lo(x.x); g[1] = bits_hi(x.x); g[2] = bits_lo(x.y); g[3] = bits_hi(x.y);
+      u[0] = bits_lo(y.x); u[1] = bits_hi(y.x); u[2] = bits_lo(y.y); u[3] = bits_hi(y.y);
     }
-    const float sg = rbf(g / (1.f + expf(-g)));
-    act[idx] = f2bf(sg * u);
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) r[j] = rbf(g[j] / (1.f + expf(-g[j]))) * u[j];
+    uint2 o; o.x = pack_bf16(r[0], r[1]); o.y = pack_bf16(r[2], r[3]);
+    *reinterpret_cast<uint2*>(act + m * I + i) = o;
   }
 }
 
 int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
              cudaStream_t s) {
-  const long long total = static_cast<long long>(M) * I;
+  MT_CHECK(I % 4 == 0, "intermediate size must be a multiple of 4");
+  const long long total = static_cast<long long>(M) * (I / 4);
   int blocks = static_cast<int>(cdivll(total, 256));
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
   silu_mul_kernel<<<blocks, 256, 0, s>>>(gu, partials, nsplit, split_stride, act, M, I);

@@ -260,6 +260,19 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
     if (step == 0) x.ban[x.nban++] = 151662;              // hard-coded id in the reference (:462)
     if (step <= n_vq) x.ban[x.nban++] = tk.im_end;
     int tok;
+    if (x.mode == 2 && !sc.text_do_sample) {
+      // inside audio only the gen/delay slots survive the mask: compare the two logits directly
+      // (first max index on ties; an all -inf row argmaxes to index 0 like torch.argmax)
+      if (threadIdx.x == 0) {
+        const int i0 = min(x.keep0, x.keep1), i1 = max(x.keep0, x.keep1);
+        const float v0 = x.get(i0), v1 = x.get(i1);
+        int t = 0;
+        if (v0 == -INFINITY && v1 == -INFINITY) t = 0;
+        else t = v1 > v0 ? i1 : i0;
+        *dst = t;
+      }
+      return;
+    }
     if (!sc.text_do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
     else tok = row_sample(x, sc.text_top_k, sc.text_top_p, mt_uniform(sc.seed, step, b, 0), sm);
     if (threadIdx.x == 0) *dst = tok;
