@@ -170,7 +170,8 @@ def time_dominant_kernel(model, batch, iters=3):
 
     def launch(w):
         a = L.GemmArgs(L.MT_DTYPE_BF16, L.MT_DTYPE_BF16, batch, N, H, x.data_ptr(), H, w.data_ptr(), H, out.data_ptr(), N,
-                       None, 0, None, 0, None, 0, ws.data_ptr(), ws.numel(), L.MT_GEMM_AUTO)
+                       None, 0, None, 0, None, 0, ws.data_ptr(), ws.numel(),
+                       L.MT_GEMM_W_STATIC | (L.MT_GEMM_W_TILED if model.weights_tiled else 0))
         L.check(L.lib().mt_gemm(C.byref(a), sp), "mt_gemm")
     for w in model._w["gu"]:
         launch(w)                                  # warm-up pass

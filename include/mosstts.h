@@ -46,6 +46,14 @@ extern "C" {
 
 #define MT_GEMM_AUTO 0   /* tcgen05/TMA kernel (the product path) */
 #define MT_GEMM_SIMT 1   /* plain CUDA-core kernel, used by tests to cross-check the tcgen05 kernel */
+/* OR-able flag for mt_gemm_args.impl: `w` is constant for the lifetime of the stream work in flight
+ * (model weights), so the kernel may fetch weight tiles BEFORE the preceding kernel on the stream has
+ * finished (programmatic dependent launch); x / residual / out are still ordered normally. */
+#define MT_GEMM_W_STATIC 2
+/* OR-able flag: `w` is stored tile-major, [ceil(N/128)][K/ke][128][ke] with ke = 64 (bf16) / 32 (fp32):
+ * every 128-row x 128-byte operand tile is one contiguous 16 KB run (rows past N are zero padding).
+ * This is the HBM layout the decode GEMMs stream fastest; ldw is ignored. */
+#define MT_GEMM_W_TILED 4
 
 typedef void* mt_stream; /* cudaStream_t */
 
@@ -55,6 +63,9 @@ const char* mt_last_error(void);
 long long mt_launch_count(void);
 /* Debug knob for tests: force every internal GEMM to MT_GEMM_SIMT (1) or back to tcgen05 (0). */
 int mt_debug_force_simt(int on);
+/* Debug knob: launch kernels with (1, default) or without (0) the programmatic-dependent-launch
+ * attribute.  Results are bit-identical either way; only kernel overlap changes. */
+int mt_debug_set_pdl(int on);
 
 /* ------------------------------------------------------------------------------------------
  * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:
@@ -92,6 +103,7 @@ typedef struct {
   int audio_pad_code;
   int max_batch, max_seq;       /* KV-cache capacity */
   int max_tokens;               /* largest B*T a single forward call may see */
+  int weights_tiled;            /* 1: every Linear weight (w_qkv/w_o/w_gate_up/w_down/heads) is tile-major, see MT_GEMM_W_TILED */
 } mt_lm_config;
 
 /* All weights bf16, row-major [out,in] as in nn.Linear / nn.Embedding. */

@@ -15,11 +15,11 @@ CSRC = os.path.join(_HERE, "csrc")
 
 MT_OK, MT_ERR_ARG, MT_ERR_CUDA, MT_ERR_UNSUPPORTED = 0, -1, -2, -3
 MT_DTYPE_BF16, MT_DTYPE_F32 = 0, 1
-MT_GEMM_AUTO, MT_GEMM_SIMT = 0, 1
+MT_GEMM_AUTO, MT_GEMM_SIMT, MT_GEMM_W_STATIC, MT_GEMM_W_TILED = 0, 1, 2, 4
 MT_CODEC_MAX_STAGES = 8
 
 EXPORTS = [
-    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_gemm",
+    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_gemm",
     "mt_lm_query_sizes", "mt_lm_create", "mt_lm_destroy", "mt_lm_forward", "mt_lm_generate",
     "mt_sample_tokens", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
     "mt_codec_create", "mt_codec_destroy", "mt_codec_workspace_bytes", "mt_rvq_fold_tables",
@@ -46,7 +46,7 @@ class LMConfigC(C.Structure):
                [(n, C.c_int) for n in ("pad_token_id", "im_start_token_id", "im_end_token_id", "audio_start_token_id",
                                        "audio_end_token_id", "audio_assistant_gen_slot_token_id",
                                        "audio_assistant_delay_slot_token_id", "audio_pad_code", "max_batch", "max_seq",
-                                       "max_tokens")]
+                                       "max_tokens", "weights_tiled")]
 
 
 class LMWeightsC(C.Structure):

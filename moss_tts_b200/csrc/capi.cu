@@ -2,13 +2,15 @@
 #include "gemm.cuh"
 #include "sampling.cuh"
 
-namespace mt { const char* last_error(); }
+namespace mt { const char* last_error(); void set_pdl(int on); }
 using namespace mt;
 
 extern "C" int mt_version(void) { return 100; }
 extern "C" const char* mt_last_error(void) { return mt::last_error(); }
 extern "C" long long mt_launch_count(void) { return g_launches; }
 extern "C" int mt_debug_force_simt(int on) { g_force_simt = on != 0; return MT_OK; }
+
+extern "C" int mt_debug_set_pdl(int on) { mt::set_pdl(on); return MT_OK; }
 
 extern "C" int mt_gemm(const mt_gemm_args* a, mt_stream s) {
   MT_CHECK(a, "mt_gemm: null args");
@@ -19,7 +21,9 @@ extern "C" int mt_gemm(const mt_gemm_args* a, mt_stream s) {
   p.x = a->x; p.ldx = a->ldx; p.w = a->w; p.ldw = a->ldw; p.out = a->out; p.ldo = a->ldo;
   p.bias = a->bias; p.act = a->act; p.residual = a->residual; p.ldr = a->ldr; p.scale = a->scale;
   p.round_bf16 = a->round_bf16; p.workspace = a->workspace; p.workspace_bytes = a->workspace_bytes;
-  p.impl = a->impl;
+  p.impl = a->impl & MT_GEMM_SIMT;
+  p.w_static = (a->impl & MT_GEMM_W_STATIC) != 0;
+  p.w_tiled = (a->impl & MT_GEMM_W_TILED) != 0;
   return linear(p, reinterpret_cast<cudaStream_t>(s));
 }
 

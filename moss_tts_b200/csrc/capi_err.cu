@@ -10,3 +10,16 @@ int fail(int code, const char* fmt, ...) {
 }
 const char* last_error() { return g_err.c_str(); }
 }
+
+#include <stdlib.h>
+namespace mt {
+static int g_pdl_state = -1;   // -1 = read MT_NO_PDL from the environment on first use
+bool pdl_enabled() {
+  if (g_pdl_state < 0) {
+    const char* e = getenv("MT_NO_PDL");
+    g_pdl_state = (e && e[0] && e[0] != '0') ? 0 : 1;
+  }
+  return g_pdl_state == 1;
+}
+void set_pdl(int on) { g_pdl_state = on ? 1 : 0; }
+}

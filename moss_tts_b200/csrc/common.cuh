@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string>
+#include <utility>
 
 #include "../../include/mosstts.h"
 
@@ -36,6 +37,30 @@ int fail(int code, const char* fmt, ...);
 #define MT_LAUNCH_CHECK() MT_CUDA(cudaGetLastError())
 
 constexpr int kNumSMs = 148;  // B200
+
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------
+// Every kernel of the library starts with pdl_trigger() (the next kernel on the stream may be
+// scheduled once all our CTAs are resident) and calls pdl_wait() before it touches any memory an
+// earlier kernel of the stream may still be writing.  Work that only reads constants (weights,
+// tables) may be issued before pdl_wait(): that is how a GEMM streams the first weight tiles into
+// shared memory / L2 while the previous kernel is still running.  Both instructions are no-ops for
+// a kernel launched without the attribute.  MT_NO_PDL=1 in the environment disables the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(std::forward<Args>(args))...);
+}
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline long long cdivll(long long a, long long b) { return (a + b - 1) / b; }

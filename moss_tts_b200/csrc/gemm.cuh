@@ -9,6 +9,9 @@ namespace mt {
 int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, long long K, long long ld_elems,
                  int box_rows);
 
+// Same for a tile-major weight matrix (see LinearPlan::w_tiled); box = one 16 KB tile.
+int make_tmap_tiled(CUtensorMap* out, const void* base, int dtype, long long N, long long K);
+
 struct LinearPlan {
   // y[M,N] = x[M,K] . w[N,K]^T
   int dtype_in = MT_DTYPE_BF16, dtype_out = MT_DTYPE_BF16;
@@ -27,6 +30,12 @@ struct LinearPlan {
   int* out_splits = nullptr;
   int impl = MT_GEMM_AUTO;
   const CUtensorMap* w_tmap = nullptr;   // optional cached weight map (box rows 128)
+  // w is constant while the stream's work is in flight: weight tiles may be fetched (smem + L2
+  // prefetch) before the previous kernel finished (PDL).  Never set it for a w produced on-stream.
+  bool w_static = false;
+  // w is stored tile-major: [ceil(N/128)][K/k_elems][128][k_elems] (k_elems = 64 bf16 / 32 fp32), so
+  // each TMA box is 16 KB of consecutive HBM addresses.  ldw is ignored; w_tmap must match.
+  bool w_tiled = false;
 };
 
 // Launches the GEMM.  With out_splits == nullptr the result is complete in `out` on return of the

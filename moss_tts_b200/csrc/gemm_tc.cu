@@ -15,11 +15,18 @@
 #include "ptx.cuh"
 
 #include <mutex>
+#include <stdlib.h>
 
 namespace mt {
 
 bool g_force_simt = false;
 long long g_launches = 0;
+// bytes of weight tiles a decode GEMM asks L2 to prefetch before it waits for the previous kernel
+// (MT_PF_MB in the environment overrides; 0 disables)
+long long g_pf_bytes = [] {
+  const char* e = getenv("MT_PF_MB");
+  return (e ? atoll(e) : 40ll) << 20;
+}();
 
 // ---------------------------------------------------------------------------------------------
 // tensor maps
@@ -56,6 +63,15 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, 
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(MT_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", static_cast<int>(r));
   return MT_OK;
+}
+
+// Tile-major weights: [ceil(N/128)][K/k_elems][128][k_elems], i.e. every {128 rows x 128 B} operand
+// tile is one contiguous 16 KB run in HBM (a TMA box then reads 16 KB of consecutive addresses instead
+// of 128 runs of 128 B at a K*esz pitch).  Rows beyond N in the last tile are zero padding.
+int make_tmap_tiled(CUtensorMap* out, const void* base, int dtype, long long N, long long K) {
+  const int k_elems = dtype == MT_DTYPE_BF16 ? 64 : 32;
+  const long long rows = ((N + 127) / 128) * (K / k_elems) * 128;
+  return make_tmap_2d(out, base, dtype, rows, k_elems, k_elems, 128);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -109,7 +125,9 @@ struct GemmSmem {
 template <int BN, int STAGES, int KIND /*1 bf16, 2 tf32*/>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep,
-               int swapped, int rowsA, int rowsB, int k_blocks, int splits, uint64_t hintA, uint64_t hintB) {
+               int swapped, int rowsA, int rowsB, int k_blocks, int splits, uint64_t hintA, uint64_t hintB,
+               int early /*0: none, 1: operand A is constant weights, 2: operand B is*/, int pf_kblocks,
+               int tiled /*0: row-major operands, 1: A is tile-major, 2: B is*/) {
   using L = GemmSmem<BN, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -143,18 +161,56 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
+  if (threadIdx.x == 0) pdl_trigger();   // the next kernel may take our place as CTAs retire
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+      // Operand loads.  `tiled` (1: A, 2: B) marks a weight operand stored tile-major: every
+      // {128 rows x 128 B} block of the matrix is one contiguous 16 KB run, addressed as rows
+      // [(row_tile * k_blocks + kb) * 128, +128) of a [*, 128 B] matrix (see LinearPlan::w_tiled).
+      auto load_a = [&](int st, int kb) {
+        uint8_t* sa = smem + st * L::kStageBytes;
+        if (tiled == 1) ptx::tma_load_2d(sa, &tmA, &full[st], 0, (tileA * k_blocks + kb) * kTileA, hintA);
+        else ptx::tma_load_2d(sa, &tmA, &full[st], kb * kKElems, tileA * kTileA, hintA);
+      };
+      auto load_b = [&](int st, int kb) {
+        uint8_t* sb = smem + st * L::kStageBytes + L::kABytes;
+        if (tiled == 2) {
+#pragma unroll
+          for (int r = 0; r < BN / 128; ++r)
+            ptx::tma_load_2d(sb + r * 128 * kTileKBytes, &tmB, &full[st], 0,
+                             ((tileB * (BN / 128) + r) * k_blocks + kb) * 128, hintB);
+        } else {
+          ptx::tma_load_2d(sb, &tmB, &full[st], kb * kKElems, tileB * BN, hintB);
+        }
+      };
+      // Constant weights do not depend on the previous kernel: fill the ring with their tiles (and ask
+      // L2 for the following ones) before waiting for it, so HBM keeps streaming across the boundary.
+      const int n = kb1 - kb0;
+      const int pre = early ? (n < STAGES ? n : STAGES) : 0;
+      for (int it = 0; it < pre; ++it) {
+        ptx::mbar_expect_tx(&full[it], L::kStageBytes);
+        if (early == 1) load_a(it, kb0 + it); else load_b(it, kb0 + it);
+      }
+      if (early == 1 && pf_kblocks > 0) {
+        const int pf_end = pre + pf_kblocks < n ? pre + pf_kblocks : n;
+        for (int it = pre; it < pf_end; ++it) {
+          if (tiled == 1) ptx::tma_prefetch_2d(&tmA, 0, (tileA * k_blocks + kb0 + it) * kTileA);
+          else ptx::tma_prefetch_2d(&tmA, (kb0 + it) * kKElems, tileA * kTileA);
+        }
+      }
+      pdl_wait();
+      for (int it = 0; it < pre; ++it) {
+        if (early == 1) load_b(it, kb0 + it); else load_a(it, kb0 + it);
+      }
+      for (int kb = kb0 + pre, it = pre; kb < kb1; ++kb, ++it) {
         const int st = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         ptx::mbar_wait(&empty[st], ph ^ 1);
         ptx::mbar_expect_tx(&full[st], L::kStageBytes);
-        uint8_t* sa = smem + st * L::kStageBytes;
-        ptx::tma_load_2d(sa, &tmA, &full[st], kb * kKElems, tileA * kTileA, hintA);
-        ptx::tma_load_2d(sa + L::kABytes, &tmB, &full[st], kb * kKElems, tileB * BN, hintB);
+        load_a(st, kb);
+        load_b(st, kb);
       }
     }
   } else if (warp == 1) {
@@ -184,6 +240,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int a_row = tileA * kTileA + q * 32 + lane;
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
+    pdl_wait();                          // residual reads / output writes are ordered after the previous kernel
     const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     constexpr int CH = BN < 32 ? 16 : 32;
 #pragma unroll 1
@@ -269,6 +326,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // split-K reduction + epilogue (deterministic order: split 0,1,2,...)
 // ---------------------------------------------------------------------------------------------
 __global__ void splitk_reduce_kernel(Epi ep, int splits) {
+  pdl_trigger();
+  pdl_wait();
   const long long total = static_cast<long long>(ep.M) * ep.N;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -284,8 +343,11 @@ __global__ void splitk_reduce_kernel(Epi ep, int splits) {
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void gemm_simt_kernel(const T* __restrict__ x, long long ldx, const T* __restrict__ w, long long ldw, int K,
-                                 Epi ep) {
+                                 Epi ep, int w_tiled) {
+  constexpr int KE = 128 / static_cast<int>(sizeof(T));   // elements per 128-byte k-block
   __shared__ float sx[16][17], sw[16][17];
+  pdl_trigger();
+  pdl_wait();
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int m = blockIdx.y * 16 + ty, n = blockIdx.x * 16 + tx;
   float acc = 0.f;
@@ -293,7 +355,12 @@ __global__ void gemm_simt_kernel(const T* __restrict__ x, long long ldx, const T
     const int mk = blockIdx.y * 16 + ty, nk = blockIdx.x * 16 + ty;
     float a = 0.f, b = 0.f;
     if (mk < ep.M && k0 + tx < K) a = static_cast<float>(x[static_cast<long long>(mk) * ldx + k0 + tx]);
-    if (nk < ep.N && k0 + tx < K) b = static_cast<float>(w[static_cast<long long>(nk) * ldw + k0 + tx]);
+    if (nk < ep.N && k0 + tx < K) {
+      const int k = k0 + tx;
+      const long long off = w_tiled ? ((static_cast<long long>(nk >> 7) * (K / KE) + k / KE) * 128 + (nk & 127)) * KE + k % KE
+                                    : static_cast<long long>(nk) * ldw + k;
+      b = static_cast<float>(w[off]);
+    }
     sx[ty][tx] = a;
     sw[ty][tx] = b;
     __syncthreads();
@@ -312,7 +379,8 @@ __global__ void gemm_simt_kernel(const T* __restrict__ x, long long ldx, const T
 // ---------------------------------------------------------------------------------------------
 template <int BN, int STAGES, int KIND>
 static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, int swapped, int rowsA, int rowsB,
-                     int k_blocks, int splits, uint64_t hintA, uint64_t hintB, cudaStream_t s) {
+                     int k_blocks, int splits, uint64_t hintA, uint64_t hintB, int early, long long pf_bytes,
+                     int tiled, cudaStream_t s) {
   using L = GemmSmem<BN, STAGES>;
   auto kern = gemm_tc_kernel<BN, STAGES, KIND>;
   static bool attr_set = false;
@@ -321,21 +389,30 @@ static int launch_tc(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& 
     attr_set = true;
   }
   dim3 grid(cdiv(rowsA, kTileA), cdiv(rowsB, BN), splits);
-  kern<<<grid, kGemmThreads, L::kTotal, s>>>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hintA, hintB);
+  // L2 prefetch depth per CTA: spread pf_bytes of weight tiles over the CTAs of the first wave
+  int pf_kblocks = 0;
+  if (early) {
+    const long long ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
+    const long long resident = static_cast<long long>(kNumSMs) * (L::kTotal > 113 * 1024 ? 1 : 2);
+    const long long tile_bytes = early == 1 ? L::kABytes : L::kBBytes;
+    pf_kblocks = static_cast<int>(pf_bytes / ((ctas < resident ? ctas : resident) * tile_bytes));
+  }
+  MT_CUDA(launch(kern, grid, dim3(kGemmThreads), L::kTotal, s, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits,
+                 hintA, hintB, early, pf_kblocks, tiled));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
 template <int KIND>
 static int dispatch_tc(int BN, const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, int swapped, int rowsA,
-                       int rowsB, int k_blocks, int splits, uint64_t hA, uint64_t hB, cudaStream_t s) {
+                       int rowsB, int k_blocks, int splits, uint64_t hA, uint64_t hB, int early, long long pf,
+                       int tiled, cudaStream_t s) {
   switch (BN) {
-    case 16: return launch_tc<16, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
-    case 32: return launch_tc<32, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
-    case 64: return launch_tc<64, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
-    case 128: return launch_tc<128, 6, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
-    case 256: return launch_tc<256, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s);
+    case 16: return launch_tc<16, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+    case 32: return launch_tc<32, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+    case 64: return launch_tc<64, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+    case 128: return launch_tc<128, 6, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+    case 256: return launch_tc<256, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
   }
   return fail(MT_ERR_ARG, "unsupported BN %d", BN);
 }
@@ -360,13 +437,12 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     if (p.out_splits) { *p.out_splits = 1; ep.partial = p.workspace; }
     dim3 grid(cdiv(p.N, 16), cdiv(p.M, 16)), block(16, 16);
     if (p.dtype_in == MT_DTYPE_BF16)
-      gemm_simt_kernel<bf16><<<grid, block, 0, s>>>(reinterpret_cast<const bf16*>(p.x), p.ldx,
-                                                    reinterpret_cast<const bf16*>(p.w), p.ldw, p.K, ep);
+      MT_CUDA(launch(gemm_simt_kernel<bf16>, grid, block, 0, s, reinterpret_cast<const bf16*>(p.x), p.ldx,
+                     reinterpret_cast<const bf16*>(p.w), p.ldw, p.K, ep, static_cast<int>(p.w_tiled)));
     else
-      gemm_simt_kernel<float><<<grid, block, 0, s>>>(reinterpret_cast<const float*>(p.x), p.ldx,
-                                                     reinterpret_cast<const float*>(p.w), p.ldw, p.K, ep);
+      MT_CUDA(launch(gemm_simt_kernel<float>, grid, block, 0, s, reinterpret_cast<const float*>(p.x), p.ldx,
+                     reinterpret_cast<const float*>(p.w), p.ldw, p.K, ep, static_cast<int>(p.w_tiled)));
     count_launch();
-    MT_LAUNCH_CHECK();
     return MT_OK;
   }
 
@@ -376,10 +452,12 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const bool swapped = p.M <= 256;
   int BN, rowsA, rowsB;
   CUtensorMap tmA, tmB;
+  if (p.w_tiled) MT_CHECK(p.K % k_elems == 0, "linear: tile-major weights need K %% %d == 0 (K=%d)", k_elems, p.K);
   if (swapped) {
     BN = pick_bn_swapped(p.M);
     rowsA = p.N; rowsB = p.M;
     if (p.w_tmap) tmA = *p.w_tmap;
+    else if (p.w_tiled) MT_TRY(make_tmap_tiled(&tmA, p.w, p.dtype_in, p.N, p.K));
     else MT_TRY(make_tmap_2d(&tmA, p.w, p.dtype_in, p.N, p.K, p.ldw, kTileA));
     MT_TRY(make_tmap_2d(&tmB, p.x, p.dtype_in, p.M, p.K, p.ldx, BN));
   } else {
@@ -387,8 +465,10 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     rowsA = p.M; rowsB = p.N;
     MT_TRY(make_tmap_2d(&tmA, p.x, p.dtype_in, p.M, p.K, p.ldx, kTileA));
     if (p.w_tmap) tmB = *p.w_tmap;
+    else if (p.w_tiled) MT_TRY(make_tmap_tiled(&tmB, p.w, p.dtype_in, p.N, p.K));
     else MT_TRY(make_tmap_2d(&tmB, p.w, p.dtype_in, p.N, p.K, p.ldw, BN));
   }
+  const int tiled = p.w_tiled ? (swapped ? 1 : 2) : 0;
   // split-K: fill ~2 CTAs per SM when the tile grid alone cannot (decode-sized problems)
   const int tiles = cdiv(rowsA, kTileA) * cdiv(rowsB, BN);
   int splits = 1;
@@ -417,17 +497,20 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const uint64_t hint_w = swapped ? ptx::kEvictFirst : ptx::kEvictNormal;
   const uint64_t hint_x = ptx::kEvictLast;
   const uint64_t hA = swapped ? hint_w : hint_x, hB = swapped ? hint_x : hint_w;
+  // constant weights: stream the first tiles before the previous kernel has finished (PDL).  The L2
+  // prefetch only pays in the decode orientation, where the kernel is HBM-bound.
+  const int early = p.w_static ? (swapped ? 1 : 2) : 0;
+  const long long pf = swapped ? g_pf_bytes : 0;
   if (p.dtype_in == MT_DTYPE_BF16)
-    MT_TRY(dispatch_tc<1>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s));
+    MT_TRY(dispatch_tc<1>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s));
   else
-    MT_TRY(dispatch_tc<2>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, s));
+    MT_TRY(dispatch_tc<2>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s));
   if (ep.partial && !p.out_splits) {
     const long long total = static_cast<long long>(p.M) * p.N;
     int blocks = static_cast<int>(cdivll(total, 256));
     if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ep, splits);
+    MT_CUDA(launch(splitk_reduce_kernel, dim3(blocks), dim3(256), 0, s, ep, splits));
     count_launch();
-    MT_LAUNCH_CHECK();
   }
   return MT_OK;
 }

@@ -4,6 +4,7 @@
 #include "lm_ops.cuh"
 #include "sampling.cuh"
 
+#include <stdlib.h>
 #include <vector>
 
 namespace mt {
@@ -88,6 +89,8 @@ static int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const
   LinearPlan p;
   p.M = M; p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = N;
   p.round_bf16 = 0; p.w_tmap = tm;
+  p.w_static = true;                       // model weights never change while the engine is alive
+  p.w_tiled = h->cfg.weights_tiled != 0;
   p.workspace = h->splitk; p.workspace_bytes = kSplitKBytes;
   if (splits) {
     if (M <= 256 && static_cast<long long>(M) * N * 4 <= kSplitKBytes) p.out_splits = splits;
@@ -109,6 +112,11 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
   const float eps = c.rms_norm_eps;
   const long long MH = static_cast<long long>(M) * H;
 
+  // MT_DEBUG_SKIP (timing experiments only; results are garbage): 1 = no GEMMs, 2 = no norm/rope/silu
+  // kernels, 4 = no heads, 8 = no attention.  Unset/0 in every product and test run.
+  static const int dbg = [] { const char* e = getenv("MT_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+#define MT_GEMM_(x) do { if (!(dbg & 1)) MT_TRY(x); else sp = 1; } while (0)
+#define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
                    h->x, M, H, c.n_vq, c.audio_head_size, c.vocab_size, s));
   MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s));
@@ -116,23 +124,27 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
     bf16* kc = h->k_cache + l * layer_stride;
     bf16* vc = h->v_cache + l * layer_stride;
     int sp = 0;
-    MT_TRY(lm_linear(h, h->xn, M, H, h->w_qkv[l], &h->tm_qkv[l], nqkv, h->qkv, &sp, s));
-    MT_TRY(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
+    MT_GEMM_(lm_linear(h, h->xn, M, H, h->w_qkv[l], &h->tm_qkv[l], nqkv, h->qkv, &sp, s));
+    MT_SMALL_(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
                     reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
                     reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), h->q, kc,
                     vc, B, T, c.num_heads, c.num_kv_heads, D, past_len, past_len_dev, c.max_seq, eps, s));
-    MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
-                     past_len_dev, max_keys, c.max_seq, s));
-    MT_TRY(lm_linear(h, h->attn, M, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
-    MT_TRY(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
+    if (!(dbg & 8))
+      MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
+                       past_len_dev, max_keys, c.max_seq, s));
+    MT_GEMM_(lm_linear(h, h->attn, M, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
+    MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
                        reinterpret_cast<const bf16*>(h->ln_post[l]), h->xn, M, H, eps, s));
-    MT_TRY(lm_linear(h, h->xn, M, H, h->w_gu[l], &h->tm_gu[l], 2 * I, h->gu, &sp, s));
-    MT_TRY(silu_mul(h->gu, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * 2 * I, h->act, M, I, s));
-    MT_TRY(lm_linear(h, h->act, M, I, h->w_down[l], &h->tm_down[l], H, h->delta, &sp, s));
+    MT_GEMM_(lm_linear(h, h->xn, M, H, h->w_gu[l], &h->tm_gu[l], 2 * I, h->gu, &sp, s));
+    MT_SMALL_(silu_mul(h->gu, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * 2 * I, h->act, M, I, s));
+    MT_GEMM_(lm_linear(h, h->act, M, I, h->w_down[l], &h->tm_down[l], H, h->delta, &sp, s));
     const void* next_gain = l + 1 < c.num_layers ? h->ln_in[l + 1] : h->w.final_norm;
-    MT_TRY(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
+    MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
                        reinterpret_cast<const bf16*>(next_gain), h->xn, M, H, eps, s));
   }
+#undef MT_GEMM_
+#undef MT_SMALL_
+  if (dbg & 4) return MT_OK;
   // heads (modeling_moss_tts.py:292-300)
   const bf16* hs = h->xn;
   int Mh = M;
@@ -187,15 +199,19 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
   const int qs = cfg->num_heads * D, kvs = cfg->num_kv_heads * D;
   h->tm_qkv.resize(L); h->tm_o.resize(L); h->tm_gu.resize(L); h->tm_down.resize(L);
   int st = MT_OK;
+  const long long NA = static_cast<long long>(cfg->n_vq) * cfg->audio_head_size;
+  auto wmap = [&](CUtensorMap* tm, const void* base, long long N, long long K) {
+    return cfg->weights_tiled ? make_tmap_tiled(tm, base, MT_DTYPE_BF16, N, K)
+                              : make_tmap_2d(tm, base, MT_DTYPE_BF16, N, K, K, 128);
+  };
   for (int l = 0; l < L && st == MT_OK; ++l) {
-    st = make_tmap_2d(&h->tm_qkv[l], h->w_qkv[l], MT_DTYPE_BF16, qs + 2 * kvs, H, H, 128);
-    if (st == MT_OK) st = make_tmap_2d(&h->tm_o[l], h->w_o[l], MT_DTYPE_BF16, H, qs, qs, 128);
-    if (st == MT_OK) st = make_tmap_2d(&h->tm_gu[l], h->w_gu[l], MT_DTYPE_BF16, 2 * I, H, H, 128);
-    if (st == MT_OK) st = make_tmap_2d(&h->tm_down[l], h->w_down[l], MT_DTYPE_BF16, H, I, I, 128);
+    st = wmap(&h->tm_qkv[l], h->w_qkv[l], qs + 2 * kvs, H);
+    if (st == MT_OK) st = wmap(&h->tm_o[l], h->w_o[l], H, qs);
+    if (st == MT_OK) st = wmap(&h->tm_gu[l], h->w_gu[l], 2 * I, H);
+    if (st == MT_OK) st = wmap(&h->tm_down[l], h->w_down[l], H, I);
   }
-  if (st == MT_OK) st = make_tmap_2d(&h->tm_text, w->text_head, MT_DTYPE_BF16, cfg->vocab_size, H, H, 128);
-  if (st == MT_OK)
-    st = make_tmap_2d(&h->tm_audio, w->audio_heads, MT_DTYPE_BF16, static_cast<long long>(cfg->n_vq) * cfg->audio_head_size, H, H, 128);
+  if (st == MT_OK) st = wmap(&h->tm_text, w->text_head, cfg->vocab_size, H);
+  if (st == MT_OK) st = wmap(&h->tm_audio, w->audio_heads, NA, H);
   if (st != MT_OK) { delete h; return st; }
   *out = h;
   return MT_OK;

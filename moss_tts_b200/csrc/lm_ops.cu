@@ -17,6 +17,8 @@ __global__ void embed_sum_kernel(const int64_t* __restrict__ ids, const bf16* __
                                  int audio_rows, int vocab) {
   const int m = blockIdx.x;
   const int64_t* row = ids + static_cast<long long>(m) * (1 + n_vq);
+  pdl_trigger();
+  pdl_wait();
   for (int c = threadIdx.x * 8; c < H; c += blockDim.x * 8) {
     long long t0 = row[0];
     t0 = t0 < 0 ? 0 : (t0 >= vocab ? vocab - 1 : t0);
@@ -43,9 +45,8 @@ int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf1
               int audio_rows, int vocab, cudaStream_t s) {
   MT_CHECK(H % 8 == 0, "hidden size must be a multiple of 8");
   int threads = H / 8 < 256 ? ((H / 8 + 31) / 32) * 32 : 256;
-  embed_sum_kernel<<<M, threads, 0, s>>>(ids, emb_text, emb_ext, out, H, n_vq, audio_rows, vocab);
+  MT_CUDA(launch(embed_sum_kernel, dim3(M), dim3(threads), 0, s, ids, emb_text, emb_ext, out, H, n_vq, audio_rows, vocab));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
@@ -63,6 +64,8 @@ add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ d
   float* scratch = srow + H;
   const long long m = blockIdx.x;
   float ss = 0.f;
+  pdl_trigger();
+  pdl_wait();
   // 4 elements per thread and iteration: every split's float4 is an independent 16-byte load
   for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
@@ -111,9 +114,9 @@ int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, 
   const size_t smem = (H + 40) * sizeof(float);
   int threads = ((H / 4 + 31) / 32) * 32;
   if (threads > 1024) threads = 1024;
-  add_rmsnorm_kernel<<<M, threads, smem, s>>>(residual, delta, partials, nsplit, split_stride, x_out, gain, normed, H, eps);
+  MT_CUDA(launch(add_rmsnorm_kernel, dim3(M), dim3(threads), smem, s, residual, delta, partials, nsplit, split_stride,
+                 x_out, gain, normed, H, eps));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
@@ -138,6 +141,8 @@ __global__ void qkv_post_kernel(const bf16* __restrict__ qkv, const float* __res
   const int heads_total = n_heads + 2 * n_kv;
   const long long m = warp / heads_total;
   const int hh = static_cast<int>(warp % heads_total);
+  pdl_trigger();
+  pdl_wait();
   if (m >= M) return;
   const int b = static_cast<int>(m / T), t = static_cast<int>(m % T);
   if (past_len_dev) past_len = *past_len_dev;
@@ -200,15 +205,16 @@ int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split
   const int threads = 128;
   const unsigned grid = static_cast<unsigned>(cdivll(warps * 32, threads));
   if (D == 128)
-    qkv_post_kernel<128><<<grid, threads, 0, s>>>(qkv, partials, nsplit, split_stride, q_gain, k_gain, rope_cos,
-        rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev, max_seq, eps);
+    MT_CUDA(launch(qkv_post_kernel<128>, dim3(grid), dim3(threads), 0, s, qkv, partials, nsplit, split_stride, q_gain,
+                   k_gain, rope_cos, rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev,
+                   max_seq, eps));
   else if (D == 64)
-    qkv_post_kernel<64><<<grid, threads, 0, s>>>(qkv, partials, nsplit, split_stride, q_gain, k_gain, rope_cos,
-        rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev, max_seq, eps);
+    MT_CUDA(launch(qkv_post_kernel<64>, dim3(grid), dim3(threads), 0, s, qkv, partials, nsplit, split_stride, q_gain,
+                   k_gain, rope_cos, rope_sin, q_out, k_cache, v_cache, M, T, n_heads, n_kv, past_len, past_len_dev,
+                   max_seq, eps));
   else
     return fail(MT_ERR_UNSUPPORTED, "head_dim %d not supported (64 or 128)", D);
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
@@ -232,6 +238,8 @@ attention_kernel(const bf16* __restrict__ q, const bf16* __restrict__ k_cache, c
   constexpr int NW = kAttThreads / 32;
   constexpr int E = D / 32;               // output dims per lane in phase 2
   const int t = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  pdl_trigger();
+  pdl_wait();
   if (past_len_dev) past_len = *past_len_dev;
   const int nkeys = past_len + t + 1;
   const int npad = (nkeys + 3) & ~3;
@@ -354,10 +362,9 @@ static int launch_attention(const bf16* q, const bf16* k_cache, const bf16* v_ca
     smem_set = 200 * 1024;
   }
   dim3 grid(T, n_kv, B);
-  kern<<<grid, kAttThreads, smem, s>>>(q, k_cache, v_cache, mask, mask_ld, out, T, n_heads, n_kv, past_len, past_len_dev,
-                               max_seq, 1.0f / sqrtf(static_cast<float>(D)));
+  MT_CUDA(launch(kern, grid, dim3(kAttThreads), smem, s, q, k_cache, v_cache, mask, mask_ld, out, T, n_heads, n_kv,
+                 past_len, past_len_dev, max_seq, 1.0f / sqrtf(static_cast<float>(D))));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
@@ -382,6 +389,8 @@ __global__ void silu_mul_kernel(const bf16* __restrict__ gu, const float* __rest
                                 long long split_stride, bf16* __restrict__ act, long long M, int I) {
   const int I4 = I / 4;
   const long long total = M * I4;
+  pdl_trigger();
+  pdl_wait();
   for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long m = idx / I4;
@@ -419,34 +428,37 @@ int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_
   const long long total = static_cast<long long>(M) * (I / 4);
   int blocks = static_cast<int>(cdivll(total, 256));
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  silu_mul_kernel<<<blocks, 256, 0, s>>>(gu, partials, nsplit, split_stride, act, M, I);
+  MT_CUDA(launch(silu_mul_kernel, dim3(blocks), dim3(256), 0, s, gu, partials, nsplit, split_stride, act,
+                 static_cast<long long>(M), I));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
 // audio_logits[..., last] = -inf  (modeling_moss_tts.py:298-299)
 __global__ void fill_audio_pad_kernel(bf16* logits, long long rows, int head_size) {
   const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  pdl_trigger();
+  pdl_wait();
   if (i < rows) logits[i * head_size + head_size - 1] = f2bf(-INFINITY);
 }
 int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s) {
-  fill_audio_pad_kernel<<<static_cast<unsigned>(cdivll(rows, 256)), 256, 0, s>>>(logits, rows, head_size);
+  MT_CUDA(launch(fill_audio_pad_kernel, dim3(static_cast<unsigned>(cdivll(rows, 256))), dim3(256), 0, s, logits, rows,
+                 head_size));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 
 // gather the last token of every batch row: dst[b,:] = src[b*T + T-1, :]
 __global__ void gather_last_kernel(const bf16* __restrict__ src, bf16* __restrict__ dst, int T, int H) {
   const int b = blockIdx.x;
+  pdl_trigger();
+  pdl_wait();
   for (int c = threadIdx.x; c < H; c += blockDim.x)
     dst[static_cast<long long>(b) * H + c] = src[(static_cast<long long>(b) * T + T - 1) * H + c];
 }
 int gather_last(const bf16* src, bf16* dst, int B, int T, int H, cudaStream_t s) {
-  gather_last_kernel<<<B, 256, 0, s>>>(src, dst, T, H);
+  MT_CUDA(launch(gather_last_kernel, dim3(B), dim3(256), 0, s, src, dst, T, H));
   count_launch();
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 

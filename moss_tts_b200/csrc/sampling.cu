@@ -235,6 +235,8 @@ __global__ void __launch_bounds__(kSampThreads)
 gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
                   const bf16* __restrict__ audio_logits, int audio_head, SampleCfg sc, TokenIds tk) {
   __shared__ SampSmem sm;
+  pdl_trigger();
+  pdl_wait();
   if (*st.done) return;
   const int ch = blockIdx.x, b = blockIdx.y;
   const int n_vq = st.C - 1;
@@ -294,6 +296,8 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
 
 // state update + history append (:472-473,505-516); a single block
 __global__ void gen_commit_kernel(GenState st, TokenIds tk) {
+  pdl_trigger();
+  pdl_wait();
   if (*st.done) return;
   const int n_vq = st.C - 1;
   const int len = *st.len;
@@ -415,10 +419,9 @@ int gen_init(const GenState& st, const int64_t* input_ids, const uint8_t* attn_m
 int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, const bf16* audio_logits, int audio_head,
                     const SampleCfg& sc, const TokenIds& tk, cudaStream_t s) {
   dim3 grid(st.C, st.B);
-  gen_sample_kernel<<<grid, kSampThreads, 0, s>>>(st, text_logits, vocab, audio_logits, audio_head, sc, tk);
-  gen_commit_kernel<<<1, 256, 0, s>>>(st, tk);
+  MT_CUDA(launch(gen_sample_kernel, grid, dim3(kSampThreads), 0, s, st, text_logits, vocab, audio_logits, audio_head, sc, tk));
+  MT_CUDA(launch(gen_commit_kernel, dim3(1), dim3(256), 0, s, st, tk));
   count_launch(2);
-  MT_LAUNCH_CHECK();
   return MT_OK;
 }
 

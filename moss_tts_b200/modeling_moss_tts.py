@@ -34,7 +34,26 @@ def _rope_tables(cfg: LMConfig, max_seq: int):
     return ang.cos().to(torch.bfloat16), ang.sin().to(torch.bfloat16)
 
 
+def tile_major(w: torch.Tensor) -> torch.Tensor:
+    """[N, K] row-major Linear weight -> the tile-major HBM layout the GEMM kernels stream
+    ([ceil(N/128)][K/ke][128][ke], ke = 128 bytes of K; include/mosstts.h MT_GEMM_W_TILED): every TMA box
+    becomes one contiguous 16 KB read.  Rows past N are zero padding.  Returned flat."""
+    N, K = w.shape
+    ke = 128 // w.element_size()
+    if K % ke:
+        raise ValueError(f"tile-major weights need K % {ke} == 0, got {K}")
+    Np = (N + 127) // 128 * 128
+    if Np != N:
+        w = torch.cat([w, w.new_zeros(Np - N, K)], dim=0)
+    return w.view(Np // 128, 128, K // ke, ke).permute(0, 2, 1, 3).contiguous().view(-1)
+
+
+_TILED_KEYS = ("qkv", "o", "gu", "down", "text_head", "audio_heads")
+
+
 class MossTTSDelayModel:
+    weights_tiled = True    # HBM layout of the Linear weights (False = plain nn.Linear row-major)
+
     def __init__(self, config: LMConfig, state_dict: Dict[str, torch.Tensor], device="cuda:0"):
         if not torch.cuda.is_available():
             raise L.MossTTSNativeError("MossTTSDelayModel needs a CUDA (sm_100) device; there is no CPU path")
@@ -75,6 +94,20 @@ class MossTTSDelayModel:
         w["text_head"] = g("lm_heads.0.weight")
         w["audio_heads"] = torch.cat([g(f"lm_heads.{i + 1}.weight") for i in range(c.n_vq)], dim=0).contiguous()
         self._w = w
+        self._retile()
+
+    def _retile(self):
+        """Record logical shapes and convert every Linear weight to the tile-major layout."""
+        w = self._w
+        self._shapes = {k: (tuple(w[k][0].shape) if isinstance(w[k], list) else tuple(w[k].shape)) for k in _TILED_KEYS}
+        if not self.weights_tiled:
+            return
+        for k in _TILED_KEYS:
+            if isinstance(w[k], list):
+                for i in range(len(w[k])):
+                    w[k][i] = tile_major(w[k][i])
+            else:
+                w[k] = tile_major(w[k])
 
     @classmethod
     def random_init(cls, config: LMConfig, device="cuda:0", seed: int = 0, never_stop: bool = True, std: float = 0.02):
@@ -107,6 +140,7 @@ class MossTTSDelayModel:
         if never_stop:   # exact tie -> argmax keeps choosing the gen slot
             w["text_head"][c.audio_assistant_delay_slot_token_id] = w["text_head"][c.audio_assistant_gen_slot_token_id]
         self._w = w
+        self._retile()
         self._engine, self._cap, self._bufs = None, (0, 0, 0), {}
         self.last_step_ms, self.last_n_steps = None, 0
         return self
@@ -129,7 +163,7 @@ class MossTTSDelayModel:
                          c.vocab_size, c.n_vq, c.audio_head_size, c.rms_norm_eps, c.pad_token_id, c.im_start_token_id,
                          c.im_end_token_id, c.audio_start_token_id, c.audio_end_token_id,
                          c.audio_assistant_gen_slot_token_id, c.audio_assistant_delay_slot_token_id, c.audio_pad_code,
-                         mb, ms, mt_)
+                         mb, ms, mt_, int(self.weights_tiled))
         kvb, wsb = C.c_longlong(0), C.c_longlong(0)
         L.check(L.lib().mt_lm_query_sizes(C.byref(cc), C.byref(kvb), C.byref(wsb)), "mt_lm_query_sizes")
         self._kv = torch.empty(kvb.value, dtype=torch.uint8, device=self.device)
