@@ -38,6 +38,41 @@ struct LinearPlan {
   bool w_tiled = false;
 };
 
+// ---------------------------------------------------------------------------------------------
+// epilogue description shared by the tcgen05 kernel, the SIMT kernel and the split-K reducer
+// ---------------------------------------------------------------------------------------------
+struct Epi {
+  void* out; long long ldo; int out_f32;
+  const float* bias; int act;
+  const void* residual; long long ldr;
+  const float* scale; int round_bf16;
+  int M, N;                       // logical output extent
+  float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
+};
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
+
+__device__ __forceinline__ float epi_apply(const Epi& e, int m, int n, float v) {
+  if (e.bias) v += e.bias[n];
+  if (e.act == 1) v = gelu_erf(v);
+  if (e.round_bf16) v = rbf(v);
+  if (e.residual) {
+    float r = e.out_f32 ? reinterpret_cast<const float*>(e.residual)[m * e.ldr + n]
+                        : bf2f(reinterpret_cast<const bf16*>(e.residual)[m * e.ldr + n]);
+    v = r + (e.scale ? e.scale[n] * v : v);
+  } else if (e.scale) {
+    v = e.scale[n] * v;
+  }
+  return v;
+}
+__device__ __forceinline__ void epi_store(const Epi& e, long long m, long long n, float v) {
+  if (e.out_f32) reinterpret_cast<float*>(e.out)[m * e.ldo + n] = v;
+  else reinterpret_cast<bf16*>(e.out)[m * e.ldo + n] = f2bf(v);
+}
+
+// Persistent 128x256-tile kernel for token-major problems (M > 256): prefill and the codec (gemm_big.cu).
+int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s);
+
 // Launches the GEMM.  With out_splits == nullptr the result is complete in `out` on return of the
 // stream work (split-K, when chosen, is reduced by a second kernel).
 int linear(const LinearPlan& p, cudaStream_t s);

@@ -1,0 +1,264 @@
+// Persistent tcgen05/TMA GEMM for token-major problems (M > 256): LM prefill and every codec Linear.
+//   y[M,N] = epilogue(x[M,K] . w[N,K]^T),  bf16 (kind::f16) or fp32 storage with TF32 math (kind::tf32).
+//
+// One CTA per SM walks output tiles of 128 (tokens) x 256 (features) in an M-fastest order, so the
+// CTAs running at the same time share a few weight-tile columns in L2.  Per CTA:
+//   warp 0        TMA producer: 4-stage ring of {A 128x128B, B 256x128B} k-blocks (48 KB / stage)
+//   warp 1        TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128x256, 4 K-slices / k-block)
+//   warps 2..9    epilogue: TMEM -> registers -> bias/GELU/LayerScale/residual -> global
+// The accumulator is double-buffered in TMEM (2 x 256 columns = all 512), so the epilogue of tile i
+// overlaps the main loop of tile i+1 -- the codec's short-K GEMMs (K = 768/1280) spend as long in the
+// epilogue as in the MMAs.  Warp w may only touch TMEM lanes 32*(w%4)..+31, so the 8 epilogue warps
+// split a tile as (lane quarter = w%4) x (column half = (w-2)/4).
+#include "gemm.cuh"
+#include "ptx.cuh"
+
+namespace mt {
+
+namespace {
+
+constexpr int kBM = 128, kBN = 256, kKBytes = 128, kStages = 4;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 64 + 32 * kEpiWarps;
+constexpr int kABytes = kBM * kKBytes, kBBytes = kBN * kKBytes, kStageBytes = kABytes + kBBytes;
+constexpr int kBarOffset = kStages * kStageBytes;
+constexpr int kSmemTotal = kBarOffset + (2 * kStages + 4) * 8 + 16 + 1024;
+
+template <int KIND /*1 bf16, 2 tf32*/>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int M, int N,
+                int k_blocks, int m_tiles, int n_tiles, int w_early, int w_tiled) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kBarOffset);
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;     // [2]
+  uint64_t* tmem_empty = tmem_full + 2;      // [2]
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  constexpr int kKElems = KIND == 1 ? 64 : 32;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = m_tiles * n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int i = 0; i < kStages; ++i) {
+      ptx::mbar_init(&full[i], 1);
+      ptx::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tmem_full[i], 1);
+      ptx::mbar_init(&tmem_empty[i], kEpiWarps);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_holder, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  if (threadIdx.x == 0) pdl_trigger();
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      auto load_a = [&](int st, int mt, int kb) {
+        ptx::tma_load_2d(smem + st * kStageBytes, &tmA, &full[st], kb * kKElems, mt * kBM, ptx::kEvictNormal);
+      };
+      auto load_b = [&](int st, int nt, int kb) {
+        uint8_t* sb = smem + st * kStageBytes + kABytes;
+        if (w_tiled) {
+#pragma unroll
+          for (int r = 0; r < kBN / 128; ++r)
+            ptx::tma_load_2d(sb + r * 128 * kKBytes, &tmB, &full[st], 0, ((nt * (kBN / 128) + r) * k_blocks + kb) * 128,
+                             ptx::kEvictLast);
+        } else {
+          ptx::tma_load_2d(sb, &tmB, &full[st], kb * kKElems, nt * kBN, ptx::kEvictLast);
+        }
+      };
+      int it = 0;
+      int pre = 0;
+      if (w_early && static_cast<int>(blockIdx.x) < total_tiles) {
+        // constant weights: first ring fill before the previous kernel is known to have finished
+        const int nt0 = blockIdx.x / m_tiles;
+        pre = k_blocks < kStages ? k_blocks : kStages;
+        for (int i = 0; i < pre; ++i) {
+          ptx::mbar_expect_tx(&full[i], kStageBytes);
+          load_b(i, nt0, i);
+        }
+      }
+      pdl_wait();
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int mt = t % m_tiles, nt = t / m_tiles;
+        for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+          const int st = it % kStages;
+          if (it < pre) { load_a(st, mt, kb); continue; }
+          ptx::mbar_wait(&empty[st], ((it / kStages) & 1) ^ 1);
+          ptx::mbar_expect_tx(&full[st], kStageBytes);
+          load_a(st, mt, kb);
+          load_b(st, nt, kb);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc(KIND, kBM, kBN);
+      int it = 0, i = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+        const int buf = i & 1;
+        ptx::mbar_wait(&tmem_empty[buf], ((i >> 1) & 1) ^ 1);     // epilogue drained this accumulator
+        ptx::tc_fence_after();
+        const uint32_t tacc = tmem_base + buf * kBN;
+        for (int kb = 0; kb < k_blocks; ++kb, ++it) {
+          const int st = it % kStages;
+          ptx::mbar_wait(&full[st], (it / kStages) & 1);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + st * kStageBytes);
+          const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
+          const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + kABytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (KIND == 1) ptx::mma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            else ptx::mma_tf32(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+          }
+          ptx::mma_commit(&empty[st]);
+        }
+        ptx::mma_commit(&tmem_full[buf]);
+      }
+    }
+  } else {
+    // ===== epilogue =====
+    const int q = warp & 3;                    // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;          // column half
+    pdl_wait();                                // residual reads / output writes follow the previous kernel
+    int i = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+      const int mt = t % m_tiles, nt = t / m_tiles;
+      const int buf = i & 1;
+      ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
+      ptx::tc_fence_after();
+      const int m = mt * kBM + q * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBN + half * (kBN / 2);
+#pragma unroll 1
+      for (int c0 = 0; c0 < kBN / 2; c0 += 32) {
+        uint32_t r[32];
+        ptx::tmem_ld32(taddr + c0, r);
+        ptx::tmem_ld_wait();
+        const int n0 = nt * kBN + half * (kBN / 2) + c0;
+        if (m < M && n0 < N) {
+          const bool full_chunk = n0 + 32 <= N;
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (ep.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] += ep.bias[n0 + j];
+          }
+          if (ep.act == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          }
+          if (ep.round_bf16) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = rbf(v[j]);
+          }
+          if (ep.scale) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] *= ep.scale[n0 + j];
+          }
+          if (ep.residual) {
+            if (ep.out_f32) {
+              const float* rr = reinterpret_cast<const float*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
+              if (full_chunk && (ep.ldr & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  const float4 x = *reinterpret_cast<const float4*>(rr + j);
+                  v[j] = x.x + v[j]; v[j + 1] = x.y + v[j + 1]; v[j + 2] = x.z + v[j + 2]; v[j + 3] = x.w + v[j + 3];
+                }
+              } else {
+                for (int j = 0; j < 32; ++j) if (n0 + j < N) v[j] = rr[j] + v[j];
+              }
+            } else {
+              const bf16* rr = reinterpret_cast<const bf16*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
+              for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] = bf2f(rr[j]) + v[j];
+            }
+          }
+          if (ep.out_f32) {
+            float* dst = reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
+            if (full_chunk && (ep.ldo & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = v[j];
+            }
+          } else {
+            bf16* dst = reinterpret_cast<bf16*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
+            if (full_chunk && (ep.ldo & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
+                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(dst + j) = pk;
+              }
+            } else {
+              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = f2bf(v[j]);
+            }
+          }
+        }
+      }
+      // this warp is done reading the accumulator: hand it back to the MMA warp
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) ptx::tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace
+
+int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s) {
+  const int esz = p.dtype_in == MT_DTYPE_BF16 ? 2 : 4;
+  const int k_elems = 128 / esz;
+  const int k_blocks = cdiv(p.K, k_elems);
+  CUtensorMap tmA, tmB;
+  MT_TRY(make_tmap_2d(&tmA, p.x, p.dtype_in, p.M, p.K, p.ldx, kBM));
+  if (p.w_tiled) {
+    if (p.w_tmap) tmB = *p.w_tmap;
+    else MT_TRY(make_tmap_tiled(&tmB, p.w, p.dtype_in, p.N, p.K));
+  } else {
+    // the cached map (if any) has a 128-row box; this kernel wants 256 rows per load
+    MT_TRY(make_tmap_2d(&tmB, p.w, p.dtype_in, p.N, p.K, p.ldw, kBN));
+  }
+  const int m_tiles = cdiv(p.M, kBM), n_tiles = cdiv(p.N, kBN);
+  const int total = m_tiles * n_tiles;
+  const int grid = total < kNumSMs ? total : kNumSMs;
+  static bool attr_set[3] = {false, false, false};
+  const int kind = p.dtype_in == MT_DTYPE_BF16 ? 1 : 2;
+  if (!attr_set[kind]) {
+    if (kind == 1) MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    else MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    attr_set[kind] = true;
+  }
+  const int w_early = p.w_static ? 1 : 0, w_tiled = p.w_tiled ? 1 : 0;
+  if (kind == 1)
+    MT_CUDA(launch(gemm_big_kernel<1>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
+                   n_tiles, w_early, w_tiled));
+  else
+    MT_CUDA(launch(gemm_big_kernel<2>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
+                   n_tiles, w_early, w_tiled));
+  count_launch();
+  return MT_OK;
+}
+
+}  // namespace mt

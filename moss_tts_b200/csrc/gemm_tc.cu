@@ -75,38 +75,6 @@ int make_tmap_tiled(CUtensorMap* out, const void* base, int dtype, long long N, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// epilogue description shared by the tcgen05 kernel, the SIMT kernel and the split-K reducer
-// ---------------------------------------------------------------------------------------------
-struct Epi {
-  void* out; long long ldo; int out_f32;
-  const float* bias; int act;
-  const void* residual; long long ldr;
-  const float* scale; int round_bf16;
-  int M, N;                       // logical output extent
-  float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
-};
-
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
-
-__device__ __forceinline__ float epi_apply(const Epi& e, int m, int n, float v) {
-  if (e.bias) v += e.bias[n];
-  if (e.act == 1) v = gelu_erf(v);
-  if (e.round_bf16) v = rbf(v);
-  if (e.residual) {
-    float r = e.out_f32 ? reinterpret_cast<const float*>(e.residual)[m * e.ldr + n]
-                        : bf2f(reinterpret_cast<const bf16*>(e.residual)[m * e.ldr + n]);
-    v = r + (e.scale ? e.scale[n] * v : v);
-  } else if (e.scale) {
-    v = e.scale[n] * v;
-  }
-  return v;
-}
-__device__ __forceinline__ void epi_store(const Epi& e, long long m, long long n, float v) {
-  if (e.out_f32) reinterpret_cast<float*>(e.out)[m * e.ldo + n] = v;
-  else reinterpret_cast<bf16*>(e.out)[m * e.ldo + n] = f2bf(v);
-}
-
-// ---------------------------------------------------------------------------------------------
 // tcgen05 kernel
 // ---------------------------------------------------------------------------------------------
 constexpr int kTileA = 128;          // UMMA M
@@ -450,6 +418,8 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const int k_elems = 128 / esz;
   const int k_blocks = cdiv(p.K, k_elems);
   const bool swapped = p.M <= 256;
+  static const bool old_big = [] { const char* e = getenv("MT_OLD_BIG"); return e && e[0] == '1'; }();
+  if (!swapped && !old_big) return linear_big(p, ep, s);
   int BN, rowsA, rowsB;
   CUtensorMap tmA, tmB;
   if (p.w_tiled) MT_CHECK(p.K % k_elems == 0, "linear: tile-major weights need K %% %d == 0 (K=%d)", k_elems, p.K);

@@ -79,8 +79,8 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 }
 // Ask L2 to fetch a tile (no shared-memory destination, no completion signal).
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1) {
-  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
-               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1)
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile.L2::cache_hint [%0, {%1, %2}], %3;"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "l"(0x12F0000000000000ull /* evict first */)
                : "memory");
 }
 // L2 eviction-priority hints (same encodings CUTLASS uses for TMA::CacheHintSm90)

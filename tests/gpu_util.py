@@ -12,15 +12,15 @@ DEV = "cuda:0"
 
 
 def gemm(x, w, *, out_dtype=None, bias=None, act=0, residual=None, scale=None, round_bf16=0, impl=L.MT_GEMM_AUTO,
-         workspace_mb=64):
+         workspace_mb=64, N=None):
     M, K = x.shape
-    N = w.shape[0]
+    N = w.shape[0] if N is None else N       # N must be given for a flat tile-major weight buffer
     din = L.MT_DTYPE_BF16 if x.dtype == torch.bfloat16 else L.MT_DTYPE_F32
     out_dtype = out_dtype or x.dtype
     dout = L.MT_DTYPE_BF16 if out_dtype == torch.bfloat16 else L.MT_DTYPE_F32
     out = torch.empty(M, N, dtype=out_dtype, device=x.device)
     ws = torch.empty(workspace_mb << 20, dtype=torch.uint8, device=x.device) if workspace_mb else None
-    a = L.GemmArgs(din, dout, M, N, K, x.data_ptr(), x.stride(0), w.data_ptr(), w.stride(0), out.data_ptr(), N,
+    a = L.GemmArgs(din, dout, M, N, K, x.data_ptr(), x.stride(0), w.data_ptr(), w.stride(0) if w.dim() == 2 else K, out.data_ptr(), N,
                    None if bias is None else bias.data_ptr(), act,
                    None if residual is None else residual.data_ptr(), 0 if residual is None else residual.stride(0),
                    None if scale is None else scale.data_ptr(), round_bf16,

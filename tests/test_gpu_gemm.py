@@ -91,3 +91,33 @@ def test_gemm_rejects_bad_args():
     w = torch.zeros(8, 100, device=DEV, dtype=torch.bfloat16)
     with pytest.raises(ValueError):
         gemm(x, w)
+
+
+@pytest.mark.parametrize("M,N,K,dt", [(6000, 2304, 768, torch.float32), (6144, 6144, 1024, torch.bfloat16),
+                                      (333, 4000, 320, torch.bfloat16)])
+def test_gemm_persistent_many_tiles(M, N, K, dt):
+    """More 128x256 tiles than SMs: the persistent loop, TMEM double buffering and ring wrap-around."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = torch.randn(M, K, device=DEV, generator=g).to(dt)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(dt)
+    out = gemm(x, w, out_dtype=torch.float32)
+    ref = x.float() @ w.float().T
+    tol = 2e-3 if dt == torch.bfloat16 else 1e-2
+    assert (out - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+    again = gemm(x, w, out_dtype=torch.float32)
+    assert torch.equal(out, again)           # deterministic
+
+
+@pytest.mark.parametrize("M,N,K,dt", [(64, 1025 * 4, 256, torch.bfloat16), (17, 384, 512, torch.bfloat16),
+                                      (700, 1100, 512, torch.bfloat16), (900, 768, 256, torch.float32)])
+@pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
+def test_gemm_tile_major_weights(M, N, K, dt, impl):
+    """MT_GEMM_W_TILED: same results from the tile-major weight layout (bit-identical to row-major)."""
+    from moss_tts_b200.modeling_moss_tts import tile_major
+    g = torch.Generator(device=DEV).manual_seed(9)
+    x = torch.randn(M, K, device=DEV, generator=g).to(dt)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(dt)
+    a = gemm(x, w, out_dtype=torch.float32, impl=impl, workspace_mb=0)
+    b = gemm(x, tile_major(w), out_dtype=torch.float32, impl=impl | L.MT_GEMM_W_TILED | L.MT_GEMM_W_STATIC,
+             workspace_mb=0, N=N)
+    assert torch.equal(a, b)
