@@ -1,0 +1,180 @@
+// Codec decoder attention on the tensor cores (reference MossAudioTokenizerMultiheadAttention.forward,
+// moss_audio_tokenizer/modeling_moss_audio_tokenizer.py:627-666): causal sliding-window attention,
+// head_dim 64, fp32 storage, TF32 mma (m16n8k8) with fp32 accumulate and an online softmax.
+//
+// CTA = 4 warps = 64 consecutive queries of one (batch, head); each warp owns 16 query rows.  Key/value
+// tiles of 64 keys are staged in shared memory (row pitch 68 floats: the fragment reads of both Q.K^T and
+// P.V are bank-conflict free) already rounded to TF32.  The probabilities never leave registers: the
+// m16n8k8 accumulator layout of S (thread holds keys 2t, 2t+1 of rows g, g+8) is reused directly as the A
+// fragment of P.V by enumerating the keys of a k-step in the order {2t | 2t+1}, and V's B fragment is
+// read in the same order.
+//
+// visible(q, k) = lo(q) <= k <= q,  lo(q) = max(q-context+1, chunk bound, 0); the chunk bound reproduces
+// the ring KV cache of decode(chunk_duration) (:413-480, :1728-1750): start(q)+len(q)-context.
+#include "codec_ops.cuh"
+
+namespace mt {
+
+namespace {
+
+constexpr int kQ = 64, kK = 64, kD = 64, kPitch = 68, kWarps = 4;
+
+__device__ __forceinline__ uint32_t to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ int vis_lo(int t, int T, int context, int chunk) {
+  int lo = t - context + 1;
+  if (chunk > 0 && T > chunk) {
+    const int start = (t / chunk) * chunk;
+    const int len = min(chunk, T - start);
+    lo = max(lo, start + len - context);
+  }
+  return max(lo, 0);
+}
+
+__global__ void __launch_bounds__(kWarps * 32)
+codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out, int T, int heads, int context,
+                          int chunk, float scale) {
+  __shared__ __align__(16) uint32_t sk[kK * kPitch];
+  __shared__ __align__(16) uint32_t sv[kK * kPitch];
+  pdl_trigger();
+  pdl_wait();
+  const int q0 = blockIdx.x * kQ, h = blockIdx.y, b = blockIdx.z;
+  const int d = heads * kD;
+  const long long tok0 = static_cast<long long>(b) * T;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+
+  // ---- Q tile -> smem (coalesced) -> A fragments (scaled, TF32)
+  for (int i = threadIdx.x; i < kQ * kD / 4; i += kWarps * 32) {
+    const int r = i / (kD / 4), c = i % (kD / 4);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (q0 + r < T) v = reinterpret_cast<const float4*>(qkv + (tok0 + q0 + r) * 3 * d + h * kD)[c];
+    uint32_t* dst = sk + r * kPitch + 4 * c;
+    dst[0] = to_tf32(v.x * scale); dst[1] = to_tf32(v.y * scale); dst[2] = to_tf32(v.z * scale); dst[3] = to_tf32(v.w * scale);
+  }
+  __syncthreads();
+  uint32_t qa[kD / 8][4];
+  {
+    const uint32_t* base = sk + (warp * 16) * kPitch;
+#pragma unroll
+    for (int s = 0; s < kD / 8; ++s) {
+      qa[s][0] = base[g * kPitch + 8 * s + t4];
+      qa[s][1] = base[(g + 8) * kPitch + 8 * s + t4];
+      qa[s][2] = base[g * kPitch + 8 * s + t4 + 4];
+      qa[s][3] = base[(g + 8) * kPitch + 8 * s + t4 + 4];
+    }
+  }
+  const int row0 = q0 + warp * 16 + g, row1 = row0 + 8;         // the two query rows this thread holds
+  const int lo0 = vis_lo(min(row0, T - 1), T, context, chunk), lo1 = vis_lo(min(row1, T - 1), T, context, chunk);
+  float o[kD / 8][4];
+#pragma unroll
+  for (int n = 0; n < kD / 8; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  const int last_q = min(q0 + kQ, T) - 1;
+  const int k_begin = (vis_lo(q0, T, context, chunk) / kK) * kK;
+  const int lo_last = vis_lo(last_q, T, context, chunk);
+  for (int k0 = k_begin; k0 <= last_q; k0 += kK) {
+    __syncthreads();                                            // previous tile (or the Q staging) is consumed
+    for (int i = threadIdx.x; i < kK * kD / 4; i += kWarps * 32) {
+      const int r = i / (kD / 4), c = i % (kD / 4);
+      float4 kv = make_float4(0.f, 0.f, 0.f, 0.f), vv = kv;
+      if (k0 + r < T) {
+        const float* base = qkv + (tok0 + k0 + r) * 3 * d + h * kD;
+        kv = reinterpret_cast<const float4*>(base + d)[c];
+        vv = reinterpret_cast<const float4*>(base + 2 * d)[c];
+      }
+      *reinterpret_cast<uint4*>(sk + r * kPitch + 4 * c) = make_uint4(to_tf32(kv.x), to_tf32(kv.y), to_tf32(kv.z), to_tf32(kv.w));
+      *reinterpret_cast<uint4*>(sv + r * kPitch + 4 * c) = make_uint4(to_tf32(vv.x), to_tf32(vv.y), to_tf32(vv.z), to_tf32(vv.w));
+    }
+    __syncthreads();
+
+    // ---- S = Q.K^T for 16 rows x 64 keys
+    float sc[kK / 8][4];
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+      const uint32_t* kr = sk + (8 * n + g) * kPitch + t4;
+#pragma unroll
+      for (int s = 0; s < kD / 8; ++s) mma_tf32_16x8x8(sc[n], qa[s], kr[8 * s], kr[8 * s + 4]);
+    }
+    // ---- mask (edge tiles only), row max
+    const bool interior = k0 + kK - 1 <= q0 && k0 >= lo_last;
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      if (!interior) {
+        const int ka = k0 + 8 * n + 2 * t4, kb = ka + 1;
+        if (ka < lo0 || ka > row0) sc[n][0] = -INFINITY;
+        if (kb < lo0 || kb > row0) sc[n][1] = -INFINITY;
+        if (ka < lo1 || ka > row1) sc[n][2] = -INFINITY;
+        if (kb < lo1 || kb > row1) sc[n][3] = -INFINITY;
+      }
+      mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
+      mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float nm0 = fmaxf(m0, mx0), nm1 = fmaxf(m1, mx1);
+    // a row whose keys so far are all masked keeps m = -inf; exp(-inf - -inf) must not poison it
+    const float c0 = nm0 == -INFINITY ? 1.f : __expf(m0 - nm0), c1 = nm1 == -INFINITY ? 1.f : __expf(m1 - nm1);
+    const float b0 = nm0 == -INFINITY ? 0.f : nm0, b1 = nm1 == -INFINITY ? 0.f : nm1;
+    m0 = nm0; m1 = nm1;
+    l0 *= c0; l1 *= c1;
+#pragma unroll
+    for (int n = 0; n < kD / 8; ++n) { o[n][0] *= c0; o[n][1] *= c0; o[n][2] *= c1; o[n][3] *= c1; }
+    // ---- P = exp(S - m), row sums; P (TF32) is the A operand of P.V with keys taken in the order {2t | 2t+1}
+    float s0 = 0.f, s1 = 0.f;
+    uint32_t pa[kK / 8][4];
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      const float p0 = __expf(sc[n][0] - b0), p1 = __expf(sc[n][1] - b0);
+      const float p2 = __expf(sc[n][2] - b1), p3 = __expf(sc[n][3] - b1);
+      s0 += p0 + p1; s1 += p2 + p3;
+      pa[n][0] = to_tf32(p0); pa[n][1] = to_tf32(p2); pa[n][2] = to_tf32(p1); pa[n][3] = to_tf32(p3);
+    }
+    l0 += s0; l1 += s1;
+    // ---- O += P.V
+#pragma unroll
+    for (int n = 0; n < kD / 8; ++n) {
+      const uint32_t* vr = sv + (2 * t4) * kPitch + 8 * n + g;
+#pragma unroll
+      for (int s = 0; s < kK / 8; ++s) mma_tf32_16x8x8(o[n], pa[s], vr[(8 * s) * kPitch], vr[(8 * s + 1) * kPitch]);
+    }
+  }
+  // ---- normalise and store
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
+#pragma unroll
+  for (int n = 0; n < kD / 8; ++n) {
+    if (row0 < T)
+      *reinterpret_cast<float2*>(out + (tok0 + row0) * d + h * kD + 8 * n + 2 * t4) = make_float2(o[n][0] * i0, o[n][1] * i0);
+    if (row1 < T)
+      *reinterpret_cast<float2*>(out + (tok0 + row1) * d + h * kD + 8 * n + 2 * t4) = make_float2(o[n][2] * i1, o[n][3] * i1);
+  }
+}
+
+}  // namespace
+
+int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
+                       cudaStream_t s) {
+  if (hd != kD) return fail(MT_ERR_UNSUPPORTED, "codec attention supports head_dim 64 only (got %d)", hd);
+  dim3 grid(cdiv(T, kQ), heads, B);
+  MT_CUDA(launch(codec_attention_tc_kernel, grid, dim3(kWarps * 32), 0, s, qkv, out, T, heads, context, chunk,
+                 1.0f / sqrtf(static_cast<float>(hd))));
+  count_launch();
+  return MT_OK;
+}
+
+}  // namespace mt

@@ -5,6 +5,7 @@
 // fp32 storage / TF32 math; LayerScale + residual and GELU are GEMM epilogues.
 #include "codec_ops.cuh"
 
+#include <stdlib.h>
 #include <vector>
 
 struct mt_codec {
@@ -128,7 +129,10 @@ static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T,
       MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s));
       MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s));
       MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
-      MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel as a cross-check of the TF32 tensor-core one
+      static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
+      if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
       MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s));
       MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s));
       MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s));

@@ -14,5 +14,8 @@ int layernorm(const float* x, const float* w, const float* b, float* out, long l
 int codec_rope(float* qkv, long long M, int T, int d, int hd, float max_period, cudaStream_t s);
 int codec_attention(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                     cudaStream_t s);
+// tensor-core (TF32 mma) version of codec_attention: the product path (codec_attn.cu)
+int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
+                       cudaStream_t s);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
 }  // namespace mt
