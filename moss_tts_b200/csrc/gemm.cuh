@@ -73,6 +73,11 @@ __device__ __forceinline__ void epi_store(const Epi& e, long long m, long long n
 // Persistent 128x256-tile kernel for token-major problems (M > 256): prefill and the codec (gemm_big.cu).
 int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s);
 
+// Persistent decode-orientation kernel (M <= 256): one CTA per SM streams (weight tile, K split) units (gemm_dec.cu).
+int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s);
+// Deterministic reduction of [splits][M][N] fp32 partials + epilogue (gemm_tc.cu).
+int splitk_reduce(const Epi& ep, int splits, cudaStream_t s);
+
 // Launches the GEMM.  With out_splits == nullptr the result is complete in `out` on return of the
 // stream work (split-K, when chosen, is reduced by a second kernel).
 int linear(const LinearPlan& p, cudaStream_t s);

@@ -23,6 +23,8 @@ bool g_force_simt = false;
 long long g_launches = 0;
 // bytes of weight tiles a decode GEMM asks L2 to prefetch before it waits for the previous kernel
 // (MT_PF_MB in the environment overrides; 0 disables)
+// experiment: BN=64 decode GEMMs with a 9-stage ring and one CTA per SM instead of 4 stages x 2 CTAs
+static const bool g_deep = [] { const char* e = getenv("MT_DEEP"); return e && e[0] == '1'; }();
 long long g_pf_bytes = [] {
   const char* e = getenv("MT_PF_MB");
   return (e ? atoll(e) : 40ll) << 20;
@@ -378,7 +380,9 @@ static int dispatch_tc(int BN, const CUtensorMap& tmA, const CUtensorMap& tmB, c
   switch (BN) {
     case 16: return launch_tc<16, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
     case 32: return launch_tc<32, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
-    case 64: return launch_tc<64, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+    case 64:
+      if (g_deep) return launch_tc<64, 9, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
+      return launch_tc<64, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
     case 128: return launch_tc<128, 6, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
     case 256: return launch_tc<256, 4, KIND>(tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s);
   }
@@ -420,6 +424,8 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const bool swapped = p.M <= 256;
   static const bool old_big = [] { const char* e = getenv("MT_OLD_BIG"); return e && e[0] == '1'; }();
   if (!swapped && !old_big) return linear_big(p, ep, s);
+  static const bool old_dec = [] { const char* e = getenv("MT_OLD_DEC"); return e && e[0] == '1'; }();
+  if (swapped && !old_dec) return linear_dec(p, ep, s);
   int BN, rowsA, rowsB;
   CUtensorMap tmA, tmB;
   if (p.w_tiled) MT_CHECK(p.K % k_elems == 0, "linear: tile-major weights need K %% %d == 0 (K=%d)", k_elems, p.K);
@@ -445,7 +451,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   const long long per_split = static_cast<long long>(p.M) * p.N * 4;
   if (p.workspace && tiles < 4 * kNumSMs) {
     // pick the split count whose CTA total fills whole waves of 2 CTAs/SM best; ties -> fewer splits
-    const int slots = 2 * kNumSMs;
+    const int slots = (g_deep && BN == 64 ? 1 : 2) * kNumSMs;
     double best_eff = 0.0;
     for (int sp = 1; sp <= 16; ++sp) {
       if (sp > 1 && k_blocks / sp < 4) break;                       // keep >= 4 k-blocks per CTA
@@ -475,13 +481,16 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     MT_TRY(dispatch_tc<1>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s));
   else
     MT_TRY(dispatch_tc<2>(BN, tmA, tmB, ep, swapped, rowsA, rowsB, k_blocks, splits, hA, hB, early, pf, tiled, s));
-  if (ep.partial && !p.out_splits) {
-    const long long total = static_cast<long long>(p.M) * p.N;
-    int blocks = static_cast<int>(cdivll(total, 256));
-    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-    MT_CUDA(launch(splitk_reduce_kernel, dim3(blocks), dim3(256), 0, s, ep, splits));
-    count_launch();
-  }
+  if (ep.partial && !p.out_splits) MT_TRY(splitk_reduce(ep, splits, s));
+  return MT_OK;
+}
+
+int splitk_reduce(const Epi& ep, int splits, cudaStream_t s) {
+  const long long total = static_cast<long long>(ep.M) * ep.N;
+  int blocks = static_cast<int>(cdivll(total, 256));
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  MT_CUDA(launch(splitk_reduce_kernel, dim3(blocks), dim3(256), 0, s, ep, splits));
+  count_launch();
   return MT_OK;
 }
 

@@ -1,0 +1,300 @@
+// Single-token (decode) GQA attention fused with the q/k RMSNorm + RoPE + KV-append step.
+// One 4-warp block per (batch row, kv head) -- all B*n_kv blocks are resident at once -- keys split over the warps.
+//
+//   prep   q (G heads), k, v rows of the new token, one warp per head: split-K partial sum -> bf16,
+//          q/k RMSNorm + RoPE (same arithmetic as qkv_post_kernel, lm_ops.cu), k/v appended to the cache
+//          (reference: Qwen3Attention.forward modeling_qwen3.py:252-291, cache_utils.py:102-121)
+//   pass 1 S = Q.K^T on the tensor cores: mma.sync m16n8k16 bf16, A = the G query heads (rows >= G are
+//          zero), B fragments read straight from the K cache (one fully used 32-byte sector per key row
+//          and k-step); s = bf16(bf16(acc) * scale), masked keys -> -inf             (:196-217)
+//   soft   fp32 max / exp / sum over the visible keys (one warp per head), p = bf16(e / sum)
+//   pass 2 O = P.V, again mma.sync; V is read as 32-bit words (two adjacent dims of one key) and the two
+//          halves of four words are permuted into the B fragments of TWO n-tiles holding the even and the
+//          odd dims, so every V sector is used exactly once and no transpose through shared memory is
+//          needed.  Per-warp partial outputs are summed in warp order; out = bf16(O).
+// Rounding points equal the reference's eager path, like attention_kernel (lm_ops.cu), which stays the
+// kernel for prefill (T > 1) and for contexts whose scores do not fit in shared memory.
+#include "lm_ops.cuh"
+
+namespace mt {
+
+namespace {
+
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                               uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+constexpr int kMaxG = 8, kWarps = 4;
+
+template <int D>
+__host__ __device__ constexpr size_t attn_fixed_bytes() { return static_cast<size_t>(kMaxG) * D * 2 + static_cast<size_t>(kWarps) * kMaxG * D * 4; }
+
+template <int D>
+__global__ void __launch_bounds__(kWarps * 32, 4)
+attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ partials, int nsplit, long long split_stride,
+                   const bf16* __restrict__ q_gain, const bf16* __restrict__ k_gain, const bf16* __restrict__ rope_cos,
+                   const bf16* __restrict__ rope_sin, bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
+                   const uint8_t* __restrict__ mask, long long mask_ld, bf16* __restrict__ out, int n_heads, int n_kv,
+                   const int* __restrict__ pos_dev, int pos_host, int spad, int max_seq, float eps, float scale) {
+  extern __shared__ __align__(16) uint8_t sm_raw[];
+  constexpr int E = D / 32;
+  const int G = n_heads / n_kv;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  // q [kMaxG][D] bf16 | partial outputs [kWarps][kMaxG][D] f32 | scores [G][spad] f32 | probabilities [G][spad] bf16
+  bf16* sq = reinterpret_cast<bf16*>(sm_raw);
+  float* red = reinterpret_cast<float*>(sm_raw + kMaxG * D * 2);
+  float* sc = reinterpret_cast<float*>(sm_raw + attn_fixed_bytes<D>());
+  bf16* sp = reinterpret_cast<bf16*>(sm_raw + attn_fixed_bytes<D>() + static_cast<size_t>(G) * spad * 4);
+
+  pdl_trigger();
+  pdl_wait();
+  const int b = blockIdx.x / n_kv, kvh = blockIdx.x % n_kv;
+  const int pos = pos_dev ? *pos_dev : pos_host;
+  const int nkeys = pos + 1;
+  const int heads_total = n_heads + 2 * n_kv;
+  const long long row_w = static_cast<long long>(heads_total) * D;
+  bf16* kbase = k_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
+  bf16* vbase = v_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
+
+  // the K/V rows of this (row, kv head) come from HBM (the cache is far larger than L2 and 15 GB of weights
+  // pass through between two visits): ask L2 for all of them now, so that the dependent phases below
+  // (scores -> softmax -> P.V) find them on chip
+  for (int i = threadIdx.x; i < 2 * pos * (D / 64); i += blockDim.x) {
+    const int which = i / (pos * (D / 64)), r = i % (pos * (D / 64));
+    const bf16* p = (which ? vbase : kbase) + static_cast<long long>(r) * 64;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  }
+
+  // first score tile of this warp: its K rows are requested now and land while the prep below runs.
+  // Row `pos` (the token being appended) does not exist yet: clamp to pos-1 and patch after the barrier.
+  uint32_t kb[2][D / 16][2];
+  auto load_k = [&](int k0, int limit) {
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const int key = min(k0 + 8 * n + g, limit);
+      const uint32_t* kr = reinterpret_cast<const uint32_t*>(kbase + static_cast<long long>(key) * D) + t4;
+#pragma unroll
+      for (int s = 0; s < D / 16; ++s) { kb[n][s][0] = kr[8 * s]; kb[n][s][1] = kr[8 * s + 4]; }
+    }
+  };
+  const int kfirst = 16 * warp;
+  if (kfirst < nkeys) load_k(kfirst, max(pos - 1, 0));
+
+  // ---- prep: G query heads, then the k and v head of this group; one warp per head (lane owns lane + 32e)
+  for (int i = warp; i < G + 2; i += kWarps) {
+    const int hh = i < G ? kvh * G + i : (i == G ? n_heads + kvh : n_heads + n_kv + kvh);
+    float x[E];
+    const long long idx0 = b * row_w + static_cast<long long>(hh) * D + lane;
+    if (partials) {
+      // all loads of four splits are issued before the first add; the sum order (split 0,1,2,...) is kept
+      float a[E];
+#pragma unroll
+      for (int e = 0; e < E; ++e) a[e] = 0.f;
+      int sidx = 0;
+      for (; sidx + 4 <= nsplit; sidx += 4) {
+        float t[4][E];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < E; ++e) t[u][e] = partials[(sidx + u) * split_stride + idx0 + 32 * e];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < E; ++e) a[e] += t[u][e];
+      }
+      for (; sidx < nsplit; ++sidx) {
+        float t[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) t[e] = partials[sidx * split_stride + idx0 + 32 * e];
+#pragma unroll
+        for (int e = 0; e < E; ++e) a[e] += t[e];
+      }
+#pragma unroll
+      for (int e = 0; e < E; ++e) x[e] = rbf(a[e]);
+    } else {
+#pragma unroll
+      for (int e = 0; e < E; ++e) x[e] = bf2f(qkv[idx0 + 32 * e]);
+    }
+    if (i <= G) {
+      const bf16* gain = i < G ? q_gain : k_gain;
+      float ss = 0.f;
+#pragma unroll
+      for (int e = 0; e < E; ++e) ss += x[e] * x[e];
+      ss = warp_sum(ss);
+      const float inv = rsqrtf(ss / static_cast<float>(D) + eps);
+#pragma unroll
+      for (int e = 0; e < E; ++e) x[e] = rbf(bf2f(gain[lane + 32 * e]) * rbf(x[e] * inv));
+      float y[E];
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        const int j = lane + 32 * e;
+        const int jh = j % (D / 2);
+        const float c = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
+        const float sn = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
+        const float partner = x[(e + E / 2) % E];
+        const float rot = j < D / 2 ? -partner : partner;
+        y[e] = rbf(rbf(x[e] * c) + rbf(rot * sn));
+      }
+#pragma unroll
+      for (int e = 0; e < E; ++e) x[e] = y[e];
+    }
+    bf16* dst = i < G ? sq + i * D : (i == G ? kbase : vbase) + static_cast<long long>(pos) * D;
+#pragma unroll
+    for (int e = 0; e < E; ++e) dst[lane + 32 * e] = f2bf(x[e]);
+  }
+  for (int i = G * D + threadIdx.x; i < kMaxG * D; i += blockDim.x) sq[i] = f2bf(0.f);   // unused query rows
+  __syncthreads();       // block-scope barrier also orders the appended k/v row before the reads below
+
+  // ---- A fragments of Q: rows 0..7 = query heads (rows 8..15 are zero)
+  uint32_t qa[D / 16][2];
+#pragma unroll
+  for (int s = 0; s < D / 16; ++s) {
+    qa[s][0] = *reinterpret_cast<const uint32_t*>(sq + g * D + 16 * s + 2 * t4);
+    qa[s][1] = *reinterpret_cast<const uint32_t*>(sq + g * D + 16 * s + 2 * t4 + 8);
+  }
+  const uint8_t* mrow = mask + b * mask_ld;
+
+  // ---- pass 1: scores, 16 keys per warp and iteration
+  for (int k0 = kfirst; k0 < nkeys; k0 += 16 * kWarps) {
+    if (k0 != kfirst) {
+      load_k(k0, nkeys - 1);
+    } else {
+#pragma unroll
+      for (int n = 0; n < 2; ++n) {
+        if (k0 + 8 * n + g >= pos) {          // this lane's row is the one the prep just wrote
+          const uint32_t* kr = reinterpret_cast<const uint32_t*>(kbase + static_cast<long long>(pos) * D) + t4;
+#pragma unroll
+          for (int s = 0; s < D / 16; ++s) { kb[n][s][0] = kr[8 * s]; kb[n][s][1] = kr[8 * s + 4]; }
+        }
+      }
+    }
+    bool vis[2][2];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) {
+      const int ka = k0 + 8 * n + 2 * t4;
+      vis[n][0] = ka < nkeys && mrow[min(ka, nkeys - 1)];
+      vis[n][1] = ka + 1 < nkeys && mrow[min(ka + 1, nkeys - 1)];
+    }
+    float c[2][4];
+#pragma unroll
+    for (int n = 0; n < 2; ++n) c[n][0] = c[n][1] = c[n][2] = c[n][3] = 0.f;
+#pragma unroll
+    for (int s = 0; s < D / 16; ++s) {
+#pragma unroll
+      for (int n = 0; n < 2; ++n) mma_bf16_16816(c[n], qa[s][0], 0u, qa[s][1], 0u, kb[n][s][0], kb[n][s][1]);
+    }
+    if (g < G) {
+#pragma unroll
+      for (int n = 0; n < 2; ++n) {
+        const int ka = k0 + 8 * n + 2 * t4;
+        const float s0 = vis[n][0] ? rbf(rbf(c[n][0]) * scale) : -INFINITY;
+        const float s1 = vis[n][1] ? rbf(rbf(c[n][1]) * scale) : -INFINITY;
+        *reinterpret_cast<float2*>(sc + g * spad + ka) = make_float2(s0, s1);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- softmax over the visible keys (fp32), one warp per head; p = bf16(e / sum), keys past nkeys get 0
+  const int kpad = (nkeys + 15) & ~15;
+  for (int h = warp; h < G; h += kWarps) {
+    float* row = sc + h * spad;
+    float mx = -INFINITY;
+    for (int k = lane; k < nkeys; k += 32) mx = fmaxf(mx, row[k]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int k = lane; k < nkeys; k += 32) {
+      const float sv = row[k];
+      const float e = (sv == -INFINITY) ? 0.f : __expf(sv - mx);
+      row[k] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    bf16* prow = sp + h * spad;
+    for (int k = lane; k < kpad; k += 32) prow[k] = f2bf((k < nkeys && sum > 0.f) ? row[k] / sum : 0.f);
+  }
+  __syncthreads();
+
+  // ---- pass 2: O = P.V, 16 keys per warp and iteration.  Dim-pair tile p covers dims [16p, 16p+16): the
+  // "even" n-tile holds dims 16p+2g, the "odd" one dims 16p+2g+1 (g = fragment column), both built from
+  // the same 32-bit V words.
+  float oe[D / 16][4], oo[D / 16][4];
+#pragma unroll
+  for (int p = 0; p < D / 16; ++p) {
+    oe[p][0] = oe[p][1] = oe[p][2] = oe[p][3] = 0.f;
+    oo[p][0] = oo[p][1] = oo[p][2] = oo[p][3] = 0.f;
+  }
+  for (int k0 = 16 * warp; k0 < kpad; k0 += 16 * kWarps) {
+    const uint32_t pa0 = g < G ? *reinterpret_cast<const uint32_t*>(sp + g * spad + k0 + 2 * t4) : 0u;
+    const uint32_t pa2 = g < G ? *reinterpret_cast<const uint32_t*>(sp + g * spad + k0 + 2 * t4 + 8) : 0u;
+    const int r0 = min(k0 + 2 * t4, nkeys - 1), r1 = min(k0 + 2 * t4 + 1, nkeys - 1);
+    const int r2 = min(k0 + 2 * t4 + 8, nkeys - 1), r3 = min(k0 + 2 * t4 + 9, nkeys - 1);
+    const uint32_t* v0 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r0) * D) + g;
+    const uint32_t* v1 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r1) * D) + g;
+    const uint32_t* v2 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r2) * D) + g;
+    const uint32_t* v3 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r3) * D) + g;
+    uint32_t w[D / 16][4];
+#pragma unroll
+    for (int p = 0; p < D / 16; ++p) { w[p][0] = v0[8 * p]; w[p][1] = v1[8 * p]; w[p][2] = v2[8 * p]; w[p][3] = v3[8 * p]; }
+#pragma unroll
+    for (int p = 0; p < D / 16; ++p) {
+      mma_bf16_16816(oe[p], pa0, 0u, pa2, 0u, __byte_perm(w[p][0], w[p][1], 0x5410), __byte_perm(w[p][2], w[p][3], 0x5410));
+      mma_bf16_16816(oo[p], pa0, 0u, pa2, 0u, __byte_perm(w[p][0], w[p][1], 0x7632), __byte_perm(w[p][2], w[p][3], 0x7632));
+    }
+  }
+  // accumulator (row g, cols 2t, 2t+1): even tile -> dims 16p+4t, 16p+4t+2; odd tile -> 16p+4t+1, 16p+4t+3
+  if (g < G) {
+#pragma unroll
+    for (int p = 0; p < D / 16; ++p)
+      *reinterpret_cast<float4*>(red + (warp * kMaxG + g) * D + 16 * p + 4 * t4) =
+          make_float4(oe[p][0], oo[p][0], oe[p][1], oo[p][1]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
+    const int h = i / D, d = i % D;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) v += red[(w * kMaxG + h) * D + d];
+    out[(static_cast<long long>(b) * n_heads + kvh * G + h) * D + d] = f2bf(v);
+  }
+}
+
+}  // namespace
+
+bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys) {
+  const int G = n_heads / n_kv;
+  if ((D != 64 && D != 128) || G > kMaxG || n_heads % n_kv) return false;
+  const int spad = (max_keys + 31) & ~31;
+  const size_t fixed = D == 128 ? attn_fixed_bytes<128>() : attn_fixed_bytes<64>();
+  return fixed + static_cast<size_t>(G) * spad * 6 <= 200 * 1024;
+}
+
+int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
+                const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* k_cache, bf16* v_cache,
+                const uint8_t* mask, long long mask_ld, bf16* out, int B, int n_heads, int n_kv, int D,
+                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s) {
+  const int G = n_heads / n_kv;
+  const int spad = (max_keys + 31) & ~31;
+  const size_t fixed = D == 128 ? attn_fixed_bytes<128>() : attn_fixed_bytes<64>();
+  const size_t smem = fixed + static_cast<size_t>(G) * spad * 6;
+  MT_CHECK(smem <= 200 * 1024, "attn_decode: %d keys do not fit in shared memory", max_keys);
+  auto kern = D == 128 ? attn_decode_kernel<128> : attn_decode_kernel<64>;
+  static size_t smem_set[2] = {0, 0};
+  size_t& cur = smem_set[D == 128];
+  if (smem > 48 * 1024 && smem > cur) {
+    MT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    cur = 200 * 1024;
+  }
+  MT_CUDA(launch(kern, dim3(B * n_kv), dim3(kWarps * 32), smem, s, qkv, partials, nsplit, split_stride, q_gain, k_gain,
+                 rope_cos, rope_sin, k_cache, v_cache, mask, mask_ld, out, n_heads, n_kv, pos_dev, pos_host, spad,
+                 max_seq, eps, 1.0f / sqrtf(static_cast<float>(D))));
+  count_launch();
+  return MT_OK;
+}
+
+}  // namespace mt

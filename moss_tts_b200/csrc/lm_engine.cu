@@ -115,6 +115,8 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
   // MT_DEBUG_SKIP (timing experiments only; results are garbage): 1 = no GEMMs, 2 = no norm/rope/silu
   // kernels, 4 = no heads, 8 = no attention.  Unset/0 in every product and test run.
   static const int dbg = [] { const char* e = getenv("MT_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
+  static const bool old_attn = [] { const char* e = getenv("MT_OLD_ATTN"); return e && e[0] == '1'; }();
+  const bool fused_attn = T == 1 && !old_attn && attn_decode_fits(B, c.num_heads, c.num_kv_heads, D, max_keys);
 #define MT_GEMM_(x) do { if (!(dbg & 1)) MT_TRY(x); else sp = 1; } while (0)
 #define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
@@ -125,13 +127,23 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
     bf16* vc = h->v_cache + l * layer_stride;
     int sp = 0;
     MT_GEMM_(lm_linear(h, h->xn, M, H, h->w_qkv[l], &h->tm_qkv[l], nqkv, h->qkv, &sp, s));
-    MT_SMALL_(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
-                    reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
-                    reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), h->q, kc,
-                    vc, B, T, c.num_heads, c.num_kv_heads, D, past_len, past_len_dev, c.max_seq, eps, s));
-    if (!(dbg & 8))
-      MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
-                       past_len_dev, max_keys, c.max_seq, s));
+    if (fused_attn) {
+      // decode: q/k norm + RoPE + KV append + attention in one warp-per-(row, kv head) kernel
+      if (!(dbg & 8))
+        MT_TRY(attn_decode(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
+                           reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
+                           reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), kc, vc,
+                           mask, mask_ld, h->attn, B, c.num_heads, c.num_kv_heads, D, past_len_dev, past_len, max_keys,
+                           c.max_seq, eps, s));
+    } else {
+      MT_SMALL_(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
+                      reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
+                      reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), h->q, kc,
+                      vc, B, T, c.num_heads, c.num_kv_heads, D, past_len, past_len_dev, c.max_seq, eps, s));
+      if (!(dbg & 8))
+        MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
+                         past_len_dev, max_keys, c.max_seq, s));
+    }
     MT_GEMM_(lm_linear(h, h->attn, M, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
     MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
                        reinterpret_cast<const bf16*>(h->ln_post[l]), h->xn, M, H, eps, s));

@@ -16,6 +16,12 @@ int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split
 int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld,
               bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
               int max_keys, int max_seq, cudaStream_t s);
+// decode (T = 1): qkv_post + attention fused, one warp per (row, kv head), mma.sync tensor cores (lm_attn.cu)
+bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys);
+int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
+                const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* k_cache, bf16* v_cache,
+                const uint8_t* mask, long long mask_ld, bf16* out, int B, int n_heads, int n_kv, int D,
+                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s);
 int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
              cudaStream_t s);
 int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s);
