@@ -36,6 +36,11 @@ struct LinearPlan {
   // w is stored tile-major: [ceil(N/128)][K/k_elems][128][k_elems] (k_elems = 64 bf16 / 32 fp32), so
   // each TMA box is 16 KB of consecutive HBM addresses.  ldw is ignored; w_tmap must match.
   bool w_tiled = false;
+  // Decode orientation only: when *tile_filter_flag == 0 (device int) only output features
+  // [tile_lo, tile_hi] (rounded out to 128-row weight tiles) are computed; the rest of `out` is left
+  // untouched.  nullptr = always compute everything.
+  const int* tile_filter_flag = nullptr;
+  int tile_lo = 0, tile_hi = 0;
 };
 
 // ---------------------------------------------------------------------------------------------

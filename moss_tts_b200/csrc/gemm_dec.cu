@@ -38,7 +38,8 @@ struct DecCfg {
 template <int BN, int KIND /*1 bf16, 2 tf32*/>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int rowsA,
-                int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled, int exp_nox) {
+                int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled, int exp_nox,
+                const int* __restrict__ full_flag, int keep_lo, int keep_hi) {
   using C = DecCfg<BN>;
   constexpr int S = C::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -54,6 +55,10 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   const int units = tiles * splits;
   // unit u = split * tiles + tile; k-range of a split as in gemm_tc_kernel
   auto kb_begin = [&](int split) { return static_cast<int>((static_cast<long long>(k_blocks) * split) / splits); };
+  // Optional row-tile filter (the text head while every utterance is inside an audio span: only the
+  // gen/delay-slot logits are read by the sampler, modeling_moss_tts.py:459-460): when *full_flag == 0 only
+  // the weight tiles keep_lo..keep_hi are computed.  The flag is read after pdl_wait by every role.
+  auto skip_tile = [&](bool restricted, int tile) { return restricted && (tile < keep_lo || tile > keep_hi); };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -102,9 +107,11 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
       pdl_wait();
+      const bool restricted = full_flag && *full_flag == 0;
       int it = 0;
       for (int u = blockIdx.x; u < units; u += gridDim.x) {
         const int tile = u % tiles, split = u / tiles;
+        if (skip_tile(restricted, tile)) continue;
         for (int kb = kb_begin(split); kb < kb_begin(split + 1); ++kb, ++it) {
           const int st = it % S;
           if (it < pre) { load_x(st, kb); continue; }
@@ -119,9 +126,12 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::make_idesc(KIND, kTileA, BN);
+      bool restricted = false;
+      if (full_flag) { pdl_wait(); restricted = *full_flag == 0; }
       int it = 0, i = 0;
-      for (int u = blockIdx.x; u < units; u += gridDim.x, ++i) {
+      for (int u = blockIdx.x; u < units; u += gridDim.x) {
         const int split = u / tiles;
+        if (skip_tile(restricted, u % tiles)) continue;
         const int buf = i & 1;
         ptx::mbar_wait(&tmem_empty[buf], ((i >> 1) & 1) ^ 1);
         ptx::tc_fence_after();
@@ -142,6 +152,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           ptx::mma_commit(&empty[st]);
         }
         ptx::mma_commit(&tmem_full[buf]);
+        ++i;
       }
     }
   } else {
@@ -151,9 +162,11 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     constexpr int CW = BN / 2;                     // columns per warp
     constexpr int CH = CW >= 32 ? 32 : CW;         // columns per tcgen05.ld (BN=16 -> 8 is not a legal shape)
     pdl_wait();
+    const bool restricted = full_flag && *full_flag == 0;
     int i = 0;
-    for (int u = blockIdx.x; u < units; u += gridDim.x, ++i) {
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
       const int tile = u % tiles, split = u / tiles;
+      if (skip_tile(restricted, tile)) continue;
       const int buf = i & 1;
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
       ptx::tc_fence_after();
@@ -181,6 +194,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
+      ++i;
     }
   }
 
@@ -191,7 +205,8 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 
 template <int BN, int KIND>
 int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, int rowsA, int rowsB, int k_blocks,
-               int tiles, int splits, int w_early, int w_tiled, cudaStream_t s) {
+               int tiles, int splits, int w_early, int w_tiled, const int* full_flag, int keep_lo, int keep_hi,
+               cudaStream_t s) {
   using C = DecCfg<BN>;
   auto kern = gemm_dec_kernel<BN, KIND>;
   static bool attr_set = false;
@@ -204,7 +219,7 @@ int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, in
   // timing experiment only (garbage results): do not load the activation operand
   static const int exp_nox = [] { const char* e = getenv("MT_EXP_NOX"); return e && e[0] == '1' ? 1 : 0; }();
   MT_CUDA(launch(kern, dim3(grid), dim3(kThreads), C::kTotal, s, tmA, tmB, ep, rowsA, rowsB, k_blocks, tiles, splits,
-                 w_early, w_tiled, exp_nox));
+                 w_early, w_tiled, exp_nox, full_flag, keep_lo, keep_hi));
   count_launch();
   return MT_OK;
 }
@@ -249,12 +264,16 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   } else if (splits > 1) {
     ep.partial = p.workspace;
   }
-  const int w_early = p.w_static ? 1 : 0, w_tiled = p.w_tiled ? 1 : 0;
+  const int w_tiled = p.w_tiled ? 1 : 0;
+  // a filtered launch decides its unit list after the dependency wait: no early weight fetch
+  const int w_early = p.w_static && !p.tile_filter_flag ? 1 : 0;
+  const int keep_lo = p.tile_lo / kTileA, keep_hi = p.tile_hi / kTileA;
+  if (p.tile_filter_flag) MT_CHECK(splits == 1 && !p.out_splits, "linear_dec: the row-tile filter needs an unsplit GEMM");
   const bool bf = p.dtype_in == MT_DTYPE_BF16;
 #define MT_DEC(BNV)                                                                                               \
   case BNV:                                                                                                       \
-    if (bf) MT_TRY((launch_dec<BNV, 1>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, s)));    \
-    else MT_TRY((launch_dec<BNV, 2>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, s)));       \
+    if (bf) MT_TRY((launch_dec<BNV, 1>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));    \
+    else MT_TRY((launch_dec<BNV, 2>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));       \
     break;
   switch (BN) {
     MT_DEC(32) MT_DEC(64) MT_DEC(128) MT_DEC(256)

@@ -5,6 +5,7 @@
 #include "sampling.cuh"
 
 #include <stdlib.h>
+#include <algorithm>
 #include <vector>
 
 namespace mt {
@@ -85,13 +86,18 @@ static int check_cfg(const mt_lm_config* c) {
 // One Linear on the LM path.  Small M: split-K partials handed to the consumer kernel (returns the
 // split count through *splits, partials in h->splitk); large M: finished bf16 output in `out`.
 static int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtensorMap* tm, int N, bf16* out,
-                     int* splits, cudaStream_t s) {
+                     int* splits, cudaStream_t s, const int* tile_filter_flag = nullptr, int tile_lo = 0,
+                     int tile_hi = 0) {
   LinearPlan p;
   p.M = M; p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = N;
   p.round_bf16 = 0; p.w_tmap = tm;
   p.w_static = true;                       // model weights never change while the engine is alive
   p.w_tiled = h->cfg.weights_tiled != 0;
   p.workspace = h->splitk; p.workspace_bytes = kSplitKBytes;
+  if (tile_filter_flag && M <= 256) {
+    p.tile_filter_flag = tile_filter_flag; p.tile_lo = tile_lo; p.tile_hi = tile_hi;
+    p.workspace = nullptr; p.workspace_bytes = 0;        // the filter needs an unsplit GEMM
+  }
   if (splits) {
     if (M <= 256 && static_cast<long long>(M) * N * 4 <= kSplitKBytes) p.out_splits = splits;
     else { *splits = 0; p.workspace = nullptr; p.workspace_bytes = 0; }
@@ -102,7 +108,7 @@ static int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const
 // forward over B*T tokens; ids may live in the generation state (decode) or come from the caller.
 static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long mask_ld, int B, int T,
                            int past_len, const int* past_len_dev, int max_keys, int last_only, bf16* text_logits,
-                           bf16* audio_logits, cudaStream_t s) {
+                           bf16* audio_logits, cudaStream_t s, const int* text_full_flag = nullptr) {
   const mt_lm_config& c = h->cfg;
   const int M = B * T, H = c.hidden_size, I = c.intermediate_size, D = c.head_dim;
   const int qs = c.num_heads * D, kvs = c.num_kv_heads * D, nqkv = qs + 2 * kvs;
@@ -116,6 +122,7 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
   // kernels, 4 = no heads, 8 = no attention.  Unset/0 in every product and test run.
   static const int dbg = [] { const char* e = getenv("MT_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
   static const bool old_attn = [] { const char* e = getenv("MT_OLD_ATTN"); return e && e[0] == '1'; }();
+  static const bool text_head_filter = [] { const char* e = getenv("MT_NO_HEAD_FILTER"); return !(e && e[0] == '1'); }();
   const bool fused_attn = T == 1 && !old_attn && attn_decode_fits(B, c.num_heads, c.num_kv_heads, D, max_keys);
 #define MT_GEMM_(x) do { if (!(dbg & 1)) MT_TRY(x); else sp = 1; } while (0)
 #define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
@@ -165,7 +172,14 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
     hs = h->last_h;
   }
   if (last_only) Mh = B;
-  if (text_logits) MT_TRY(lm_linear(h, hs, Mh, H, h->w.text_head, &h->tm_text, c.vocab_size, text_logits, nullptr, s));
+  if (text_logits) {
+    // generate(): while every row is forced or inside an audio span the sampler reads only the gen/delay-slot
+    // logits, so the 1.2 GB text head shrinks to the weight tile(s) holding those two rows
+    const int lo = std::min(c.audio_assistant_gen_slot_token_id, c.audio_assistant_delay_slot_token_id);
+    const int hi = std::max(c.audio_assistant_gen_slot_token_id, c.audio_assistant_delay_slot_token_id);
+    MT_TRY(lm_linear(h, hs, Mh, H, h->w.text_head, &h->tm_text, c.vocab_size, text_logits, nullptr, s,
+                     text_head_filter ? text_full_flag : nullptr, lo, hi));
+  }
   if (audio_logits) {
     const int NA = c.n_vq * c.audio_head_size;
     MT_TRY(lm_linear(h, hs, Mh, H, h->w.audio_heads, &h->tm_audio, NA, audio_logits, nullptr, s));
@@ -298,7 +312,7 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   auto decode_step = [&](cudaStream_t cs) -> int {
     // position of the token appended by the previous commit = *len - 1; kernels read it from st.pos
     MT_TRY(lm_forward_impl(h, st.next_ids, st.mask, max_len, B, 1, 0, st.pos, max_len, 1, h->text_logits,
-                           h->audio_logits, cs));
+                           h->audio_logits, cs, st.text_full));
     return gen_sample_step(st, h->text_logits, c.vocab_size, h->audio_logits, c.audio_head_size, sc, tk, cs);
   };
 

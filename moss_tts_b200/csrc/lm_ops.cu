@@ -25,14 +25,27 @@ __global__ void embed_sum_kernel(const int64_t* __restrict__ ids, const bf16* __
     uint4 a = *reinterpret_cast<const uint4*>(emb_text + t0 * H + c);
     float acc[8] = {bits_lo(a.x), bits_hi(a.x), bits_lo(a.y), bits_hi(a.y),
                     bits_lo(a.z), bits_hi(a.z), bits_lo(a.w), bits_hi(a.w)};
-    for (int i = 0; i < n_vq; ++i) {
-      long long t = row[1 + i];
-      t = t < 0 ? 0 : (t >= audio_rows ? audio_rows - 1 : t);
-      uint4 b = *reinterpret_cast<const uint4*>(emb_ext + (static_cast<long long>(i) * audio_rows + t) * H + c);
-      const float e[8] = {bits_lo(b.x), bits_hi(b.x), bits_lo(b.y), bits_hi(b.y),
-                          bits_lo(b.z), bits_hi(b.z), bits_lo(b.w), bits_hi(b.w)};
+    // eight table rows are requested before the first add (the add order stays left to right)
+    for (int i0 = 0; i0 < n_vq; i0 += 8) {
+      uint4 bb[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = rbf(acc[j] + e[j]);
+      for (int u = 0; u < 8; ++u) {
+        if (i0 + u < n_vq) {
+          long long t = row[1 + i0 + u];
+          t = t < 0 ? 0 : (t >= audio_rows ? audio_rows - 1 : t);
+          bb[u] = *reinterpret_cast<const uint4*>(emb_ext + (static_cast<long long>(i0 + u) * audio_rows + t) * H + c);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        if (i0 + u < n_vq) {
+          const uint4 b = bb[u];
+          const float e[8] = {bits_lo(b.x), bits_hi(b.x), bits_lo(b.y), bits_hi(b.y),
+                              bits_lo(b.z), bits_hi(b.z), bits_lo(b.w), bits_hi(b.w)};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = rbf(acc[j] + e[j]);
+        }
+      }
     }
     uint4 o;
     o.x = pack_bf16(acc[0], acc[1]); o.y = pack_bf16(acc[2], acc[3]);

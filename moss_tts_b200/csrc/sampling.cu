@@ -301,7 +301,7 @@ __global__ void gen_commit_kernel(GenState st, TokenIds tk) {
   if (*st.done) return;
   const int n_vq = st.C - 1;
   const int len = *st.len;
-  int all_stopped = 1;
+  int all_stopped = 1, need_full = 0;
   for (int b = threadIdx.x; b < st.B; b += blockDim.x) {
     const int64_t* nx = st.next_ids + static_cast<long long>(b) * st.C;
     const int tok = static_cast<int>(nx[0]);
@@ -317,26 +317,29 @@ __global__ void gen_commit_kernel(GenState st, TokenIds tk) {
     if (delayed >= 0) delayed += 1;
     if (delayed > n_vq) delayed = -1;
     st.audio_len[b] = al; st.delayed[b] = delayed; st.stopping[b] = stopping; st.is_audio[b] = is_audio;
-    if (len < st.max_len) {
-      int64_t* g = st.gen_ids + (static_cast<long long>(b) * st.max_len + len) * st.C;
-      for (int c = 0; c < st.C; ++c) g[c] = nx[c];
-      st.mask[static_cast<long long>(b) * st.max_len + len] = !stopping;
-    }
-    // repetition-penalty id sets grow with every appended row (pad code included, as torch.unique sees it)
-    const long long a0 = nx[1];
-    if (a0 >= 0 && a0 < st.bitmap_words * 32) atomicOr(&st.seen0[a0 >> 5], 1u << (a0 & 31));
-    for (int c = 2; c < st.C; ++c) {
-      const long long a = nx[c];
-      if (a >= 0 && a < st.bitmap_words * 32) atomicOr(&st.seen_rest[a >> 5], 1u << (a & 31));
-    }
+    if (len < st.max_len) st.mask[static_cast<long long>(b) * st.max_len + len] = !stopping;
     all_stopped &= stopping;
+    // will the next step's text sampler read this row's whole logit row?  (forced rows read nothing,
+    // rows inside an audio span read only the gen/delay-slot logits; see gen_sample_kernel)
+    const bool forced = stopping || (delayed >= 0 && delayed <= n_vq);
+    need_full |= !forced && !is_audio;
+  }
+  // history append + repetition-penalty id sets (pad code included, as torch.unique sees it), one thread
+  // per (row, channel)
+  for (int i = threadIdx.x; i < st.B * st.C; i += blockDim.x) {
+    const int b = i / st.C, c = i % st.C;
+    const long long a = st.next_ids[i];
+    if (len < st.max_len) st.gen_ids[(static_cast<long long>(b) * st.max_len + len) * st.C + c] = a;
+    if (c >= 1 && a >= 0 && a < st.bitmap_words * 32) atomicOr(c == 1 ? &st.seen0[a >> 5] : &st.seen_rest[a >> 5], 1u << (a & 31));
   }
   all_stopped = __syncthreads_and(all_stopped);
+  need_full = __syncthreads_or(need_full);
   if (threadIdx.x == 0) {
     *st.len = len + 1;
     *st.pos = len;
     *st.step = *st.step + 1;
     if (all_stopped) *st.done = 1;
+    *st.text_full = need_full;
   }
 }
 
@@ -372,7 +375,7 @@ __global__ void gen_init_kernel(GenState st, const int64_t* __restrict__ input_i
     st.stopping[b] = 0;
     st.delayed[b] = -1;
     start_indices[b] = s_last_im + 3;
-    if (b == 0) { *st.len = S0; *st.step = 0; *st.done = 0; *st.pos = S0 - 1; }
+    if (b == 0) { *st.len = S0; *st.step = 0; *st.done = 0; *st.pos = S0 - 1; *st.text_full = 1; }
   }
 }
 
@@ -393,7 +396,8 @@ GenState gen_state_carve(void* buf, int B, int C, int max_len, int audio_head, i
   GenState st{};
   uint8_t* p = reinterpret_cast<uint8_t*>(buf);
   const int words = (audio_head + 31) / 32;
-  st.len = reinterpret_cast<int*>(p); st.step = st.len + 1; st.done = st.len + 2; st.pos = st.len + 3; p += 256;
+  st.len = reinterpret_cast<int*>(p); st.step = st.len + 1; st.done = st.len + 2; st.pos = st.len + 3;
+  st.text_full = st.len + 4; p += 256;
   st.stopping = p; p += align_up(B, 256);
   st.is_audio = p; p += align_up(B, 256);
   st.audio_len = reinterpret_cast<int*>(p); p += align_up(B * sizeof(int), 256);
@@ -420,7 +424,7 @@ int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, cons
                     const SampleCfg& sc, const TokenIds& tk, cudaStream_t s) {
   dim3 grid(st.C, st.B);
   MT_CUDA(launch(gen_sample_kernel, grid, dim3(kSampThreads), 0, s, st, text_logits, vocab, audio_logits, audio_head, sc, tk));
-  MT_CUDA(launch(gen_commit_kernel, dim3(1), dim3(256), 0, s, st, tk));
+  MT_CUDA(launch(gen_commit_kernel, dim3(1), dim3(1024), 0, s, st, tk));
   count_launch(2);
   return MT_OK;
 }

@@ -14,6 +14,8 @@ struct GenState {
   int* step;         // time_step
   int* done;         // all rows stopped
   int* pos;          // index of the row appended by the last commit (= KV position of the next decode input)
+  int* text_full;    // 1 if some row of the NEXT step reads its whole text-logit row (not forced, not inside audio);
+                     // 0 lets the text head compute only the gen/delay-slot logits (modeling_moss_tts.py:459-460)
   // per row
   uint8_t* stopping;
   uint8_t* is_audio;
