@@ -177,6 +177,72 @@ int mt_apply_delay_pattern(const int64_t* codes, int T, int n, long long pad_cod
 int mt_apply_de_delay_pattern(const int64_t* delayed, int Td, int n, int64_t* out, mt_stream s);
 
 /* ------------------------------------------------------------------------------------------
+ * MossTTSLocal (reference moss_tts_local/modeling_moss_tts.py): global Qwen3 backbone + depth transformer.
+ * Replaces MossTTSDelayModel(CustomMixin)._sample :316-477 (the body of generate()) and the modules it calls:
+ * MosiTTSModel.forward :532-569, MossTTSLocalTransformer :178-292, MossTTSMLP :47-95, MossTTSRMSNorm :34-44.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  mt_lm_config lm;              /* backbone shape, vocab / n_vq / audio_head_size, token ids, capacity, weights_tiled */
+  int local_hidden_size, local_ffn_hidden_size, local_num_layers, additional_mlp_ffn_hidden_size;
+} mt_local_config;
+
+/* bf16, [out,in] (tile-major when lm.weights_tiled).  The local layers copy the backbone's head layout
+ * (num_heads / num_kv_heads / head_dim, :585-590). */
+typedef struct {
+  mt_lm_weights lm;                /* embed_tokens = embedding_list[0], emb_ext = embedding_list[1..n_vq] stacked
+                                      [n_vq, audio_head_size, H]; text_head / audio_heads unused (NULL) */
+  const void* const* l_w_qkv;      /* per local layer [q+2kv, LH] */
+  const void* const* l_w_o;        /* [LH, q] */
+  const void* const* l_w_gate_up;  /* [2*LF, LH] */
+  const void* const* l_w_down;     /* [LH, LF] */
+  const void* const* l_ln_in;      /* [LH] */
+  const void* const* l_ln_post;    /* [LH] */
+  const void* const* l_q_norm;     /* [head_dim] */
+  const void* const* l_k_norm;
+  const void* l_final_norm;        /* [LH] */
+  const void* in_gate_up;          /* speech_embedding_to_local_mlp: gate|up [2*AF, H] */
+  const void* in_down;             /* [LH, AF] */
+  const void* const* out_gate_up;  /* per channel local_to_speech_embedding_mlps[c]: [2*AF, LH] */
+  const void* const* out_down;     /* per channel [H, AF] */
+  const void* const* head_norm;    /* per channel layer_norm_before_lm_heads[c]: [H] */
+  const void* const* heads;        /* per channel lm_heads[c]: [vocab | audio_head_size, H] */
+} mt_local_weights;
+
+typedef struct mt_local mt_local;
+int mt_local_query_sizes(const mt_local_config* cfg, long long* kv_bytes, long long* workspace_bytes);
+int mt_local_create(const mt_local_config* cfg, const mt_local_weights* w, void* kv_cache, void* workspace, mt_local** out);
+int mt_local_destroy(mt_local* h);
+
+/* One teacher-forced frame (the body of the :379-450 loop with the sampled tokens replaced by frame_ids):
+ * backbone over input_ids [B,S0,1+n_vq], then the depth loop feeding frame_ids [B,1+n_vq] (device int64).
+ * logits_out: bf16 [min(1+n_vq, 1+n_vq_for_inference)][B][ldv]; channel c fills its first vocab / audio_head_size
+ * columns, audio channels carry -inf at the pad code (:411-412).  Parity tests compare these with the oracle. */
+int mt_local_forward(mt_local* h, const int64_t* input_ids, int B, int S0, int n_vq_for_inference,
+                     const int64_t* frame_ids, void* logits_out, long long ldv, mt_stream s);
+
+/* generation_config of the reference (:359-370): per-channel host arrays of 1+n_vq entries.  Channels with
+ * do_sample[c] == 0 take the argmax of the raw logits; the others apply RepetitionPenalty (c > 0 only, over the
+ * row's own history of that channel) -> Temperature -> TopK -> TopP and draw by inverse CDF from (seed, step, row, c). */
+typedef struct {
+  int max_new_tokens;
+  int n_vq_for_inference;          /* channels 1..n_vq_for_inference are generated, the rest stay 0 (:397,:427) */
+  int eos_token_id;                /* -1: no EOS handling */
+  const int* do_sample;
+  const float* temperature;        /* 1.0 = none */
+  const float* top_p;              /* 1.0 = none */
+  const int* top_k;                /* 1..1024 */
+  const float* repetition_penalty; /* 1.0 = none */
+  unsigned int seed;
+  int use_cuda_graph;
+  int check_stop_every;
+} mt_local_gen_params;
+
+/* input_ids [B,S0,1+n_vq] int64 (device; un-padded prompts: the attention mask is all ones).
+ * gen_ids [B, S0+max_new_tokens, 1+n_vq] int64 (device) receives prompt + generated frames; *n_steps = frames made. */
+int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, int S0, const mt_local_gen_params* p,
+                      int64_t* gen_ids, int* n_steps, float* step_ms, mt_stream s);
+
+/* ------------------------------------------------------------------------------------------
  * MOSS-Audio-Tokenizer decode side
  * ------------------------------------------------------------------------------------------ */
 #define MT_CODEC_MAX_STAGES 8

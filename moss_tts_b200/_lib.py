@@ -24,6 +24,7 @@ EXPORTS = [
     "mt_sample_tokens", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
     "mt_codec_create", "mt_codec_destroy", "mt_codec_workspace_bytes", "mt_rvq_fold_tables",
     "mt_rvq_dequant", "mt_codec_decode",
+    "mt_local_query_sizes", "mt_local_create", "mt_local_destroy", "mt_local_forward", "mt_local_generate",
 ]
 
 
@@ -63,6 +64,26 @@ class GenParamsC(C.Structure):
     _fields_ = [("max_new_tokens", C.c_int), ("text_temperature", C.c_float), ("text_top_p", C.c_float),
                 ("text_top_k", C.c_int), ("audio_temperature", C.c_float), ("audio_top_p", C.c_float),
                 ("audio_top_k", C.c_int), ("audio_repetition_penalty", C.c_float), ("seed", C.c_uint),
+                ("use_cuda_graph", C.c_int), ("check_stop_every", C.c_int)]
+
+
+class LocalConfigC(C.Structure):
+    _fields_ = [("lm", LMConfigC)] + [(n, C.c_int) for n in ("local_hidden_size", "local_ffn_hidden_size",
+                                                            "local_num_layers", "additional_mlp_ffn_hidden_size")]
+
+
+class LocalWeightsC(C.Structure):
+    _fields_ = [("lm", LMWeightsC)] + \
+               [(n, C.POINTER(C.c_void_p)) for n in ("l_w_qkv", "l_w_o", "l_w_gate_up", "l_w_down", "l_ln_in", "l_ln_post",
+                                                     "l_q_norm", "l_k_norm")] + \
+               [("l_final_norm", C.c_void_p), ("in_gate_up", C.c_void_p), ("in_down", C.c_void_p)] + \
+               [(n, C.POINTER(C.c_void_p)) for n in ("out_gate_up", "out_down", "head_norm", "heads")]
+
+
+class LocalGenParamsC(C.Structure):
+    _fields_ = [("max_new_tokens", C.c_int), ("n_vq_for_inference", C.c_int), ("eos_token_id", C.c_int),
+                ("do_sample", C.POINTER(C.c_int)), ("temperature", C.POINTER(C.c_float)), ("top_p", C.POINTER(C.c_float)),
+                ("top_k", C.POINTER(C.c_int)), ("repetition_penalty", C.POINTER(C.c_float)), ("seed", C.c_uint),
                 ("use_cuda_graph", C.c_int), ("check_stop_every", C.c_int)]
 
 

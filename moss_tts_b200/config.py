@@ -69,6 +69,36 @@ class LMConfig:
 
 
 @dataclass
+class LocalConfig(LMConfig):
+    """MossTTSLocal (reference moss_tts_local/configuration_moss_tts.py:62-106): a Qwen3 "global" backbone
+    (the LMConfig fields) plus a small "local"/depth transformer that emits the 1+n_vq tokens of one frame
+    sequentially.  The local transformer copies the backbone's head layout (num_heads / num_kv_heads /
+    head_dim, modeling_moss_tts.py:585-590) with its own hidden / ffn sizes and no rotary embedding."""
+    local_hidden_size: int = 1536
+    local_ffn_hidden_size: int = 8960
+    local_num_layers: int = 4
+    additional_mlp_ffn_hidden_size: int = 2048
+
+    @staticmethod
+    def local_1p7b(n_vq: int = 32) -> "LocalConfig":
+        """Assumed released MossTTSLocal shape = public Qwen3-1.7B backbone (SURVEY.md §8 d)."""
+        return LocalConfig(hidden_size=2048, intermediate_size=6144, num_layers=28, num_heads=16, num_kv_heads=8,
+                           head_dim=128, n_vq=n_vq)
+
+    @staticmethod
+    def tiny(n_vq: int = 4) -> "LocalConfig":
+        return LocalConfig(hidden_size=128, intermediate_size=256, num_layers=2, num_heads=4, num_kv_heads=2,
+                           head_dim=64, n_vq=n_vq, local_hidden_size=192, local_ffn_hidden_size=320,
+                           local_num_layers=2, additional_mlp_ffn_hidden_size=256)
+
+    @staticmethod
+    def mid(n_vq: int = 8) -> "LocalConfig":
+        return LocalConfig(hidden_size=512, intermediate_size=1024, num_layers=2, num_heads=8, num_kv_heads=2,
+                           head_dim=128, n_vq=n_vq, local_hidden_size=384, local_ffn_hidden_size=768,
+                           local_num_layers=2, additional_mlp_ffn_hidden_size=512)
+
+
+@dataclass
 class CodecStage:
     """One ProjectedTransformer stage followed by a patch upsample (reference
     modeling_moss_audio_tokenizer.py:888-953)."""

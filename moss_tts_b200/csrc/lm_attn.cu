@@ -132,6 +132,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
       float y[E];
 #pragma unroll
       for (int e = 0; e < E; ++e) {
+        if (!rope_cos) { y[e] = x[e]; continue; }     // MossTTSLocal's depth transformer has no rotary embedding
         const int j = lane + 32 * e;
         const int jh = j % (D / 2);
         const float c = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);

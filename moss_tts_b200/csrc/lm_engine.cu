@@ -1,8 +1,7 @@
 // Host-side engine of the MossTTSDelay hot path: owns tensor maps, carves the caller's workspace,
 // sequences one forward (prefill or single-token decode) and the generate() loop with a CUDA graph.
 // Reference: moss_tts_delay/modeling_moss_tts.py forward :225-300, generate :392-525.
-#include "lm_ops.cuh"
-#include "sampling.cuh"
+#include "lm_engine.cuh"
 
 #include <stdlib.h>
 #include <algorithm>
@@ -21,27 +20,8 @@ struct Carver {
   }
 };
 
-constexpr long long kSplitKBytes = 96ll << 20;
 
 }  // namespace mt
-
-struct mt_lm {
-  mt_lm_config cfg;
-  mt_lm_weights w;
-  std::vector<const void*> w_qkv, w_o, w_gu, w_down, ln_in, ln_post, q_norm, k_norm;
-  std::vector<CUtensorMap> tm_qkv, tm_o, tm_gu, tm_down;
-  CUtensorMap tm_text, tm_audio;
-  // workspace views
-  mt::bf16 *x, *xn, *qkv, *q, *attn, *gu, *act, *delta, *last_h, *text_logits, *audio_logits;
-  float* splitk;
-  void* gen_state_buf;
-  mt::bf16 *k_cache, *v_cache;   // [L][B][kv][S][D] each
-  size_t ws_bytes;
-  // graph
-  cudaGraphExec_t graph_exec = nullptr;
-  cudaStream_t cap_stream = nullptr;   // capture-only stream (the caller's stream may be the legacy default stream)
-  int graph_B = 0; long long graph_key = 0;
-};
 
 namespace mt {
 
@@ -85,9 +65,8 @@ static int check_cfg(const mt_lm_config* c) {
 
 // One Linear on the LM path.  Small M: split-K partials handed to the consumer kernel (returns the
 // split count through *splits, partials in h->splitk); large M: finished bf16 output in `out`.
-static int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtensorMap* tm, int N, bf16* out,
-                     int* splits, cudaStream_t s, const int* tile_filter_flag = nullptr, int tile_lo = 0,
-                     int tile_hi = 0) {
+int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtensorMap* tm, int N, bf16* out,
+              int* splits, cudaStream_t s, const int* tile_filter_flag, int tile_lo, int tile_hi) {
   LinearPlan p;
   p.M = M; p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = N;
   p.round_bf16 = 0; p.w_tmap = tm;
@@ -106,9 +85,9 @@ static int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const
 }
 
 // forward over B*T tokens; ids may live in the generation state (decode) or come from the caller.
-static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long mask_ld, int B, int T,
-                           int past_len, const int* past_len_dev, int max_keys, int last_only, bf16* text_logits,
-                           bf16* audio_logits, cudaStream_t s, const int* text_full_flag = nullptr) {
+int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long mask_ld, int B, int T,
+                    int past_len, const int* past_len_dev, int max_keys, int last_only, bf16* text_logits,
+                    bf16* audio_logits, cudaStream_t s, const int* text_full_flag, int n_vq_embed) {
   const mt_lm_config& c = h->cfg;
   const int M = B * T, H = c.hidden_size, I = c.intermediate_size, D = c.head_dim;
   const int qs = c.num_heads * D, kvs = c.num_kv_heads * D, nqkv = qs + 2 * kvs;
@@ -127,7 +106,7 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
 #define MT_GEMM_(x) do { if (!(dbg & 1)) MT_TRY(x); else sp = 1; } while (0)
 #define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
-                   h->x, M, H, c.n_vq, c.audio_head_size, c.vocab_size, s));
+                   h->x, M, H, n_vq_embed < 0 ? c.n_vq : n_vq_embed, c.audio_head_size, c.vocab_size, s, 1 + c.n_vq));
   MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s));
   for (int l = 0; l < c.num_layers; ++l) {
     bf16* kc = h->k_cache + l * layer_stride;
@@ -172,6 +151,7 @@ static int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, lo
     hs = h->last_h;
   }
   if (last_only) Mh = B;
+  MT_CHECK((!text_logits || h->w.text_head) && (!audio_logits || h->w.audio_heads), "forward: this engine was created without heads");
   if (text_logits) {
     // generate(): while every row is forced or inside an audio span the sampler reads only the gen/delay-slot
     // logits, so the 1.2 GB text head shrinks to the weight tile(s) holding those two rows
@@ -236,8 +216,9 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
     if (st == MT_OK) st = wmap(&h->tm_gu[l], h->w_gu[l], 2 * I, H);
     if (st == MT_OK) st = wmap(&h->tm_down[l], h->w_down[l], H, I);
   }
-  if (st == MT_OK) st = wmap(&h->tm_text, w->text_head, cfg->vocab_size, H);
-  if (st == MT_OK) st = wmap(&h->tm_audio, w->audio_heads, NA, H);
+  // a backbone without heads (MossTTSLocal's global transformer) passes NULL head weights
+  if (st == MT_OK && w->text_head) st = wmap(&h->tm_text, w->text_head, cfg->vocab_size, H);
+  if (st == MT_OK && w->audio_heads) st = wmap(&h->tm_audio, w->audio_heads, NA, H);
   if (st != MT_OK) { delete h; return st; }
   *out = h;
   return MT_OK;

@@ -14,9 +14,9 @@ namespace mt {
 // ---------------------------------------------------------------------------------------------
 __global__ void embed_sum_kernel(const int64_t* __restrict__ ids, const bf16* __restrict__ emb_text,
                                  const bf16* __restrict__ emb_ext, bf16* __restrict__ out, int H, int n_vq,
-                                 int audio_rows, int vocab) {
+                                 int audio_rows, int vocab, int row_stride) {
   const int m = blockIdx.x;
-  const int64_t* row = ids + static_cast<long long>(m) * (1 + n_vq);
+  const int64_t* row = ids + static_cast<long long>(m) * row_stride;
   pdl_trigger();
   pdl_wait();
   for (int c = threadIdx.x * 8; c < H; c += blockDim.x * 8) {
@@ -55,10 +55,12 @@ __global__ void embed_sum_kernel(const int64_t* __restrict__ ids, const bf16* __
 }
 
 int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf16* out, int M, int H, int n_vq,
-              int audio_rows, int vocab, cudaStream_t s) {
+              int audio_rows, int vocab, cudaStream_t s, int row_stride) {
+  if (row_stride <= 0) row_stride = 1 + n_vq;
   MT_CHECK(H % 8 == 0, "hidden size must be a multiple of 8");
   int threads = H / 8 < 256 ? ((H / 8 + 31) / 32) * 32 : 256;
-  MT_CUDA(launch(embed_sum_kernel, dim3(M), dim3(threads), 0, s, ids, emb_text, emb_ext, out, H, n_vq, audio_rows, vocab));
+  MT_CUDA(launch(embed_sum_kernel, dim3(M), dim3(threads), 0, s, ids, emb_text, emb_ext, out, H, n_vq, audio_rows, vocab,
+                 row_stride));
   count_launch();
   return MT_OK;
 }
@@ -471,6 +473,71 @@ __global__ void gather_last_kernel(const bf16* __restrict__ src, bf16* __restric
 }
 int gather_last(const bf16* src, bf16* dst, int B, int T, int H, cudaStream_t s) {
   MT_CUDA(launch(gather_last_kernel, dim3(B), dim3(256), 0, s, src, dst, T, H));
+  count_launch();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// MossTTSLocal helpers
+//   moss_rmsnorm: MossTTSRMSNorm (reference moss_tts_local/modeling_moss_tts.py:34-44) - unlike Qwen3RMSNorm every
+//     operation runs in the working dtype: p = bf16(x*x); m = bf16(sum p / H)  (fp32 accumulate); r = bf16(rsqrt(bf16(m + eps)));
+//     y = bf16(bf16(x*r) * gain).  x comes as bf16 or as split-K partials of the producing Linear.
+//   embed_rows: out[b,:] = table[ids[b*stride + col], :]   (embedding_list[c] lookup of the token just sampled, :417-420)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+moss_rmsnorm_kernel(const bf16* __restrict__ x, const float* __restrict__ partials, int nsplit, long long split_stride,
+                    const bf16* __restrict__ gain, bf16* __restrict__ out, int H, float eps) {
+  extern __shared__ float srow[];
+  float* scratch = srow + H;
+  const long long m = blockIdx.x;
+  pdl_trigger();
+  pdl_wait();
+  float ss = 0.f;
+  for (int c = threadIdx.x; c < H; c += blockDim.x) {
+    float v;
+    if (partials) {
+      float a = 0.f;
+      for (int s = 0; s < nsplit; ++s) a += partials[s * split_stride + m * H + c];
+      v = rbf(a);
+    } else {
+      v = bf2f(x[m * H + c]);
+    }
+    srow[c] = v;
+    ss += rbf(v * v);
+  }
+  ss = block_sum(ss, scratch);
+  const float mean = rbf(ss / static_cast<float>(H));      // torch's CPU/CUDA mean: fp32 sum, fp32 divide, one rounding
+  const float r = rbf(1.0f / sqrtf(rbf(mean + eps)));
+  for (int c = threadIdx.x; c < H; c += blockDim.x)
+    out[m * H + c] = f2bf(rbf(srow[c] * r) * bf2f(gain[c]));
+}
+
+int moss_rmsnorm(const bf16* x, const float* partials, int nsplit, long long split_stride, const bf16* gain, bf16* out,
+                 int M, int H, float eps, cudaStream_t s) {
+  const size_t smem = (H + 40) * sizeof(float);
+  int threads = ((H + 31) / 32) * 32;
+  if (threads > 1024) threads = 1024;
+  MT_CUDA(launch(moss_rmsnorm_kernel, dim3(M), dim3(threads), smem, s, x, partials, nsplit, split_stride, gain, out, H, eps));
+  count_launch();
+  return MT_OK;
+}
+
+__global__ void embed_rows_kernel(const int64_t* __restrict__ ids, int stride, int col, const bf16* __restrict__ table,
+                                  long long rows, bf16* __restrict__ out, int H) {
+  const int b = blockIdx.x;
+  pdl_trigger();
+  pdl_wait();
+  long long id = ids[static_cast<long long>(b) * stride + col];
+  id = id < 0 ? 0 : (id >= rows ? rows - 1 : id);
+  const uint4* src = reinterpret_cast<const uint4*>(table + id * H);
+  uint4* dst = reinterpret_cast<uint4*>(out + static_cast<long long>(b) * H);
+  for (int c = threadIdx.x; c < H / 8; c += blockDim.x) dst[c] = src[c];
+}
+
+int embed_rows(const int64_t* ids, int stride, int col, const bf16* table, long long rows, bf16* out, int B, int H,
+               cudaStream_t s) {
+  MT_CHECK(H % 8 == 0, "hidden size must be a multiple of 8");
+  MT_CUDA(launch(embed_rows_kernel, dim3(B), dim3(128), 0, s, ids, stride, col, table, rows, out, H));
   count_launch();
   return MT_OK;
 }

@@ -5,8 +5,9 @@
 
 namespace mt {
 
+// ids rows are `row_stride` int64 wide (0 = 1 + n_vq); only channel 0 and the first n_vq audio channels are summed
 int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf16* out, int M, int H, int n_vq,
-              int audio_rows, int vocab, cudaStream_t s);
+              int audio_rows, int vocab, cudaStream_t s, int row_stride = 0);
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
                 bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s);
 int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
@@ -26,5 +27,10 @@ int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_
              cudaStream_t s);
 int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s);
 int gather_last(const bf16* src, bf16* dst, int B, int T, int H, cudaStream_t s);
+// MossTTSLocal: MossTTSRMSNorm (all ops in bf16) and the per-channel embedding lookup of a sampled token
+int moss_rmsnorm(const bf16* x, const float* partials, int nsplit, long long split_stride, const bf16* gain, bf16* out,
+                 int M, int H, float eps, cudaStream_t s);
+int embed_rows(const int64_t* ids, int stride, int col, const bf16* table, long long rows, bf16* out, int B, int H,
+               cudaStream_t s);
 
 }  // namespace mt

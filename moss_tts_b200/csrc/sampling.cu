@@ -12,6 +12,7 @@
 namespace mt {
 
 constexpr int kSampThreads = 256;
+static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- uniform hash shared with oracle/sampling.py::uniform_u ----------------------------------
 __host__ __device__ inline uint32_t mix32(uint32_t x) {
@@ -34,8 +35,17 @@ struct RowXform {
   int ban[6]; int nban;       // ids forced to -inf (all modes)
   int keep0, keep1;           // mode 2: everything else is -inf
   const uint32_t* bitmap; float penalty;   // repetition penalty on ids whose bit is set
+  int penalty_first;          // HF processor order (MossTTSLocal): penalty on the raw logit, then temperature
   __device__ __forceinline__ float get(int i) const {
     float v = bf2f(row[i]);
+    if (penalty_first) {
+      if (bitmap && (bitmap[i >> 5] >> (i & 31) & 1u)) v = v < 0.f ? rbf(v * penalty) : rbf(v / penalty);
+      v = rbf(v / temp);
+#pragma unroll
+      for (int j = 0; j < 6; ++j)
+        if (j < nban && i == ban[j]) return -INFINITY;
+      return v;
+    }
     v = rbf(v / temp);
     if (mode == 2 && i != keep0 && i != keep1) return -INFINITY;
 #pragma unroll
@@ -244,7 +254,7 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
   const int delayed = st.delayed[b];
   int64_t* dst = st.next_ids + static_cast<long long>(b) * st.C + ch;
   RowXform x;
-  x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1; x.bitmap = nullptr; x.penalty = 1.f;
+  x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1; x.bitmap = nullptr; x.penalty = 1.f; x.penalty_first = 0;
   if (ch == 0) {
     // ---- text channel: forced tokens first (modeling_moss_tts.py:453-458)
     int forced = -1;
@@ -379,7 +389,6 @@ __global__ void gen_init_kernel(GenState st, const int64_t* __restrict__ input_i
   }
 }
 
-static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 size_t gen_state_bytes(int B, int C, int max_len, int audio_head) {
   const int words = (audio_head + 31) / 32;
@@ -440,7 +449,7 @@ sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int V, float
   const int r = blockIdx.x;
   RowXform x;
   x.row = logits + r * ld; x.V = V; x.temp = temperature; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
-  x.bitmap = penalty != 1.0f ? bitmap : nullptr; x.penalty = penalty;
+  x.bitmap = penalty != 1.0f ? bitmap : nullptr; x.penalty = penalty; x.penalty_first = 0;
   int tok;
   if (!do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
   else tok = row_sample(x, top_k, top_p, uniforms ? uniforms[r] : 0.f, sm);
@@ -458,6 +467,131 @@ int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperat
                                                   do_sample, uniforms, out);
   count_launch();
   MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// MossTTSLocal (reference moss_tts_local/modeling_moss_tts.py:316-477): one channel of one frame per launch.
+//   local_sample  : logits [B,V] of channel c -> next_ids[b][c]; greedy channels use the raw logits (:361-362),
+//                   sampled ones RepetitionPenalty (per row, over that row's history of the channel, c > 0)
+//                   -> Temperature -> TopK -> TopP (:359-370) and the inverse-CDF draw of this library
+//   local_commit  : EOS / pad substitution for finished rows (:430-433), history append, stop flags
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSampThreads)
+local_sample_kernel(LocalState st, const bf16* __restrict__ logits, int V, int c, int do_sample, float temperature,
+                    float penalty, float top_p, int top_k, unsigned seed) {
+  __shared__ SampSmem sm;
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int b = blockIdx.x;
+  RowXform x;
+  x.row = logits + static_cast<long long>(b) * V; x.V = V; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
+  x.temp = do_sample ? temperature : 1.f; x.bitmap = nullptr; x.penalty = 1.f; x.penalty_first = 1;
+  if (c > 0) { x.ban[0] = V - 1; x.nban = 1; }                 // audio pad code (:411-412)
+  if (do_sample && c > 0 && penalty != 1.0f) {
+    x.bitmap = st.seen + (static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words;
+    x.penalty = penalty;
+  }
+  int tok;
+  if (!do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
+  else tok = row_sample(x, top_k, top_p, mt_uniform(seed, *st.step, b, c), sm);
+  if (threadIdx.x == 0) st.next_ids[static_cast<long long>(b) * st.C + c] = tok;
+}
+
+__global__ void local_commit_kernel(LocalState st, int eos, int pad_code, int n_channels_sampled) {
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int len = *st.len;
+  __shared__ int any_unfinished;
+  if (threadIdx.x == 0) any_unfinished = 0;
+  __syncthreads();
+  for (int i = threadIdx.x; i < st.B * st.C; i += blockDim.x) {
+    const int b = i / st.C, c = i % st.C;
+    long long t = c < n_channels_sampled ? st.next_ids[i] : 0;          // channels beyond n_vq_for_inference: 0 (:427-428)
+    if (eos >= 0 && !st.unfinished[b]) t = c == 0 ? eos : pad_code;
+    st.next_ids[i] = t;
+    if (len < st.max_len) st.gen_ids[(static_cast<long long>(b) * st.max_len + len) * st.C + c] = t;
+    if (c >= 1 && t >= 0 && t < st.bitmap_words * 32)
+      atomicOr(&st.seen[(static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words + (t >> 5)], 1u << (t & 31));
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < st.B; b += blockDim.x) {
+    uint8_t u = st.unfinished[b];
+    if (eos >= 0 && st.next_ids[static_cast<long long>(b) * st.C] == eos) u = 0;
+    st.unfinished[b] = u;
+    if (u) atomicOr(&any_unfinished, 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *st.len = len + 1;
+    *st.pos = len;
+    *st.step = *st.step + 1;
+    if (!any_unfinished) *st.done = 1;
+  }
+}
+
+__global__ void local_init_kernel(LocalState st, const int64_t* __restrict__ input_ids, int S0) {
+  const int b = blockIdx.x;
+  const int64_t* src = input_ids + static_cast<long long>(b) * S0 * st.C;
+  int64_t* g = st.gen_ids + static_cast<long long>(b) * st.max_len * st.C;
+  for (int i = threadIdx.x; i < S0 * st.C; i += blockDim.x) {
+    const int64_t v = src[i];
+    if (st.gen_ids) g[i] = v;
+    const int c = i % st.C;
+    if (c >= 1 && v >= 0 && v < st.bitmap_words * 32)
+      atomicOr(&st.seen[(static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words + (v >> 5)], 1u << (v & 31));
+  }
+  for (int t = threadIdx.x; t < st.max_len; t += blockDim.x) st.mask[static_cast<long long>(b) * st.max_len + t] = 1;
+  if (b == 0)
+    for (int t = threadIdx.x; t < st.C; t += blockDim.x) st.ones[t] = 1;
+  if (threadIdx.x == 0) {
+    st.unfinished[b] = 1;
+    if (b == 0) { *st.len = S0; *st.step = 0; *st.done = 0; *st.pos = S0 - 1; }
+  }
+}
+
+size_t local_state_bytes(int B, int C, int max_len, int audio_head) {
+  const int words = (audio_head + 31) / 32;
+  return 256 + align_up(B, 256) + align_up(static_cast<size_t>(B) * C * 8, 256) + align_up(static_cast<size_t>(B) * max_len, 256) +
+         align_up(C, 256) + align_up(static_cast<size_t>(B) * (C - 1) * words * 4, 256);
+}
+
+LocalState local_state_carve(void* buf, int B, int C, int max_len, int audio_head, int64_t* gen_ids) {
+  LocalState st{};
+  uint8_t* p = reinterpret_cast<uint8_t*>(buf);
+  const int words = (audio_head + 31) / 32;
+  st.len = reinterpret_cast<int*>(p); st.step = st.len + 1; st.done = st.len + 2; st.pos = st.len + 3; p += 256;
+  st.unfinished = p; p += align_up(B, 256);
+  st.next_ids = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * C * 8, 256);
+  st.mask = p; p += align_up(static_cast<size_t>(B) * max_len, 256);
+  st.ones = p; p += align_up(C, 256);
+  st.seen = reinterpret_cast<uint32_t*>(p);
+  st.gen_ids = gen_ids; st.B = B; st.C = C; st.max_len = max_len; st.bitmap_words = words;
+  return st;
+}
+
+int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s) {
+  MT_CUDA(cudaMemsetAsync(st.seen, 0, static_cast<size_t>(st.B) * (st.C - 1) * st.bitmap_words * 4, s));
+  MT_CUDA(launch(local_init_kernel, dim3(st.B), dim3(256), 0, s, st, input_ids, S0));
+  count_launch();
+  return MT_OK;
+}
+
+int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
+                 float top_p, int top_k, unsigned seed, cudaStream_t s) {
+  if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
+    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
+  MT_CUDA(launch(local_sample_kernel, dim3(st.B), dim3(kSampThreads), 0, s, st, logits, V, c, do_sample, temperature,
+                 penalty, top_p, top_k, seed));
+  count_launch();
+  return MT_OK;
+}
+
+int local_commit(const LocalState& st, int eos, int pad_code, int n_channels_sampled, cudaStream_t s) {
+  MT_CUDA(launch(local_commit_kernel, dim3(1), dim3(1024), 0, s, st, eos, pad_code, n_channels_sampled));
+  count_launch();
   return MT_OK;
 }
 

@@ -51,6 +51,24 @@ int gen_init(const GenState& st, const int64_t* input_ids, const uint8_t* attn_m
 int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, const bf16* audio_logits, int audio_head,
                     const SampleCfg& sc, const TokenIds& tk, cudaStream_t s);
 
+// Device-resident state of one MossTTSLocal generate() call (reference moss_tts_local/modeling_moss_tts.py:343-352).
+struct LocalState {
+  int *len, *step, *done, *pos;   // as in GenState
+  uint8_t* unfinished;            // [B] unfinished_sequences (:350)
+  int64_t* next_ids;              // [B, C] tokens of the frame being built == input of the next global forward
+  int64_t* gen_ids;               // [B, max_len, C]
+  uint8_t* mask;                  // [B, max_len] all ones (HF extends the attention mask with ones)
+  uint8_t* ones;                  // [C] all ones: the depth transformer attends to its whole causal prefix
+  uint32_t* seen;                 // [B, C-1, words] per-row, per-channel id sets for RepetitionPenaltyLogitsProcessor
+  int B, C, max_len, bitmap_words;
+};
+size_t local_state_bytes(int B, int C, int max_len, int audio_head);
+LocalState local_state_carve(void* buf, int B, int C, int max_len, int audio_head, int64_t* gen_ids);
+int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s);
+int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
+                 float top_p, int top_k, unsigned seed, cudaStream_t s);
+int local_commit(const LocalState& st, int eos, int pad_code, int n_channels_sampled, cudaStream_t s);
+
 int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
                   float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
                   cudaStream_t s);

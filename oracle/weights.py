@@ -14,7 +14,7 @@ from typing import Dict
 
 import torch
 
-from moss_tts_b200.config import LMConfig, CodecConfig
+from moss_tts_b200.config import LMConfig, CodecConfig, LocalConfig
 
 
 def _gen(seed: int, name: str) -> torch.Generator:
@@ -59,6 +59,50 @@ def make_lm_weights(cfg: LMConfig, seed: int = 0, never_stop: bool = False,
     if never_stop:
         w["lm_heads.0.weight"][cfg.audio_assistant_delay_slot_token_id] = \
             w["lm_heads.0.weight"][cfg.audio_assistant_gen_slot_token_id]
+    return w
+
+
+def _qwen_layer(w, seed, p, H, I, q_size, kv_size, head_dim, std):
+    w[p + "self_attn.q_proj.weight"] = _normal(seed, p + "q", (q_size, H), std)
+    w[p + "self_attn.k_proj.weight"] = _normal(seed, p + "k", (kv_size, H), std)
+    w[p + "self_attn.v_proj.weight"] = _normal(seed, p + "v", (kv_size, H), std)
+    w[p + "self_attn.o_proj.weight"] = _normal(seed, p + "o", (H, q_size), std)
+    w[p + "self_attn.q_norm.weight"] = _normal(seed, p + "qn", (head_dim,), 0.1, 1.0)
+    w[p + "self_attn.k_norm.weight"] = _normal(seed, p + "kn", (head_dim,), 0.1, 1.0)
+    w[p + "mlp.gate_proj.weight"] = _normal(seed, p + "g", (I, H), std)
+    w[p + "mlp.up_proj.weight"] = _normal(seed, p + "u", (I, H), std)
+    w[p + "mlp.down_proj.weight"] = _normal(seed, p + "d", (H, I), std)
+    w[p + "input_layernorm.weight"] = _normal(seed, p + "ln1", (H,), 0.1, 1.0)
+    w[p + "post_attention_layernorm.weight"] = _normal(seed, p + "ln2", (H,), 0.1, 1.0)
+
+
+def make_local_weights(cfg: LocalConfig, seed: int = 0, std: float = 0.02, eos_bias: float = 0.0) -> Dict[str, torch.Tensor]:
+    """fp32 master weights of MossTTSLocal under the reference's state_dict keys
+    (moss_tts_local/modeling_moss_tts.py:495-507, 573-611).  std 0.05 on the small adapters keeps the
+    depth chain's activations O(1) so that rounding-point mistakes show up in the greedy ids."""
+    w: Dict[str, torch.Tensor] = {}
+    H, I, C = cfg.hidden_size, cfg.intermediate_size, cfg.n_vq + 1
+    LH, LF, AF = cfg.local_hidden_size, cfg.local_ffn_hidden_size, cfg.additional_mlp_ffn_hidden_size
+    w["model.embedding_list.0.weight"] = _normal(seed, "emb0", (cfg.vocab_size, H), std)
+    for i in range(1, C):
+        w[f"model.embedding_list.{i}.weight"] = _normal(seed, f"emb{i}", (cfg.audio_head_size, H), std)
+    for l in range(cfg.num_layers):
+        _qwen_layer(w, seed, f"model.language_model.layers.{l}.", H, I, cfg.q_size, cfg.kv_size, cfg.head_dim, std)
+    w["model.language_model.norm.weight"] = _normal(seed, "gnorm", (H,), 0.1, 1.0)
+    for l in range(cfg.local_num_layers):
+        _qwen_layer(w, seed, f"local_transformer.layers.{l}.", LH, LF, cfg.q_size, cfg.kv_size, cfg.head_dim, 2 * std)
+    w["local_transformer.norm.weight"] = _normal(seed, "lnorm", (LH,), 0.1, 1.0)
+    a = 3 * std
+    w["speech_embedding_to_local_mlp.gate_proj.weight"] = _normal(seed, "in.g", (AF, H), a)
+    w["speech_embedding_to_local_mlp.up_proj.weight"] = _normal(seed, "in.u", (AF, H), a)
+    w["speech_embedding_to_local_mlp.down_proj.weight"] = _normal(seed, "in.d", (LH, AF), a)
+    for c in range(C):
+        p = f"local_to_speech_embedding_mlps.{c}."
+        w[p + "gate_proj.weight"] = _normal(seed, p + "g", (AF, LH), a)
+        w[p + "up_proj.weight"] = _normal(seed, p + "u", (AF, LH), a)
+        w[p + "down_proj.weight"] = _normal(seed, p + "d", (H, AF), a)
+        w[f"layer_norm_before_lm_heads.{c}.weight"] = _normal(seed, f"hn{c}", (H,), 0.1, 1.0)
+        w[f"lm_heads.{c}.weight"] = _normal(seed, f"head{c}", (cfg.vocab_size if c == 0 else cfg.audio_head_size, H), std)
     return w
 
 
