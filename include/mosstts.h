@@ -66,6 +66,10 @@ int mt_debug_force_simt(int on);
 /* Debug knob: launch kernels with (1, default) or without (0) the programmatic-dependent-launch
  * attribute.  Results are bit-identical either way; only kernel overlap changes. */
 int mt_debug_set_pdl(int on);
+/* Debug timeline: every decode-GEMM launch issued (or captured into a graph) after this call takes the next
+ * 148*8 uint64 slots of the device buffer `buf` and records 8 %globaltimer stamps per CTA (scripts/trace_decode.py).
+ * NULL switches it off.  Returns the number of slots handed out since the previous call. */
+long long mt_debug_set_trace(void* buf, long long words);
 
 /* ------------------------------------------------------------------------------------------
  * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:

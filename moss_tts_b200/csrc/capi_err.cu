@@ -23,3 +23,18 @@ bool pdl_enabled() {
 }
 void set_pdl(int on) { g_pdl_state = on ? 1 : 0; }
 }
+
+namespace mt {
+static unsigned long long* g_trace_buf = nullptr;
+static long long g_trace_cap = 0, g_trace_next = 0;
+void set_trace(void* buf, long long words) {
+  g_trace_buf = reinterpret_cast<unsigned long long*>(buf); g_trace_cap = buf ? words : 0; g_trace_next = 0;
+}
+long long trace_used() { return g_trace_next; }
+unsigned long long* trace_slot(int words) {
+  if (!g_trace_buf || g_trace_next + words > g_trace_cap) return nullptr;
+  unsigned long long* p = g_trace_buf + g_trace_next;
+  g_trace_next += words;
+  return p;
+}
+}

@@ -49,6 +49,8 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 bool pdl_enabled();
+// Debug timeline buffer (mt_debug_set_trace): returns the next `words` uint64 slots, or nullptr when tracing is off.
+unsigned long long* trace_slot(int words);
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {

@@ -39,7 +39,8 @@ template <int BN, int KIND /*1 bf16, 2 tf32*/>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int rowsA,
                 int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled, int exp_nox,
-                const int* __restrict__ full_flag, int keep_lo, int keep_hi) {
+                const int* __restrict__ full_flag, int keep_lo, int keep_hi, int pf_stages, int pf_hint,
+                unsigned long long* __restrict__ trace) {
   using C = DecCfg<BN>;
   constexpr int S = C::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -59,6 +60,15 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   // gen/delay-slot logits are read by the sampler, modeling_moss_tts.py:459-460): when *full_flag == 0 only
   // the weight tiles keep_lo..keep_hi are computed.  The flag is read after pdl_wait by every role.
   auto skip_tile = [&](bool restricted, int tile) { return restricted && (tile < keep_lo || tile > keep_hi); };
+  // timeline instrumentation (mt_debug_set_trace; null in every product run): 8 global-timer stamps per CTA
+  auto stamp = [&](int e) {
+    if (trace) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      trace[blockIdx.x * 8 + e] = t;
+    }
+  };
+  if (threadIdx.x == 0) stamp(0);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -81,7 +91,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
-  if (threadIdx.x == 0) pdl_trigger();
+  if (threadIdx.x == 0) { pdl_trigger(); stamp(1); }
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -105,8 +115,23 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             load_w(pre, tile, kb);
           }
         }
+        // the ring is full and x is not there yet: use the idle HBM time to pull the NEXT weight tiles of this
+        // CTA's unit list into L2, where the ring will find them once the main loop drains it
+        if (pf_stages > 0) {
+          int idx = 0;
+          for (int u = blockIdx.x; u < units && idx < pre + pf_stages; u += gridDim.x) {
+            const int tile = u % tiles, split = u / tiles;
+            for (int kb = kb_begin(split); kb < kb_begin(split + 1) && idx < pre + pf_stages; ++kb, ++idx) {
+              if (idx < pre) continue;
+              const uint64_t hint = pf_hint == 0 ? ptx::kEvictFirst : (pf_hint == 1 ? ptx::kEvictNormal : ptx::kEvictLast);
+              if (w_tiled) ptx::tma_prefetch_2d(&tmA, 0, (tile * k_blocks + kb) * kTileA, hint);
+              else ptx::tma_prefetch_2d(&tmA, kb * kKElems, tile * kTileA, hint);
+            }
+          }
+        }
       }
       pdl_wait();
+      stamp(3);
       const bool restricted = full_flag && *full_flag == 0;
       int it = 0;
       for (int u = blockIdx.x; u < units; u += gridDim.x) {
@@ -140,6 +165,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int j = 0; j < n; ++j, ++it) {
           const int st = it % S;
           ptx::mbar_wait(&full[st], (it / S) & 1);
+          if (it == 0) stamp(4);
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(smem + st * C::kStageBytes);
           const uint64_t adesc = ptx::make_smem_desc_sw128(sa);
@@ -154,6 +180,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         ptx::mma_commit(&tmem_full[buf]);
         ++i;
       }
+      stamp(5);
     }
   } else {
     // ===== epilogue: warp w reads TMEM lanes 32*(w%4).., columns [(w-2)/4 * BN/2, +BN/2) =====
@@ -169,6 +196,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (skip_tile(restricted, tile)) continue;
       const int buf = i & 1;
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
+      if (warp == 2 && lane == 0) stamp(6);
       ptx::tc_fence_after();
       const int n = tile * kTileA + q * 32 + lane;       // output feature of this lane
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN + half * CW;
@@ -180,13 +208,25 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         ptx::tmem_ld_wait();
         if (n < rowsA) {
           const int m0 = half * CW + c0;
+          if (ep.partial) {
+            // hot path of every decode layer: one base pointer, predicated stores (the generic epilogue below
+            // unrolls into ~9k instructions and ran out of the instruction cache: 3 us per unit)
+            // (32-bit element offsets: linear_dec checks that the partial buffer holds < 2^31 floats)
+            float* dst = ep.partial + (static_cast<uint32_t>(split * ep.M + m0) * static_cast<uint32_t>(ep.N) + static_cast<uint32_t>(n));
+            const int ldn = ep.N;
+            const int valid = rowsB - m0;
+            if (valid >= CH) {
 #pragma unroll
-          for (int j = 0; j < CH; ++j) {
-            const int m = m0 + j;
-            if (m < rowsB) {
-              const float v = __uint_as_float(r[j]);
-              if (ep.partial) ep.partial[(static_cast<long long>(split) * ep.M + m) * ep.N + n] = v;
-              else epi_store(ep, m, n, epi_apply(ep, m, n, v));
+              for (int j = 0; j < CH; ++j) { *dst = __uint_as_float(r[j]); dst += ldn; }
+            } else {
+#pragma unroll
+              for (int j = 0; j < CH; ++j) { if (j < valid) *dst = __uint_as_float(r[j]); dst += ldn; }
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < CH; ++j) {
+              const int m = m0 + j;
+              if (m < rowsB) epi_store(ep, m, n, epi_apply(ep, m, n, __uint_as_float(r[j])));
             }
           }
         }
@@ -196,11 +236,13 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
       ++i;
     }
+    if (warp == 2 && lane == 0) stamp(7);
   }
 
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 1) ptx::tmem_dealloc(tmem_base, C::kTmemCols);
+  if (threadIdx.x == 0) stamp(2);
 }
 
 template <int BN, int KIND>
@@ -218,8 +260,11 @@ int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, in
   const int grid = units < kNumSMs ? units : kNumSMs;
   // timing experiment only (garbage results): do not load the activation operand
   static const int exp_nox = [] { const char* e = getenv("MT_EXP_NOX"); return e && e[0] == '1' ? 1 : 0; }();
+  // L2 prefetch depth (ring stages' worth of weight tiles per CTA) issued while waiting for the producer kernel
+  static const int pf_stages = [] { const char* e = getenv("MT_DEC_PF"); return e ? atoi(e) : 0; }();
+  static const int pf_hint = [] { const char* e = getenv("MT_DEC_PF_HINT"); return e ? atoi(e) : 0; }();
   MT_CUDA(launch(kern, dim3(grid), dim3(kThreads), C::kTotal, s, tmA, tmB, ep, rowsA, rowsB, k_blocks, tiles, splits,
-                 w_early, w_tiled, exp_nox, full_flag, keep_lo, keep_hi));
+                 w_early, w_tiled, exp_nox, full_flag, keep_lo, keep_hi, pf_stages, pf_hint, trace_slot(kNumSMs * 8)));
   count_launch();
   return MT_OK;
 }
@@ -257,6 +302,7 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   const long long per_split = static_cast<long long>(p.M) * p.N * 4;
   int splits = 1;
   if (p.workspace) splits = dec_pick_splits(tiles, k_blocks, per_split, p.workspace_bytes);
+  MT_CHECK(per_split / 4 * splits < (1ll << 31), "linear_dec: split-K partials exceed 2^31 elements");
   if (p.out_splits) {
     MT_CHECK(p.workspace && per_split <= p.workspace_bytes, "linear: workspace too small for partial output");
     *p.out_splits = splits;

@@ -39,7 +39,8 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
                    const bf16* __restrict__ q_gain, const bf16* __restrict__ k_gain, const bf16* __restrict__ rope_cos,
                    const bf16* __restrict__ rope_sin, bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
                    const uint8_t* __restrict__ mask, long long mask_ld, bf16* __restrict__ out, int n_heads, int n_kv,
-                   const int* __restrict__ pos_dev, int pos_host, int spad, int max_seq, float eps, float scale) {
+                   const int* __restrict__ pos_dev, int pos_host, int spad, int max_seq, float eps, float scale,
+                   unsigned long long* __restrict__ trace) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
   constexpr int E = D / 32;
   const int G = n_heads / n_kv;
@@ -51,8 +52,18 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   float* sc = reinterpret_cast<float*>(sm_raw + attn_fixed_bytes<D>());
   bf16* sp = reinterpret_cast<bf16*>(sm_raw + attn_fixed_bytes<D>() + static_cast<size_t>(G) * spad * 4);
 
+  // timeline instrumentation (mt_debug_set_trace; null in every product run)
+  auto stamp = [&](int e) {
+    if (trace && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      trace[blockIdx.x * 8 + e] = t;
+    }
+  };
+  stamp(0);
   pdl_trigger();
   pdl_wait();
+  stamp(1);
   const int b = blockIdx.x / n_kv, kvh = blockIdx.x % n_kv;
   const int pos = pos_dev ? *pos_dev : pos_host;
   const int nkeys = pos + 1;
@@ -150,6 +161,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   }
   for (int i = G * D + threadIdx.x; i < kMaxG * D; i += blockDim.x) sq[i] = f2bf(0.f);   // unused query rows
   __syncthreads();       // block-scope barrier also orders the appended k/v row before the reads below
+  stamp(2);
 
   // ---- A fragments of Q: rows 0..7 = query heads (rows 8..15 are zero)
   uint32_t qa[D / 16][2];
@@ -200,6 +212,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
     }
   }
   __syncthreads();
+  stamp(3);
 
   // ---- softmax over the visible keys (fp32), one warp per head; p = bf16(e / sum), keys past nkeys get 0
   const int kpad = (nkeys + 15) & ~15;
@@ -220,6 +233,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
     for (int k = lane; k < kpad; k += 32) prow[k] = f2bf((k < nkeys && sum > 0.f) ? row[k] / sum : 0.f);
   }
   __syncthreads();
+  stamp(4);
 
   // ---- pass 2: O = P.V, 16 keys per warp and iteration.  Dim-pair tile p covers dims [16p, 16p+16): the
   // "even" n-tile holds dims 16p+2g, the "odd" one dims 16p+2g+1 (g = fragment column), both built from
@@ -256,6 +270,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
           make_float4(oe[p][0], oo[p][0], oe[p][1], oo[p][1]);
   }
   __syncthreads();
+  stamp(5);
   for (int i = threadIdx.x; i < G * D; i += blockDim.x) {
     const int h = i / D, d = i % D;
     float v = 0.f;
@@ -263,6 +278,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
     for (int w = 0; w < kWarps; ++w) v += red[(w * kMaxG + h) * D + d];
     out[(static_cast<long long>(b) * n_heads + kvh * G + h) * D + d] = f2bf(v);
   }
+  stamp(6);
 }
 
 }  // namespace
@@ -293,7 +309,7 @@ int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long sp
   }
   MT_CUDA(launch(kern, dim3(B * n_kv), dim3(kWarps * 32), smem, s, qkv, partials, nsplit, split_stride, q_gain, k_gain,
                  rope_cos, rope_sin, k_cache, v_cache, mask, mask_ld, out, n_heads, n_kv, pos_dev, pos_host, spad,
-                 max_seq, eps, 1.0f / sqrtf(static_cast<float>(D))));
+                 max_seq, eps, 1.0f / sqrtf(static_cast<float>(D)), trace_slot(B * n_kv * 8)));
   count_launch();
   return MT_OK;
 }

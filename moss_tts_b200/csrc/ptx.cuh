@@ -78,9 +78,10 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 // Ask L2 to fetch a tile (no shared-memory destination, no completion signal).
-__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1) {
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int c0, int c1,
+                                                uint64_t hint = 0x12F0000000000000ull /* evict first */) {
   asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile.L2::cache_hint [%0, {%1, %2}], %3;"
-               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "l"(0x12F0000000000000ull /* evict first */)
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "l"(hint)
                : "memory");
 }
 // L2 eviction-priority hints (same encodings CUTLASS uses for TMA::CacheHintSm90)

@@ -1,0 +1,60 @@
+"""Standalone roofline of the sampler (SURVEY.md §8d "sampling"): mt_sample_tokens over many rows so that the
+logits (one read, the algorithmic bytes) exceed L2.  Prints one JSON line per case.
+
+  python scripts/bench_sampling.py [--rows 2048] [--iters 5]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--rows", type=int, default=2048)
+    ap.add_argument("--iters", type=int, default=5)
+    args = ap.parse_args()
+    from moss_tts_b200 import _lib as L
+    from moss_tts_b200.inference_utils import sample_token
+    import bench
+    hbm, _, src = bench.measured_peaks()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    cases = [("text greedy", args.rows, 151936, dict(do_sample=False)),
+             ("text top-k 50", args.rows, 151936, dict(do_sample=True, top_k=50, top_p=1.0)),
+             ("audio greedy", args.rows * 64, 1025, dict(do_sample=False)),
+             ("audio top-k 25 top-p 0.8 penalty 1.1", args.rows * 64, 1025,
+              dict(do_sample=True, top_k=25, top_p=0.8, repetition_penalty=1.1))]
+    for name, n, v, kw in cases:
+        logits = (torch.randn(n, v, device=dev) * 2).to(torch.bfloat16)
+        prev = torch.randint(0, v, (4096,), device=dev) if "repetition_penalty" in kw else None
+        u = torch.rand(n, device=dev)
+        for _ in range(2):
+            sample_token(logits, prev, uniforms=u, **kw)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = L.launch_count()
+        e0.record()
+        for _ in range(args.iters):
+            sample_token(logits, prev, uniforms=u, **kw)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.iters
+        nbytes = logits.numel() * 2 + n * 8
+        print(json.dumps({"case": name, "rows": n, "vocab": v, "ms": ms, "algorithmic_bytes": nbytes,
+                          "achieved_gbs": nbytes / (ms * 1e-3) / 1e9, "peak_gbs": hbm, "frac": nbytes / (ms * 1e-3) / 1e9 / hbm,
+                          "launches_per_call": (L.launch_count() - l0) / args.iters, "peak_source": src,
+                          "note": "logits larger than L2 (%.0f MB); host-side bitmap/uniform prep of the wrapper is inside the timing" % (logits.numel() * 2 / 1e6)}),
+              flush=True)
+        del logits
+
+
+if __name__ == "__main__":
+    main()

@@ -145,3 +145,21 @@ def test_forward_rejects_bad_shape():
         model.forward(torch.zeros(1, 4, 3, dtype=torch.int64))
     with pytest.raises(ValueError):
         model.generate(torch.zeros(1, 4, 3, dtype=torch.int64))
+
+
+def test_generate_long_context_n_vq16():
+    """configs[4] shape family (TTSD: n_vq = 16, long multi-speaker prompt with codes in the audio channels,
+    ragged left padding, repetition penalty 1.1): KV lengths ~900-960 through the fused decode attention."""
+    cfg = LMConfig.tiny(n_vq=16)
+    w = make_lm_weights(cfg, seed=21, never_stop=True)
+    model = MossTTSDelayModel(cfg, w, device=DEV)
+    oracle = OracleLM(cfg, w, torch.bfloat16)
+    ids, mask = make_prompt(cfg, 3, 900, seed=21, left_pad=[0, 37, 411])
+    g = torch.Generator().manual_seed(3)
+    codes = torch.randint(0, cfg.audio_vocab_size, (3, 600, cfg.n_vq), generator=g)
+    ids[:, 200:800, 1:] = torch.where(mask[:, 200:800, None], codes, ids[:, 200:800, 1:])    # reference audio in the prompt
+    kw = dict(max_new_tokens=40, text_temperature=0, audio_temperature=0, audio_repetition_penalty=1.1)
+    out = model.generate(ids, mask, **kw)
+    o_out, trace = oracle.generate(ids, mask, return_trace=True, **kw)
+    exact = _check_tokens(out, [o[1].numpy() for o in o_out], trace, [o[0] for o in o_out], "tiny-nvq16-long")
+    print(f"[tiny-nvq16-long] greedy ids bit-exact vs oracle: {exact}")
