@@ -108,9 +108,10 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       // pass 1 (only with constant weights): fill the ring with weight tiles before the dependency wait
       int pre = 0;
       if (w_early) {
-        for (int u = blockIdx.x; u < units && pre < S; u += gridDim.x) {
+        const int depth = w_early < S ? w_early : S;
+        for (int u = blockIdx.x; u < units && pre < depth; u += gridDim.x) {
           const int tile = u % tiles, split = u / tiles;
-          for (int kb = kb_begin(split); kb < kb_begin(split + 1) && pre < S; ++kb, ++pre) {
+          for (int kb = kb_begin(split); kb < kb_begin(split + 1) && pre < depth; ++kb, ++pre) {
             ptx::mbar_expect_tx(&full[pre], exp_nox ? C::kABytes : C::kStageBytes);
             load_w(pre, tile, kb);
           }
@@ -279,7 +280,9 @@ int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long lon
   for (int sp = 1; sp <= 32; ++sp) {
     if (sp > 1 && (k_blocks / sp < 4 || per_split_bytes * sp > workspace_bytes)) break;
     const long long rounds = (static_cast<long long>(tiles) * sp + kNumSMs - 1) / kNumSMs;
-    const long long cost = rounds * ((k_blocks + sp - 1) / sp + 2);
+    // + sp: every split is another [M, N] fp32 slab the consumer kernel has to pull through its few SMs' L2 ports
+    // (add_rmsnorm: one block per row), about one k-block of time each
+    const long long cost = rounds * ((k_blocks + sp - 1) / sp + 2) + sp;
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = sp; }
   }
   return best;
@@ -312,7 +315,11 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   }
   const int w_tiled = p.w_tiled ? 1 : 0;
   // a filtered launch decides its unit list after the dependency wait: no early weight fetch
-  const int w_early = p.w_static && !p.tile_filter_flag ? 1 : 0;
+  // (w_early = number of ring stages requested before the dependency wait.  The full ring is NOT the best
+  // choice: 148 CTAs x 8 stages = 19 MB of HBM requests land exactly when the small kernel between two GEMMs
+  // issues its handful of latency-critical L2 reads, which then queue behind them for ~3 us.)
+  static const int early_depth = [] { const char* e = getenv("MT_DEC_EARLY"); return e ? atoi(e) : 64; }();
+  const int w_early = p.w_static && !p.tile_filter_flag ? early_depth : 0;
   const int keep_lo = p.tile_lo / kTileA, keep_hi = p.tile_hi / kTileA;
   if (p.tile_filter_flag) MT_CHECK(splits == 1 && !p.out_splits, "linear_dec: the row-tile filter needs an unsplit GEMM");
   const bool bf = p.dtype_in == MT_DTYPE_BF16;

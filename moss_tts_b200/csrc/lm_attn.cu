@@ -16,6 +16,8 @@
 // kernel for prefill (T > 1) and for contexts whose scores do not fit in shared memory.
 #include "lm_ops.cuh"
 
+#include <stdlib.h>
+
 namespace mt {
 
 namespace {
@@ -40,7 +42,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
                    const bf16* __restrict__ rope_sin, bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
                    const uint8_t* __restrict__ mask, long long mask_ld, bf16* __restrict__ out, int n_heads, int n_kv,
                    const int* __restrict__ pos_dev, int pos_host, int spad, int max_seq, float eps, float scale,
-                   unsigned long long* __restrict__ trace) {
+                   unsigned long long* __restrict__ trace, int exp_flags) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
   constexpr int E = D / 32;
   const int G = n_heads / n_kv;
@@ -65,95 +67,156 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   pdl_wait();
   stamp(1);
   const int b = blockIdx.x / n_kv, kvh = blockIdx.x % n_kv;
-  const int pos = pos_dev ? *pos_dev : pos_host;
-  const int nkeys = pos + 1;
   const int heads_total = n_heads + 2 * n_kv;
   const long long row_w = static_cast<long long>(heads_total) * D;
+
+  // ---- the q/k/v inputs of this block are requested first (they do not depend on the position): a warp owns
+  // heads warp, warp + kWarps, ... (G query heads, then the k and the v head); lane owns elements lane + 32e.
+  // Every load of the first four splits is in flight before anything else is asked of the memory system.
+  constexpr int kSlots = (kMaxG + 2 + kWarps - 1) / kWarps;
+  long long idx0[kSlots];
+  bool live[kSlots];
+#pragma unroll
+  for (int sl = 0; sl < kSlots; ++sl) {
+    const int i = warp + sl * kWarps;
+    live[sl] = i < G + 2;
+    const int hh = i < G ? kvh * G + i : (i == G ? n_heads + kvh : n_heads + n_kv + kvh);
+    idx0[sl] = b * row_w + static_cast<long long>(hh) * D + lane;
+  }
+  float t0[kSlots][4][E];
+#pragma unroll
+  for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        if (partials) t0[sl][u][e] = (live[sl] && u < nsplit) ? __ldcg(partials + u * split_stride + idx0[sl] + 32 * e) : 0.f;
+        else t0[sl][u][e] = (live[sl] && u == 0) ? bf2f(qkv[idx0[sl] + 32 * e]) : 0.f;
+      }
+  float gq[E], gk[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) {
+    gq[e] = bf2f(q_gain[lane + 32 * e]);
+    gk[e] = bf2f(k_gain[lane + 32 * e]);
+  }
+
+  const int pos = pos_dev ? *pos_dev : pos_host;
+  const int nkeys = pos + 1;
   bf16* kbase = k_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
   bf16* vbase = v_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
 
   // the K/V rows of this (row, kv head) come from HBM (the cache is far larger than L2 and 15 GB of weights
   // pass through between two visits): ask L2 for all of them now, so that the dependent phases below
   // (scores -> softmax -> P.V) find them on chip
-  for (int i = threadIdx.x; i < 2 * pos * (D / 64); i += blockDim.x) {
-    const int which = i / (pos * (D / 64)), r = i % (pos * (D / 64));
-    const bf16* p = (which ? vbase : kbase) + static_cast<long long>(r) * 64;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  // (one bulk prefetch per tensor: the rows [0, pos) of a (row, kv head) are contiguous)
+  if (threadIdx.x < 2 && pos > 0 && !(exp_flags & 1)) {
+    const bf16* p = threadIdx.x ? vbase : kbase;
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(pos * D * 2) : "memory");
   }
 
   // first score tile of this warp: its K rows are requested now and land while the prep below runs.
   // Row `pos` (the token being appended) does not exist yet: clamp to pos-1 and patch after the barrier.
-  uint32_t kb[2][D / 16][2];
+  // The dot product over the head dim does not care in which MMA k-slot a dim sits as long as Q uses the same
+  // order: lane (g, t4) reads 16 contiguous bytes (dims 32c + 8 t4 .. +7) of its key row per chunk c, and k-step
+  // s = 2c + h takes dims +4h, +4h+1 as k-slots (2 t4, 2 t4 + 1) and dims +4h+2, +4h+3 as slots (2 t4 + 8, + 9).
+  // 8 LDG.128 per 16-key tile instead of 32 LDG.32 that each touched 8 rows (the LSU was the bottleneck).
+  uint4 kq[2][D / 32];
   auto load_k = [&](int k0, int limit) {
 #pragma unroll
     for (int n = 0; n < 2; ++n) {
       const int key = min(k0 + 8 * n + g, limit);
-      const uint32_t* kr = reinterpret_cast<const uint32_t*>(kbase + static_cast<long long>(key) * D) + t4;
+      const uint4* kr = reinterpret_cast<const uint4*>(kbase + static_cast<long long>(key) * D) + t4;
 #pragma unroll
-      for (int s = 0; s < D / 16; ++s) { kb[n][s][0] = kr[8 * s]; kb[n][s][1] = kr[8 * s + 4]; }
+      for (int c = 0; c < D / 32; ++c) kq[n][c] = kr[4 * c];
     }
   };
   const int kfirst = 16 * warp;
-  if (kfirst < nkeys) load_k(kfirst, max(pos - 1, 0));
+  const bool early_k = kfirst < nkeys && !(exp_flags & 2);
+  if (early_k) load_k(kfirst, max(pos - 1, 0));
 
-  // ---- prep: G query heads, then the k and v head of this group; one warp per head (lane owns lane + 32e)
-  for (int i = warp; i < G + 2; i += kWarps) {
-    const int hh = i < G ? kvh * G + i : (i == G ? n_heads + kvh : n_heads + n_kv + kvh);
-    float x[E];
-    const long long idx0 = b * row_w + static_cast<long long>(hh) * D + lane;
-    if (partials) {
-      // all loads of four splits are issued before the first add; the sum order (split 0,1,2,...) is kept
-      float a[E];
+  // ---- prep: sum the split-K partials (split order 0, 1, 2, ... kept), RMSNorm, RoPE, append k/v
+  float rc[E], rs[E];
 #pragma unroll
-      for (int e = 0; e < E; ++e) a[e] = 0.f;
-      int sidx = 0;
-      for (; sidx + 4 <= nsplit; sidx += 4) {
-        float t[4][E];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-#pragma unroll
-          for (int e = 0; e < E; ++e) t[u][e] = partials[(sidx + u) * split_stride + idx0 + 32 * e];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-#pragma unroll
-          for (int e = 0; e < E; ++e) a[e] += t[u][e];
-      }
-      for (; sidx < nsplit; ++sidx) {
-        float t[E];
-#pragma unroll
-        for (int e = 0; e < E; ++e) t[e] = partials[sidx * split_stride + idx0 + 32 * e];
-#pragma unroll
-        for (int e = 0; e < E; ++e) a[e] += t[e];
-      }
-#pragma unroll
-      for (int e = 0; e < E; ++e) x[e] = rbf(a[e]);
+  for (int e = 0; e < E; ++e) {
+    if (rope_cos) {
+      const int jh = (lane + 32 * e) % (D / 2);
+      rc[e] = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
+      rs[e] = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
     } else {
-#pragma unroll
-      for (int e = 0; e < E; ++e) x[e] = bf2f(qkv[idx0 + 32 * e]);
+      rc[e] = 1.f; rs[e] = 0.f;
     }
+  }
+  float xs[kSlots][E];
+  if (partials) {
+    float a[kSlots][E];
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+      for (int e = 0; e < E; ++e) a[sl][e] = 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (u < nsplit) {
+#pragma unroll
+        for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+          for (int e = 0; e < E; ++e) a[sl][e] += t0[sl][u][e];
+      }
+    for (int s0 = 4; s0 < nsplit; s0 += 4) {
+      float t[kSlots][4][E];
+#pragma unroll
+      for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+#pragma unroll
+          for (int e = 0; e < E; ++e)
+            t[sl][u][e] = (live[sl] && s0 + u < nsplit) ? __ldcg(partials + (s0 + u) * split_stride + idx0[sl] + 32 * e) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < nsplit) {
+#pragma unroll
+          for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+            for (int e = 0; e < E; ++e) a[sl][e] += t[sl][u][e];
+        }
+    }
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+      for (int e = 0; e < E; ++e) xs[sl][e] = rbf(a[sl][e]);
+    if (xs[0][0] != 12345.678f) stamp(7);
+  } else {
+#pragma unroll
+    for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+      for (int e = 0; e < E; ++e) xs[sl][e] = t0[sl][0][e];
+  }
+#pragma unroll
+  for (int sl = 0; sl < kSlots; ++sl) {
+    const int i = warp + sl * kWarps;
+    if (i >= G + 2) break;
+    float x[E];
+#pragma unroll
+    for (int e = 0; e < E; ++e) x[e] = xs[sl][e];
     if (i <= G) {
-      const bf16* gain = i < G ? q_gain : k_gain;
       float ss = 0.f;
 #pragma unroll
       for (int e = 0; e < E; ++e) ss += x[e] * x[e];
       ss = warp_sum(ss);
       const float inv = rsqrtf(ss / static_cast<float>(D) + eps);
 #pragma unroll
-      for (int e = 0; e < E; ++e) x[e] = rbf(bf2f(gain[lane + 32 * e]) * rbf(x[e] * inv));
-      float y[E];
+      for (int e = 0; e < E; ++e) x[e] = rbf((i < G ? gq[e] : gk[e]) * rbf(x[e] * inv));
+      if (rope_cos) {                // MossTTSLocal's depth transformer has no rotary embedding
+        float y[E];
 #pragma unroll
-      for (int e = 0; e < E; ++e) {
-        if (!rope_cos) { y[e] = x[e]; continue; }     // MossTTSLocal's depth transformer has no rotary embedding
-        const int j = lane + 32 * e;
-        const int jh = j % (D / 2);
-        const float c = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
-        const float sn = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
-        const float partner = x[(e + E / 2) % E];
-        const float rot = j < D / 2 ? -partner : partner;
-        y[e] = rbf(rbf(x[e] * c) + rbf(rot * sn));
+        for (int e = 0; e < E; ++e) {
+          const int j = lane + 32 * e;
+          const float partner = x[(e + E / 2) % E];
+          const float rot = j < D / 2 ? -partner : partner;
+          y[e] = rbf(rbf(x[e] * rc[e]) + rbf(rot * rs[e]));
+        }
+#pragma unroll
+        for (int e = 0; e < E; ++e) x[e] = y[e];
       }
-#pragma unroll
-      for (int e = 0; e < E; ++e) x[e] = y[e];
     }
     bf16* dst = i < G ? sq + i * D : (i == G ? kbase : vbase) + static_cast<long long>(pos) * D;
 #pragma unroll
@@ -167,22 +230,23 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   uint32_t qa[D / 16][2];
 #pragma unroll
   for (int s = 0; s < D / 16; ++s) {
-    qa[s][0] = *reinterpret_cast<const uint32_t*>(sq + g * D + 16 * s + 2 * t4);
-    qa[s][1] = *reinterpret_cast<const uint32_t*>(sq + g * D + 16 * s + 2 * t4 + 8);
+    const int d0 = 32 * (s >> 1) + 8 * t4 + 4 * (s & 1);
+    qa[s][0] = *reinterpret_cast<const uint32_t*>(sq + g * D + d0);
+    qa[s][1] = *reinterpret_cast<const uint32_t*>(sq + g * D + d0 + 2);
   }
   const uint8_t* mrow = mask + b * mask_ld;
 
   // ---- pass 1: scores, 16 keys per warp and iteration
   for (int k0 = kfirst; k0 < nkeys; k0 += 16 * kWarps) {
-    if (k0 != kfirst) {
+    if (k0 != kfirst || !early_k) {
       load_k(k0, nkeys - 1);
     } else {
 #pragma unroll
       for (int n = 0; n < 2; ++n) {
         if (k0 + 8 * n + g >= pos) {          // this lane's row is the one the prep just wrote
-          const uint32_t* kr = reinterpret_cast<const uint32_t*>(kbase + static_cast<long long>(pos) * D) + t4;
+          const uint4* kr = reinterpret_cast<const uint4*>(kbase + static_cast<long long>(pos) * D) + t4;
 #pragma unroll
-          for (int s = 0; s < D / 16; ++s) { kb[n][s][0] = kr[8 * s]; kb[n][s][1] = kr[8 * s + 4]; }
+          for (int c = 0; c < D / 32; ++c) kq[n][c] = kr[4 * c];
         }
       }
     }
@@ -199,7 +263,10 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
 #pragma unroll
     for (int s = 0; s < D / 16; ++s) {
 #pragma unroll
-      for (int n = 0; n < 2; ++n) mma_bf16_16816(c[n], qa[s][0], 0u, qa[s][1], 0u, kb[n][s][0], kb[n][s][1]);
+      for (int n = 0; n < 2; ++n) {
+        const uint4 w = kq[n][s >> 1];
+        mma_bf16_16816(c[n], qa[s][0], 0u, qa[s][1], 0u, (s & 1) ? w.z : w.x, (s & 1) ? w.w : w.y);
+      }
     }
     if (g < G) {
 #pragma unroll
@@ -235,9 +302,9 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   __syncthreads();
   stamp(4);
 
-  // ---- pass 2: O = P.V, 16 keys per warp and iteration.  Dim-pair tile p covers dims [16p, 16p+16): the
-  // "even" n-tile holds dims 16p+2g, the "odd" one dims 16p+2g+1 (g = fragment column), both built from
-  // the same 32-bit V words.
+  // ---- pass 2: O = P.V, 16 keys per warp and iteration.  Lane (g, t4) reads 16 contiguous bytes (dims
+  // 64 pp + 8 g .. +7) of its four key rows; word w of that chunk feeds dim-pair tile p = 4 pp + w, whose "even"
+  // n-tile holds dim 64 pp + 8 n + 2 w in fragment column n and whose "odd" n-tile holds that dim + 1.
   float oe[D / 16][4], oo[D / 16][4];
 #pragma unroll
   for (int p = 0; p < D / 16; ++p) {
@@ -249,25 +316,34 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
     const uint32_t pa2 = g < G ? *reinterpret_cast<const uint32_t*>(sp + g * spad + k0 + 2 * t4 + 8) : 0u;
     const int r0 = min(k0 + 2 * t4, nkeys - 1), r1 = min(k0 + 2 * t4 + 1, nkeys - 1);
     const int r2 = min(k0 + 2 * t4 + 8, nkeys - 1), r3 = min(k0 + 2 * t4 + 9, nkeys - 1);
-    const uint32_t* v0 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r0) * D) + g;
-    const uint32_t* v1 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r1) * D) + g;
-    const uint32_t* v2 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r2) * D) + g;
-    const uint32_t* v3 = reinterpret_cast<const uint32_t*>(vbase + static_cast<long long>(r3) * D) + g;
+    const uint4* v0 = reinterpret_cast<const uint4*>(vbase + static_cast<long long>(r0) * D) + g;
+    const uint4* v1 = reinterpret_cast<const uint4*>(vbase + static_cast<long long>(r1) * D) + g;
+    const uint4* v2 = reinterpret_cast<const uint4*>(vbase + static_cast<long long>(r2) * D) + g;
+    const uint4* v3 = reinterpret_cast<const uint4*>(vbase + static_cast<long long>(r3) * D) + g;
     uint32_t w[D / 16][4];
 #pragma unroll
-    for (int p = 0; p < D / 16; ++p) { w[p][0] = v0[8 * p]; w[p][1] = v1[8 * p]; w[p][2] = v2[8 * p]; w[p][3] = v3[8 * p]; }
+    for (int pp = 0; pp < D / 64; ++pp) {       // 16 contiguous bytes (dims 64 pp + 8 g .. +7) of each of the four keys
+      const uint4 a0 = v0[8 * pp], a1 = v1[8 * pp], a2 = v2[8 * pp], a3 = v3[8 * pp];
+      w[4 * pp + 0][0] = a0.x; w[4 * pp + 0][1] = a1.x; w[4 * pp + 0][2] = a2.x; w[4 * pp + 0][3] = a3.x;
+      w[4 * pp + 1][0] = a0.y; w[4 * pp + 1][1] = a1.y; w[4 * pp + 1][2] = a2.y; w[4 * pp + 1][3] = a3.y;
+      w[4 * pp + 2][0] = a0.z; w[4 * pp + 2][1] = a1.z; w[4 * pp + 2][2] = a2.z; w[4 * pp + 2][3] = a3.z;
+      w[4 * pp + 3][0] = a0.w; w[4 * pp + 3][1] = a1.w; w[4 * pp + 3][2] = a2.w; w[4 * pp + 3][3] = a3.w;
+    }
 #pragma unroll
     for (int p = 0; p < D / 16; ++p) {
       mma_bf16_16816(oe[p], pa0, 0u, pa2, 0u, __byte_perm(w[p][0], w[p][1], 0x5410), __byte_perm(w[p][2], w[p][3], 0x5410));
       mma_bf16_16816(oo[p], pa0, 0u, pa2, 0u, __byte_perm(w[p][0], w[p][1], 0x7632), __byte_perm(w[p][2], w[p][3], 0x7632));
     }
   }
-  // accumulator (row g, cols 2t, 2t+1): even tile -> dims 16p+4t, 16p+4t+2; odd tile -> 16p+4t+1, 16p+4t+3
+  // tile p = 4 pp + w, fragment column n (= the g of the lane that loaded it) holds dims 64 pp + 8 n + 2 w (even
+  // tile) and + 1 (odd tile); this lane's accumulators are row g, columns 2 t4 and 2 t4 + 1
   if (g < G) {
 #pragma unroll
-    for (int p = 0; p < D / 16; ++p)
-      *reinterpret_cast<float4*>(red + (warp * kMaxG + g) * D + 16 * p + 4 * t4) =
-          make_float4(oe[p][0], oo[p][0], oe[p][1], oo[p][1]);
+    for (int p = 0; p < D / 16; ++p) {
+      const int d0 = 64 * (p >> 2) + 16 * t4 + 2 * (p & 3);
+      *reinterpret_cast<float2*>(red + (warp * kMaxG + g) * D + d0) = make_float2(oe[p][0], oo[p][0]);
+      *reinterpret_cast<float2*>(red + (warp * kMaxG + g) * D + d0 + 8) = make_float2(oe[p][1], oo[p][1]);
+    }
   }
   __syncthreads();
   stamp(5);
@@ -301,6 +377,7 @@ int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long sp
   const size_t smem = fixed + static_cast<size_t>(G) * spad * 6;
   MT_CHECK(smem <= 200 * 1024, "attn_decode: %d keys do not fit in shared memory", max_keys);
   auto kern = D == 128 ? attn_decode_kernel<128> : attn_decode_kernel<64>;
+  static const int exp_flags = [] { const char* e = getenv("MT_ATTN_EXP"); return e ? atoi(e) : 1; }();   // bit 0: no bulk L2 prefetch of the K/V rows (measured 1.3 % faster over 150 steps), bit 1: no early K tile
   static size_t smem_set[2] = {0, 0};
   size_t& cur = smem_set[D == 128];
   if (smem > 48 * 1024 && smem > cur) {
@@ -309,7 +386,7 @@ int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long sp
   }
   MT_CUDA(launch(kern, dim3(B * n_kv), dim3(kWarps * 32), smem, s, qkv, partials, nsplit, split_stride, q_gain, k_gain,
                  rope_cos, rope_sin, k_cache, v_cache, mask, mask_ld, out, n_heads, n_kv, pos_dev, pos_host, spad,
-                 max_seq, eps, 1.0f / sqrtf(static_cast<float>(D)), trace_slot(B * n_kv * 8)));
+                 max_seq, eps, 1.0f / sqrtf(static_cast<float>(D)), trace_slot(B * n_kv * 8), exp_flags));
   count_launch();
   return MT_OK;
 }

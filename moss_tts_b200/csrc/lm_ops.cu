@@ -70,27 +70,48 @@ int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf1
 // normed = gain * bf16(x_new * rsqrt(mean(x_new^2) + eps))
 // One block per token row.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(1024)
-add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
+// v[0..3] += sum over splits (in split order) of the float4 at p + s * stride.  Eight splits' loads are issued before
+// the first add: a rolled `for s` loop costs one L2 round trip per split.
+__device__ __forceinline__ void sum_splits4(const float* __restrict__ p, long long stride, int nsplit, float (&v)[4]) {
+  for (int s0 = 0; s0 < nsplit; s0 += 8) {
+    float4 t[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (s0 + u < nsplit) t[u] = __ldcg(reinterpret_cast<const float4*>(p + (s0 + u) * stride));
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (s0 + u < nsplit) { v[0] += t[u].x; v[1] += t[u].y; v[2] += t[u].z; v[3] += t[u].w; }
+  }
+}
+
+// 512 threads at most: a 1024-thread block at 64 registers takes the whole register file of an SM, so it could
+// neither start next to a resident GEMM CTA nor let the next GEMM's CTA start its early weight fetch beside it.
+__global__ void __launch_bounds__(512)
+add_rmsnorm_generic_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
                    const float* __restrict__ partials, int nsplit, long long split_stride,
                    bf16* __restrict__ x_out, const bf16* __restrict__ gain, bf16* __restrict__ normed, int H,
-                   float eps) {
+                   float eps, unsigned long long* __restrict__ trace) {
   extern __shared__ float srow[];            // H floats + 33 scratch
   float* scratch = srow + H;
   const long long m = blockIdx.x;
   float ss = 0.f;
+  auto stamp = [&](int e) {                  // timeline instrumentation (mt_debug_set_trace; null in product runs)
+    if (trace && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      trace[blockIdx.x * 8 + e] = t;
+    }
+  };
+  stamp(0);
   pdl_trigger();
   pdl_wait();
+  stamp(1);
   // 4 elements per thread and iteration: every split's float4 is an independent 16-byte load
+#pragma unroll 2
   for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     if (partials) {
-      const float* p = partials + m * H + c;
-#pragma unroll 4
-      for (int s = 0; s < nsplit; ++s) {
-        const float4 t = *reinterpret_cast<const float4*>(p + s * split_stride);
-        v[0] += t.x; v[1] += t.y; v[2] += t.z; v[3] += t.w;
-      }
+      sum_splits4(partials + m * H + c, split_stride, nsplit, v);
 #pragma unroll
       for (int j = 0; j < 4; ++j) v[j] = rbf(v[j]);
     } else if (delta) {
@@ -109,7 +130,9 @@ add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ d
     *reinterpret_cast<float4*>(srow + c) = make_float4(v[0], v[1], v[2], v[3]);
     ss += v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3];
   }
+  stamp(2);
   ss = block_sum(ss, scratch);
+  stamp(3);
   const float inv = rsqrtf(ss / static_cast<float>(H) + eps);
   if (normed) {
     for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
@@ -121,6 +144,98 @@ add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ d
       *reinterpret_cast<uint2*>(normed + m * H + c) = o;
     }
   }
+  stamp(4);
+}
+
+// Same operation for H <= 2 * 4 * blockDim.x (every LM shape here): each thread owns at most two float4 columns and
+// issues EVERY global load it will need (split-K partials of both columns, residual, gain) before the first use.
+// The generic kernel above pays four dependent L2 round trips (partials, residual, partials, residual) plus one for
+// the gain; this one pays one.
+__global__ void __launch_bounds__(512)
+add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
+                   const float* __restrict__ partials, int nsplit, long long split_stride,
+                   bf16* __restrict__ x_out, const bf16* __restrict__ gain, bf16* __restrict__ normed, int H,
+                   float eps, unsigned long long* __restrict__ trace) {
+  __shared__ float scratch[40];
+  const long long m = blockIdx.x;
+  auto stamp = [&](int e) {                  // timeline instrumentation (mt_debug_set_trace; null in product runs)
+    if (trace && threadIdx.x == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+      trace[blockIdx.x * 8 + e] = t;
+    }
+  };
+  stamp(0);
+  pdl_trigger();
+  pdl_wait();
+  stamp(1);
+  constexpr int kIt = 2, kBatch = 8;
+  float4 t[kIt][kBatch];
+  uint2 rr[kIt], dd[kIt], gg[kIt];
+  bool ok[kIt];
+#pragma unroll
+  for (int it = 0; it < kIt; ++it) {
+    const int c = (threadIdx.x + it * blockDim.x) * 4;
+    ok[it] = c < H;
+    rr[it] = dd[it] = gg[it] = make_uint2(0u, 0u);
+    if (ok[it]) {
+      if (partials) {
+#pragma unroll
+        for (int u = 0; u < kBatch; ++u)
+          if (u < nsplit) t[it][u] = __ldcg(reinterpret_cast<const float4*>(partials + u * split_stride + m * H + c));
+      } else if (delta) {
+        dd[it] = *reinterpret_cast<const uint2*>(delta + m * H + c);
+      }
+      if (residual) rr[it] = *reinterpret_cast<const uint2*>(residual + m * H + c);
+      if (normed) gg[it] = *reinterpret_cast<const uint2*>(gain + c);
+    }
+  }
+  float v[kIt][4];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < kIt; ++it) {
+    v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
+    if (!ok[it]) continue;
+    const int c = (threadIdx.x + it * blockDim.x) * 4;
+    if (partials) {
+#pragma unroll
+      for (int u = 0; u < kBatch; ++u)
+        if (u < nsplit) { v[it][0] += t[it][u].x; v[it][1] += t[it][u].y; v[it][2] += t[it][u].z; v[it][3] += t[it][u].w; }
+      for (int s = kBatch; s < nsplit; ++s) {          // more than eight splits: rare, plain loop
+        const float4 x = __ldcg(reinterpret_cast<const float4*>(partials + s * split_stride + m * H + c));
+        v[it][0] += x.x; v[it][1] += x.y; v[it][2] += x.z; v[it][3] += x.w;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[it][j] = rbf(v[it][j]);
+    } else if (delta) {
+      v[it][0] = bits_lo(dd[it].x); v[it][1] = bits_hi(dd[it].x); v[it][2] = bits_lo(dd[it].y); v[it][3] = bits_hi(dd[it].y);
+    }
+    if (residual) {
+      v[it][0] = rbf(bits_lo(rr[it].x) + v[it][0]); v[it][1] = rbf(bits_hi(rr[it].x) + v[it][1]);
+      v[it][2] = rbf(bits_lo(rr[it].y) + v[it][2]); v[it][3] = rbf(bits_hi(rr[it].y) + v[it][3]);
+    }
+    if (x_out) {
+      uint2 o; o.x = pack_bf16(v[it][0], v[it][1]); o.y = pack_bf16(v[it][2], v[it][3]);
+      *reinterpret_cast<uint2*>(x_out + m * H + c) = o;
+    }
+    ss += v[it][0] * v[it][0] + v[it][1] * v[it][1] + v[it][2] * v[it][2] + v[it][3] * v[it][3];
+  }
+  stamp(2);
+  ss = block_sum(ss, scratch);
+  stamp(3);
+  const float inv = rsqrtf(ss / static_cast<float>(H) + eps);
+  if (normed) {
+#pragma unroll
+    for (int it = 0; it < kIt; ++it) {
+      if (!ok[it]) continue;
+      const int c = (threadIdx.x + it * blockDim.x) * 4;
+      uint2 o;
+      o.x = pack_bf16(bits_lo(gg[it].x) * rbf(v[it][0] * inv), bits_hi(gg[it].x) * rbf(v[it][1] * inv));
+      o.y = pack_bf16(bits_lo(gg[it].y) * rbf(v[it][2] * inv), bits_hi(gg[it].y) * rbf(v[it][3] * inv));
+      *reinterpret_cast<uint2*>(normed + m * H + c) = o;
+    }
+  }
+  stamp(4);
 }
 
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
@@ -128,9 +243,14 @@ int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, 
   MT_CHECK(H % 4 == 0, "hidden size must be a multiple of 4");
   const size_t smem = (H + 40) * sizeof(float);
   int threads = ((H / 4 + 31) / 32) * 32;
-  if (threads > 1024) threads = 1024;
-  MT_CUDA(launch(add_rmsnorm_kernel, dim3(M), dim3(threads), smem, s, residual, delta, partials, nsplit, split_stride,
-                 x_out, gain, normed, H, eps));
+  if (threads > 512) threads = 512;
+  if (H <= 2 * 4 * threads) {
+    MT_CUDA(launch(add_rmsnorm_kernel, dim3(M), dim3(threads), 0, s, residual, delta, partials, nsplit, split_stride,
+                   x_out, gain, normed, H, eps, M <= 1024 ? trace_slot(M * 8) : nullptr));
+  } else {
+    MT_CUDA(launch(add_rmsnorm_generic_kernel, dim3(M), dim3(threads), smem, s, residual, delta, partials, nsplit,
+                   split_stride, x_out, gain, normed, H, eps, static_cast<unsigned long long*>(nullptr)));
+  }
   count_launch();
   return MT_OK;
 }
@@ -414,12 +534,20 @@ __global__ void silu_mul_kernel(const bf16* __restrict__ gu, const float* __rest
     if (partials) {
       float a[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
       const float* p = partials + m * 2 * I + i;
-#pragma unroll 4
-      for (int s = 0; s < nsplit; ++s) {
-        const float4 x = *reinterpret_cast<const float4*>(p + s * split_stride);
-        const float4 y = *reinterpret_cast<const float4*>(p + s * split_stride + I);
-        a[0] += x.x; a[1] += x.y; a[2] += x.z; a[3] += x.w;
-        c[0] += y.x; c[1] += y.y; c[2] += y.z; c[3] += y.w;
+      for (int s0 = 0; s0 < nsplit; s0 += 4) {        // gate and up of four splits in flight together
+        float4 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (s0 + u < nsplit) {
+            x[u] = *reinterpret_cast<const float4*>(p + (s0 + u) * split_stride);
+            y[u] = *reinterpret_cast<const float4*>(p + (s0 + u) * split_stride + I);
+          }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (s0 + u < nsplit) {
+            a[0] += x[u].x; a[1] += x[u].y; a[2] += x[u].z; a[3] += x[u].w;
+            c[0] += y[u].x; c[1] += y[u].y; c[2] += y[u].z; c[3] += y[u].w;
+          }
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) { g[j] = rbf(a[j]); u[j] = rbf(c[j]); }

@@ -42,8 +42,9 @@ def main():
     ids, mask = ids.to(dev), mask.to(dev)
     kw = dict(max_new_tokens=args.steps, text_temperature=0, audio_temperature=0, record_step_times=True)
     model.generate(ids, mask, **kw)                      # warm
-    GW, AW = 148 * 8, B * cfg.num_kv_heads * 8
-    step_words = cfg.num_layers * (4 * GW + AW) + 2 * GW
+    GW, AW, NW = 148 * 8, B * cfg.num_kv_heads * 8, B * 8
+    # launch order of a step: add_rmsnorm | per layer: qkv, attention, o, add_rmsnorm, gate|up, (silu), down, add_rmsnorm | heads
+    step_words = NW + cfg.num_layers * (4 * GW + AW + 2 * NW) + 2 * GW
     buf = torch.zeros(2 * GW + 2 * step_words + 1024, dtype=torch.int64, device=dev)
     lib = L.lib()
     lib.mt_debug_set_trace.restype = C.c_longlong
@@ -54,13 +55,23 @@ def main():
     ms = model.last_step_ms
     print(f"decode ms/step (median of last 20): {sorted(ms[-20:])[10]:.3f}; trace words used {used} (expected {2 * GW + 2 * step_words})")
     raw = buf[:used].cpu().numpy().astype(np.int64)[-step_words:]      # the captured step = last replay
-    gemm, attn = [], []
-    off = 0
+    gemm, attn, norm = [], [], []
+    off = NW                                              # the step's first add_rmsnorm (after the embedding)
+
+    def take(n, rows):
+        nonlocal off
+        a = raw[off:off + n].reshape(rows, 8)
+        off += n
+        return a
+
     for l in range(cfg.num_layers):
-        gemm.append(raw[off:off + GW].reshape(148, 8)); off += GW
-        attn.append(raw[off:off + AW].reshape(-1, 8)); off += AW
-        for _ in range(3):
-            gemm.append(raw[off:off + GW].reshape(148, 8)); off += GW
+        gemm.append(take(GW, 148))                        # qkv
+        attn.append(take(AW, -1))
+        gemm.append(take(GW, 148))                        # o
+        norm.append(take(NW, B))                          # + residual, post-attention norm
+        gemm.append(take(GW, 148))                        # gate|up
+        gemm.append(take(GW, 148))                        # down
+        norm.append(take(NW, B))                          # + residual, next input norm
     names = ["qkv", "o", "gate|up", "down"]
     nbytes = {"qkv": 50.3e6, "o": 33.6e6, "gate|up": 201.3e6, "down": 100.7e6}
     EXIT = 2
@@ -92,7 +103,7 @@ def main():
         arows.append(dict(
             entry_med=(np.median(at[:, 0]) - q_end) / 1e3, entry_max=(at[:, 0].max() - q_end) / 1e3,
             wait_med=(np.median(at[:, 1]) - q_end) / 1e3, wait_max=(at[:, 1].max() - q_end) / 1e3,
-            prep=np.median(at[:, 2] - at[:, 1]) / 1e3, scores=np.median(at[:, 3] - at[:, 2]) / 1e3,
+            inputs=np.median(at[:, 7] - at[:, 1]) / 1e3, prep=np.median(at[:, 2] - at[:, 1]) / 1e3, scores=np.median(at[:, 3] - at[:, 2]) / 1e3,
             softmax=np.median(at[:, 4] - at[:, 3]) / 1e3, pv=np.median(at[:, 5] - at[:, 4]) / 1e3,
             write=np.median(at[:, 6] - at[:, 5]) / 1e3, block_total=np.median(at[:, 6] - at[:, 1]) / 1e3,
             end_max=(at[:, 6].max() - q_end) / 1e3, end_med=(np.median(at[:, 6]) - q_end) / 1e3))
@@ -110,6 +121,20 @@ def main():
     print("| " + " | ".join(arows[0].keys()) + " |")
     print("|" + "---:|" * len(arows[0]))
     print("| " + " | ".join(f"{np.mean([x[k] for x in arows]):.2f}" for k in arows[0]) + " |")
+    # add_rmsnorm after the o projection (index 2l) and after the down projection (2l + 1)
+    nrows = []
+    for l in range(1, cfg.num_layers):
+        for which, gi in ((0, 4 * l + 1), (1, 4 * l + 3)):
+            nt = norm[2 * l + which]
+            g_end = ev(gemm[gi], EXIT, np.max)
+            nrows.append(dict(entry_med=(np.median(nt[:, 0]) - g_end) / 1e3, wait_med=(np.median(nt[:, 1]) - g_end) / 1e3,
+                              probe1=np.median(nt[:, 5] - nt[:, 1]) / 1e3, probe2=np.median(nt[:, 6] - nt[:, 5]) / 1e3,
+                              loads=np.median(nt[:, 2] - nt[:, 1]) / 1e3, block_sum=np.median(nt[:, 3] - nt[:, 2]) / 1e3,
+                              normalise=np.median(nt[:, 4] - nt[:, 3]) / 1e3, end_max=(nt[:, 4].max() - g_end) / 1e3))
+    print("\nadd_rmsnorm blocks (microseconds; entry/wait/end measured from the last CTA exit of the producing GEMM):")
+    print("| " + " | ".join(nrows[0].keys()) + " |")
+    print("|" + "---:|" * len(nrows[0]))
+    print("| " + " | ".join(f"{np.mean([x[k] for x in nrows]):.2f}" for k in nrows[0]) + " |")
 
 
 if __name__ == "__main__":
