@@ -43,7 +43,7 @@ __device__ __forceinline__ int vis_lo(int t, int T, int context, int chunk) {
 
 __global__ void __launch_bounds__(kWarps * 32)
 codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out, int T, int heads, int context,
-                          int chunk, float scale) {
+                          int chunk, float scale, const float4* __restrict__ rope) {
   __shared__ __align__(16) uint32_t sk[kK * kPitch];
   __shared__ __align__(16) uint32_t sv[kK * kPitch];
   pdl_trigger();
@@ -58,7 +58,13 @@ codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out
   for (int i = threadIdx.x; i < kQ * kD / 4; i += kWarps * 32) {
     const int r = i / (kD / 4), c = i % (kD / 4);
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (q0 + r < T) v = reinterpret_cast<const float4*>(qkv + (tok0 + q0 + r) * 3 * d + h * kD)[c];
+    if (q0 + r < T) {
+      v = reinterpret_cast<const float4*>(qkv + (tok0 + q0 + r) * 3 * d + h * kD)[c];
+      if (rope) {       // interleaved-pair RoPE (:255-300) applied on the way in: (cos, sin) of pairs 2c and 2c + 1
+        const float4 cs = rope[static_cast<long long>(q0 + r) * (kD / 4) + c];
+        v = make_float4(v.x * cs.x - v.y * cs.y, v.x * cs.y + v.y * cs.x, v.z * cs.z - v.w * cs.w, v.z * cs.w + v.w * cs.z);
+      }
+    }
     uint32_t* dst = sk + r * kPitch + 4 * c;
     dst[0] = to_tf32(v.x * scale); dst[1] = to_tf32(v.y * scale); dst[2] = to_tf32(v.z * scale); dst[3] = to_tf32(v.w * scale);
   }
@@ -93,6 +99,10 @@ codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out
         const float* base = qkv + (tok0 + k0 + r) * 3 * d + h * kD;
         kv = reinterpret_cast<const float4*>(base + d)[c];
         vv = reinterpret_cast<const float4*>(base + 2 * d)[c];
+        if (rope) {
+          const float4 cs = rope[static_cast<long long>(k0 + r) * (kD / 4) + c];
+          kv = make_float4(kv.x * cs.x - kv.y * cs.y, kv.x * cs.y + kv.y * cs.x, kv.z * cs.z - kv.w * cs.w, kv.z * cs.w + kv.w * cs.z);
+        }
       }
       *reinterpret_cast<uint4*>(sk + r * kPitch + 4 * c) = make_uint4(to_tf32(kv.x), to_tf32(kv.y), to_tf32(kv.z), to_tf32(kv.w));
       *reinterpret_cast<uint4*>(sv + r * kPitch + 4 * c) = make_uint4(to_tf32(vv.x), to_tf32(vv.y), to_tf32(vv.z), to_tf32(vv.w));
@@ -168,11 +178,11 @@ codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out
 }  // namespace
 
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
-                       cudaStream_t s) {
+                       cudaStream_t s, const float* rope_table) {
   if (hd != kD) return fail(MT_ERR_UNSUPPORTED, "codec attention supports head_dim 64 only (got %d)", hd);
   dim3 grid(cdiv(T, kQ), heads, B);
   MT_CUDA(launch(codec_attention_tc_kernel, grid, dim3(kWarps * 32), 0, s, qkv, out, T, heads, context, chunk,
-                 1.0f / sqrtf(static_cast<float>(hd))));
+                 1.0f / sqrtf(static_cast<float>(hd)), reinterpret_cast<const float4*>(rope_table)));
   count_launch();
   return MT_OK;
 }

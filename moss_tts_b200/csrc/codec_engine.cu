@@ -124,15 +124,22 @@ static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T,
     if (h->w.input_proj[st]) MT_TRY(codec_linear(in, M, c.input_dim[st], h->w.input_proj[st], d, x, d, 0, nullptr, nullptr, s));
     else MT_CUDA(cudaMemcpyAsync(x, in, M * d * sizeof(float), cudaMemcpyDeviceToDevice, s));
     const int chunk = chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0;
+    // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel (+ the separate RoPE pass) as a cross-check of the TF32 one
+    static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
+    // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
+    const bool table_fits = static_cast<long long>(Ts) * 64 <= ys * nb;
+    if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
     for (int l = 0; l < c.num_layers[st]; ++l) {
       const mt_codec_layer& L = h->layers[st][l];
       MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s));
       MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s));
-      MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
-      // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel as a cross-check of the TF32 tensor-core one
-      static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
-      if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
-      else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      if (simt_attn || !table_fits) {
+        MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
+        if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+        else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      } else {
+        MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
+      }
       MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s));
       MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s));
       MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s));

@@ -115,7 +115,61 @@ __global__ void layernorm_kernel(const float* __restrict__ x, const float* __res
   const float rstd = rsqrtf(block_sum(ss, scratch) / d + eps);
   for (int c = threadIdx.x; c < d; c += blockDim.x) out[m * d + c] = (srow[c] - mean) * rstd * w[c] + b[c];
 }
+// Warp-per-token form for d <= 32 * 4 * kLnVec (the codec's 768 / 1280): the row lives in registers (float4 loads, all
+// issued before the first use), mean / variance by warp shuffles, no shared memory and no block barriers; 8 tokens per
+// block.  Same two-pass fp32 formula as above (the summation order differs).
+constexpr int kLnVec = 10;
+template <int NV>
+__global__ void __launch_bounds__(256)
+layernorm_warp_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                      float* __restrict__ out, long long M, int d, float eps) {
+  const int lane = threadIdx.x & 31;
+  const long long m = blockIdx.x * 8ll + (threadIdx.x >> 5);
+  pdl_trigger();
+  pdl_wait();
+  if (m >= M) return;
+  const int nvec = d / 4;
+  const float4* xr = reinterpret_cast<const float4*>(x + m * d);
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    v[i] = c < nvec ? xr[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int i = 0; i < NV; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(s) / d;
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    if (lane + 32 * i < nvec) {
+      const float a = v[i].x - mean, bb = v[i].y - mean, c2 = v[i].z - mean, e = v[i].w - mean;
+      ss += (a * a + bb * bb) + (c2 * c2 + e * e);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(ss) / d + eps);
+  float4* orow = reinterpret_cast<float4*>(out + m * d);
+  const float4* w4 = reinterpret_cast<const float4*>(w);
+  const float4* b4 = reinterpret_cast<const float4*>(b);
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nvec) {
+      const float4 ww = w4[c], bb = b4[c];
+      orow[c] = make_float4((v[i].x - mean) * rstd * ww.x + bb.x, (v[i].y - mean) * rstd * ww.y + bb.y,
+                            (v[i].z - mean) * rstd * ww.z + bb.z, (v[i].w - mean) * rstd * ww.w + bb.w);
+    }
+  }
+}
 int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s) {
+  if (d % 4 == 0 && d <= 32 * 4 * kLnVec) {
+    const unsigned blocks = static_cast<unsigned>((M + 7) / 8);
+    if (d <= 32 * 4 * 6) MT_CUDA(launch(layernorm_warp_kernel<6>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f));
+    else MT_CUDA(launch(layernorm_warp_kernel<kLnVec>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f));
+    count_launch();
+    return MT_OK;
+  }
   layernorm_kernel<<<static_cast<unsigned>(M), 256, (d + 40) * sizeof(float), s>>>(x, w, b, out, d, 1e-5f);
   count_launch();
   MT_LAUNCH_CHECK();
@@ -144,6 +198,24 @@ __global__ void codec_rope_kernel(float* __restrict__ qkv, long long M, int T, i
     *p = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
   }
 }
+__global__ void codec_rope_table_kernel(float2* __restrict__ table, int T, int hd, float log_period) {
+  const int total = T * (hd / 2);
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int t = idx / (hd / 2), j = idx % (hd / 2);
+    const float freq = expf(static_cast<float>(j) * (-log_period * 2.f / hd));     // same expressions as codec_rope_kernel
+    float sn, cs;
+    sincosf(freq * static_cast<float>(t), &sn, &cs);
+    table[idx] = make_float2(cs, sn);
+  }
+}
+int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s) {
+  const int total = T * (hd / 2);
+  codec_rope_table_kernel<<<(total + 255) / 256, 256, 0, s>>>(reinterpret_cast<float2*>(table), T, hd, logf(max_period));
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
 int codec_rope(float* qkv, long long M, int T, int d, int hd, float max_period, cudaStream_t s) {
   const long long total = M * d;
   int blocks = static_cast<int>(cdivll(total, 256));

@@ -15,7 +15,10 @@ int codec_rope(float* qkv, long long M, int T, int d, int hd, float max_period, 
 int codec_attention(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                     cudaStream_t s);
 // tensor-core (TF32 mma) version of codec_attention: the product path (codec_attn.cu)
+// (cos, sin) of every (position, pair) as codec_rope computes them: table[t * hd/2 + j] = (cos, sin)(t * freq_j)
+int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s);
+// rope_table != nullptr: q and k are rotated while they are staged (no separate codec_rope pass over qkv)
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
-                       cudaStream_t s);
+                       cudaStream_t s, const float* rope_table = nullptr);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
 }  // namespace mt

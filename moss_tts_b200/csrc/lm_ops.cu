@@ -238,13 +238,73 @@ add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ d
   stamp(4);
 }
 
+// Prefill form (finished bf16 delta, thousands of rows): one 256-thread block per row, 16 elements per thread
+// (two 16-byte loads of delta and of the residual, all issued before the first use), results kept in registers
+// between the two passes.  Needs H <= 4096; larger rows take the generic kernel.
+__global__ void __launch_bounds__(256)
+add_rmsnorm_rows_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta, bf16* __restrict__ x_out,
+                        const bf16* __restrict__ gain, bf16* __restrict__ normed, int H, float eps) {
+  __shared__ float scratch[40];
+  const long long m = blockIdx.x;
+  pdl_trigger();
+  pdl_wait();
+  uint4 dd[2], rr[2], gg[2];
+  bool ok[2];
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const int c = (threadIdx.x + it * 256) * 8;
+    ok[it] = c < H;
+    dd[it] = rr[it] = gg[it] = make_uint4(0u, 0u, 0u, 0u);
+    if (ok[it]) {
+      dd[it] = *reinterpret_cast<const uint4*>(delta + m * H + c);
+      if (residual) rr[it] = *reinterpret_cast<const uint4*>(residual + m * H + c);
+      if (normed) gg[it] = *reinterpret_cast<const uint4*>(gain + c);
+    }
+  }
+  float v[2][8];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {
+    const uint32_t dw[4] = {dd[it].x, dd[it].y, dd[it].z, dd[it].w}, rw[4] = {rr[it].x, rr[it].y, rr[it].z, rr[it].w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float a = bits_lo(dw[j]), b = bits_hi(dw[j]);
+      if (residual) { a = rbf(bits_lo(rw[j]) + a); b = rbf(bits_hi(rw[j]) + b); }
+      v[it][2 * j] = a; v[it][2 * j + 1] = b;
+      ss += a * a + b * b;
+    }
+    if (ok[it] && x_out) {
+      const int c = (threadIdx.x + it * 256) * 8;
+      *reinterpret_cast<uint4*>(x_out + m * H + c) = make_uint4(pack_bf16(v[it][0], v[it][1]), pack_bf16(v[it][2], v[it][3]),
+                                                               pack_bf16(v[it][4], v[it][5]), pack_bf16(v[it][6], v[it][7]));
+    }
+  }
+  ss = block_sum(ss, scratch);
+  const float inv = rsqrtf(ss / static_cast<float>(H) + eps);
+  if (normed) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      if (!ok[it]) continue;
+      const int c = (threadIdx.x + it * 256) * 8;
+      const uint32_t gw[4] = {gg[it].x, gg[it].y, gg[it].z, gg[it].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        o[j] = pack_bf16(bits_lo(gw[j]) * rbf(v[it][2 * j] * inv), bits_hi(gw[j]) * rbf(v[it][2 * j + 1] * inv));
+      *reinterpret_cast<uint4*>(normed + m * H + c) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
                 bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s) {
   MT_CHECK(H % 4 == 0, "hidden size must be a multiple of 4");
   const size_t smem = (H + 40) * sizeof(float);
   int threads = ((H / 4 + 31) / 32) * 32;
   if (threads > 512) threads = 512;
-  if (H <= 2 * 4 * threads) {
+  if (!partials && delta && M > 256 && H % 8 == 0 && H <= 4096) {
+    MT_CUDA(launch(add_rmsnorm_rows_kernel, dim3(M), dim3(256), 0, s, residual, delta, x_out, gain, normed, H, eps));
+  } else if (H <= 2 * 4 * threads) {
     MT_CUDA(launch(add_rmsnorm_kernel, dim3(M), dim3(threads), 0, s, residual, delta, partials, nsplit, split_stride,
                    x_out, gain, normed, H, eps, M <= 1024 ? trace_slot(M * 8) : nullptr));
   } else {
@@ -506,6 +566,8 @@ static int launch_attention(const bf16* q, const bf16* k_cache, const bf16* v_ca
 int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld,
               bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
               int max_keys, int max_seq, cudaStream_t s) {
+  if (attention_tc_supported(n_heads, n_kv, D))
+    return attention_tc(q, k_cache, v_cache, mask, mask_ld, out, B, T, n_heads, n_kv, D, past_len, past_len_dev, max_seq, s);
   const int G = n_heads / n_kv;
 #define MT_ATT(DD, GG)                                                                                   \
   if (D == DD && G == GG)                                                                                \
@@ -530,49 +592,86 @@ __global__ void silu_mul_kernel(const bf16* __restrict__ gu, const float* __rest
        idx += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long m = idx / I4;
     const int i = static_cast<int>(idx % I4) * 4;
-    float g[4], u[4];
-    if (partials) {
-      float a[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
-      const float* p = partials + m * 2 * I + i;
-      for (int s0 = 0; s0 < nsplit; s0 += 4) {        // gate and up of four splits in flight together
-        float4 x[4], y[4];
+    float a[4] = {0.f, 0.f, 0.f, 0.f}, c[4] = {0.f, 0.f, 0.f, 0.f};
+    const float* p = partials + m * 2 * I + i;
+    for (int s0 = 0; s0 < nsplit; s0 += 4) {        // gate and up of four splits in flight together
+      float4 x[4], y[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (s0 + u < nsplit) {
-            x[u] = *reinterpret_cast<const float4*>(p + (s0 + u) * split_stride);
-            y[u] = *reinterpret_cast<const float4*>(p + (s0 + u) * split_stride + I);
-          }
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < nsplit) {
+          x[u] = __ldcg(reinterpret_cast<const float4*>(p + (s0 + u) * split_stride));
+          y[u] = __ldcg(reinterpret_cast<const float4*>(p + (s0 + u) * split_stride + I));
+        }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (s0 + u < nsplit) {
-            a[0] += x[u].x; a[1] += x[u].y; a[2] += x[u].z; a[3] += x[u].w;
-            c[0] += y[u].x; c[1] += y[u].y; c[2] += y[u].z; c[3] += y[u].w;
-          }
-      }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { g[j] = rbf(a[j]); u[j] = rbf(c[j]); }
-    } else {
-      const uint2 x = *reinterpret_cast<const uint2*>(gu + m * 2 * I + i);
-      const uint2 y = *reinterpret_cast<const uint2*>(gu + m * 2 * I + I + i);
-      g[0] = bits_lo(x.x); g[1] = bits_hi(x.x); g[2] = bits_lo(x.y); g[3] = bits_hi(x.y);
-      u[0] = bits_lo(y.x); u[1] = bits_hi(y.x); u[2] = bits_lo(y.y); u[3] = bits_hi(y.y);
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < nsplit) {
+          a[0] += x[u].x; a[1] += x[u].y; a[2] += x[u].z; a[3] += x[u].w;
+          c[0] += y[u].x; c[1] += y[u].y; c[2] += y[u].z; c[3] += y[u].w;
+        }
     }
     float r[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) r[j] = rbf(g[j] / (1.f + expf(-g[j]))) * u[j];
+    for (int j = 0; j < 4; ++j) {
+      const float g = rbf(a[j]), u = rbf(c[j]);
+      r[j] = rbf(g / (1.f + expf(-g))) * u;
+    }
     uint2 o; o.x = pack_bf16(r[0], r[1]); o.y = pack_bf16(r[2], r[3]);
     *reinterpret_cast<uint2*>(act + m * I + i) = o;
   }
 }
 
+// Prefill form (finished bf16 gate|up): a pure streaming op, 8 outputs per thread and iteration, two iterations'
+// 16-byte loads in flight (the one-uint2-per-iteration loop ran at a quarter of the HBM rate).
+__global__ void silu_mul_bf16_kernel(const bf16* __restrict__ gu, bf16* __restrict__ act, long long M, int I) {
+  const int I8 = I / 8;
+  const long long total = M * I8;
+  pdl_trigger();
+  pdl_wait();
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long idx0 = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx0 < total; idx0 += 2 * stride) {
+    uint4 x[2], y[2];
+    long long m[2]; int i[2]; bool ok[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long idx = idx0 + u * stride;
+      ok[u] = idx < total;
+      m[u] = ok[u] ? idx / I8 : 0;
+      i[u] = ok[u] ? static_cast<int>(idx % I8) * 8 : 0;
+      if (ok[u]) {
+        x[u] = *reinterpret_cast<const uint4*>(gu + m[u] * 2 * I + i[u]);
+        y[u] = *reinterpret_cast<const uint4*>(gu + m[u] * 2 * I + I + i[u]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!ok[u]) continue;
+      const uint32_t gx[4] = {x[u].x, x[u].y, x[u].z, x[u].w}, ux[4] = {y[u].x, y[u].y, y[u].z, y[u].w};
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float g0 = bits_lo(gx[j]), g1 = bits_hi(gx[j]);
+        o[j] = pack_bf16(rbf(g0 / (1.f + expf(-g0))) * bits_lo(ux[j]), rbf(g1 / (1.f + expf(-g1))) * bits_hi(ux[j]));
+      }
+      *reinterpret_cast<uint4*>(act + m[u] * I + i[u]) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
 int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
              cudaStream_t s) {
-  MT_CHECK(I % 4 == 0, "intermediate size must be a multiple of 4");
-  const long long total = static_cast<long long>(M) * (I / 4);
-  int blocks = static_cast<int>(cdivll(total, 256));
-  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  MT_CUDA(launch(silu_mul_kernel, dim3(blocks), dim3(256), 0, s, gu, partials, nsplit, split_stride, act,
-                 static_cast<long long>(M), I));
+  MT_CHECK(I % 8 == 0, "intermediate size must be a multiple of 8");
+  if (partials) {
+    const long long total = static_cast<long long>(M) * (I / 4);
+    int blocks = static_cast<int>(cdivll(total, 256));
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    MT_CUDA(launch(silu_mul_kernel, dim3(blocks), dim3(256), 0, s, gu, partials, nsplit, split_stride, act,
+                   static_cast<long long>(M), I));
+  } else {
+    const long long total = static_cast<long long>(M) * (I / 8);
+    int blocks = static_cast<int>(cdivll(total, 512));
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    MT_CUDA(launch(silu_mul_bf16_kernel, dim3(blocks), dim3(256), 0, s, gu, act, static_cast<long long>(M), I));
+  }
   count_launch();
   return MT_OK;
 }

@@ -17,6 +17,12 @@ int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split
 int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld,
               bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
               int max_keys, int max_seq, cudaStream_t s);
+// tensor-core two-pass form of `attention` for any T and any number of keys (lm_attn_prefill.cu); `attention`
+// dispatches to it when the head layout is supported (MT_OLD_PREFILL_ATTN=1 keeps the SIMT kernel for A/B runs)
+bool attention_tc_supported(int n_heads, int n_kv, int D);
+int attention_tc(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld, bf16* out,
+                 int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev, int max_seq,
+                 cudaStream_t s);
 // decode (T = 1): qkv_post + attention fused, one warp per (row, kv head), mma.sync tensor cores (lm_attn.cu)
 bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys);
 int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
