@@ -107,7 +107,18 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
 #define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
                    h->x, M, H, n_vq_embed < 0 ? c.n_vq : n_vq_embed, c.audio_head_size, c.vocab_size, s, 1 + c.n_vq));
-  MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s));
+  // decode: the norm in front of a layer's qkv GEMM also asks L2 for that layer's K/V rows (KvPrefetch)
+  static const bool kv_pf = [] { const char* e = getenv("MT_NO_KV_PREFETCH"); return !(e && e[0] == '1'); }();
+  KvPrefetch kvp;
+  auto kv_job = [&](int l) -> const KvPrefetch* {
+    if (!fused_attn || !kv_pf || !past_len_dev || l >= c.num_layers) return nullptr;
+    kvp.k = h->k_cache + l * layer_stride; kvp.v = h->v_cache + l * layer_stride;
+    kvp.item_stride = static_cast<long long>(c.max_seq) * D; kvp.items = B * c.num_kv_heads; kvp.row_bytes = D * 2;
+    kvp.pos_dev = past_len_dev;
+    return &kvp;
+  };
+  MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s,
+                     kv_job(0)));
   for (int l = 0; l < c.num_layers; ++l) {
     bf16* kc = h->k_cache + l * layer_stride;
     bf16* vc = h->v_cache + l * layer_stride;
@@ -138,7 +149,7 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
     MT_GEMM_(lm_linear(h, h->act, M, I, h->w_down[l], &h->tm_down[l], H, h->delta, &sp, s));
     const void* next_gain = l + 1 < c.num_layers ? h->ln_in[l + 1] : h->w.final_norm;
     MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
-                       reinterpret_cast<const bf16*>(next_gain), h->xn, M, H, eps, s));
+                       reinterpret_cast<const bf16*>(next_gain), h->xn, M, H, eps, s, kv_job(l + 1)));
   }
 #undef MT_GEMM_
 #undef MT_SMALL_
