@@ -190,6 +190,16 @@ def time_dominant_kernel(model, batch, iters=3):
     return ms, alg
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel's launch, from the committed `ncu --set full`
+    capture of this round (profiles/ncu_traffic.json, written by scripts/gpu_job_profile.sh); None if absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return float(json.load(f)["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def run_ours(args):
     from moss_tts_b200 import _lib as L
     from moss_tts_b200.config import LMConfig, CodecConfig
@@ -309,7 +319,7 @@ def run_ours(args):
         "decode_ms_per_step": dec_med, "prefill_ms": prefill_ms, "codec_ms": codec_ms,
         "decode_weight_stream_gbs": weight_bytes / (dec_med * 1e-3) / 1e9 if dec_med == dec_med else None,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                     "traffic": None, "kernel": "gemm_tc_kernel<BN=64> gate|up decode GEMM (M=%d,N=%d,K=%d) + its split-K reduce" % (B, 2 * cfg.intermediate_size, cfg.hidden_size),
+                     "traffic": ncu_traffic(), "kernel": "gemm_dec_kernel<BN=64,bf16> gate|up decode GEMM (M=%d,N=%d,K=%d) through mt_gemm, incl. its split-K reduce kernel" % (B, 2 * cfg.intermediate_size, cfg.hidden_size),
                      "ms_per_launch": k_ms, "algorithmic_bytes": k_bytes, "peak_source": src},
         "clocks": clocks,
     }

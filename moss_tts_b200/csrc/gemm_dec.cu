@@ -274,7 +274,7 @@ int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, in
 
 // Split count for the persistent kernel: minimise the longest CTA's work, counted in k-blocks, with every
 // unit charged ~2 k-blocks for its epilogue (a [128 x BN] fp32 partial tile costs about as much traffic).
-int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long long workspace_bytes) {
+int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long long workspace_bytes, bool own_reduce) {
   int best = 1;
   long long best_cost = -1;
   for (int sp = 1; sp <= 32; ++sp) {
@@ -282,7 +282,10 @@ int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long lon
     const long long rounds = (static_cast<long long>(tiles) * sp + kNumSMs - 1) / kNumSMs;
     // + sp: every split is another [M, N] fp32 slab the consumer kernel has to pull through its few SMs' L2 ports
     // (add_rmsnorm: one block per row), about one k-block of time each
-    const long long cost = rounds * ((k_blocks + sp - 1) / sp + 2) + sp;
+    long long cost = rounds * ((k_blocks + sp - 1) / sp + 2) + sp;
+    // a GEMM that has to hand back a finished tensor pays a separate reduce kernel for any split (launch + a pass
+    // over all slabs, ~17 us for the audio heads): only worth it when the balance gain is large
+    if (own_reduce && sp > 1) cost += 24 + 2 * sp;
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = sp; }
   }
   return best;
@@ -304,7 +307,7 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   const int tiles = cdiv(p.N, kTileA);
   const long long per_split = static_cast<long long>(p.M) * p.N * 4;
   int splits = 1;
-  if (p.workspace) splits = dec_pick_splits(tiles, k_blocks, per_split, p.workspace_bytes);
+  if (p.workspace) splits = dec_pick_splits(tiles, k_blocks, per_split, p.workspace_bytes, p.out_splits == nullptr);
   MT_CHECK(per_split / 4 * splits < (1ll << 31), "linear_dec: split-K partials exceed 2^31 elements");
   if (p.out_splits) {
     MT_CHECK(p.workspace && per_split <= p.workspace_bytes, "linear: workspace too small for partial output");
