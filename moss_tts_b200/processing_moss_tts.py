@@ -68,6 +68,30 @@ class MossTTSDelayProcessor:
         pieces = torch.tensor_split(idx, breaks) if breaks else [idx]
         return [audio_codes[s] for s in pieces]
 
+    def _split_segments_many(self, mats: List[torch.Tensor]) -> List[List[torch.Tensor]]:
+        """_split_segments for a list of de-delayed matrices with ONE device->host transfer (the all-pad row masks of
+        every utterance); the runs are then plain row slices."""
+        if not mats:
+            return []
+        pad = self.model_config.audio_pad_code
+        masks = [(m == pad).all(dim=1) for m in mats]
+        flat = torch.cat(masks).cpu().numpy()
+        out, off = [], 0
+        for m in mats:
+            n = int(m.shape[0])
+            is_pad = flat[off: off + n]
+            off += n
+            segs, start = [], None
+            for r in range(n):
+                if not is_pad[r] and start is None:
+                    start = r
+                elif is_pad[r] and start is not None:
+                    segs.append(m[start:r]); start = None
+            if start is not None:
+                segs.append(m[start:n])
+            out.append(segs)
+        return out
+
     @staticmethod
     def _trim_first(wavs: List[torch.Tensor], first_len: int, start_length: int) -> List[torch.Tensor]:
         """:692-707"""
@@ -126,9 +150,8 @@ class MossTTSDelayProcessor:
         equal the per-utterance reference path (:668-709)."""
         per_utt = []
         all_segs = []
-        for start_length, gen in output:
-            dd = self.apply_de_delay_pattern(gen[:, 1:])
-            segs = self._split_segments(dd)
+        dds = [self.apply_de_delay_pattern(gen[:, 1:]) for _, gen in output]
+        for (start_length, _), segs in zip(output, self._split_segments_many(dds)):
             per_utt.append((int(start_length), len(all_segs), [int(s.shape[0]) for s in segs]))
             all_segs += segs
         wavs = self._decode_segments_device(all_segs) if all_segs else []
