@@ -89,6 +89,48 @@ class MossTTSLocalModel:
             w["heads"].append(self._lin(sd[f"lm_heads.{ch}.weight"]))
         self._w = w
 
+    @classmethod
+    def random_init(cls, config: LocalConfig, device="cuda:0", seed: int = 0, std: float = 0.02):
+        """Random weights generated directly on the device (benchmarks: no checkpoint, no network)."""
+        self = cls.__new__(cls)
+        self.config, self.device, self.dtype = config, torch.device(device), torch.bfloat16
+        c = config
+        gen = torch.Generator(device=self.device)
+        gen.manual_seed(seed)
+
+        def rn(*shape, s=std, mean=0.0):
+            return (torch.randn(*shape, device=self.device, dtype=torch.float32, generator=gen) * s + mean).to(torch.bfloat16)
+
+        def lin(n, k, s=std):
+            return self._lin(rn(n, k, s=s))
+
+        H, I, C_ = c.hidden_size, c.intermediate_size, c.n_vq + 1
+        LH, LF, AF = c.local_hidden_size, c.local_ffn_hidden_size, c.additional_mlp_ffn_hidden_size
+        w: Dict[str, object] = {"embed": rn(c.vocab_size, H), "emb_ext": rn(c.n_vq, c.audio_head_size, H)}
+        for sfx, (n_layers, hid, ffn) in (("", (c.num_layers, H, I)), ("_l", (c.local_num_layers, LH, LF))):
+            for key in ("qkv", "o", "gu", "down", "ln_in", "ln_post", "qn", "kn"):
+                w[key + sfx] = []
+            for _ in range(n_layers):
+                w["qkv" + sfx].append(lin(c.q_size + 2 * c.kv_size, hid))
+                w["o" + sfx].append(lin(hid, c.q_size))
+                w["gu" + sfx].append(lin(2 * ffn, hid))
+                w["down" + sfx].append(lin(hid, ffn))
+                w["ln_in" + sfx].append(rn(hid, s=0.05, mean=1.0))
+                w["ln_post" + sfx].append(rn(hid, s=0.05, mean=1.0))
+                w["qn" + sfx].append(rn(c.head_dim, s=0.05, mean=1.0))
+                w["kn" + sfx].append(rn(c.head_dim, s=0.05, mean=1.0))
+        w["norm"] = rn(H, s=0.05, mean=1.0)
+        w["norm_l"] = rn(LH, s=0.05, mean=1.0)
+        w["in_gu"], w["in_down"] = lin(2 * AF, H), lin(LH, AF)
+        w["out_gu"] = [lin(2 * AF, LH) for _ in range(C_)]
+        w["out_down"] = [lin(H, AF) for _ in range(C_)]
+        w["head_norm"] = [rn(H, s=0.05, mean=1.0) for _ in range(C_)]
+        w["heads"] = [lin(c.vocab_size if ch == 0 else c.audio_head_size, H, s=4 * std) for ch in range(C_)]
+        self._w = w
+        self._engine, self._cap = None, (0, 0, 0)
+        self.last_step_ms, self.last_n_steps = None, 0
+        return self
+
     def weight_bytes(self) -> int:
         n = 0
         for v in self._w.values():

@@ -1,0 +1,115 @@
+"""Measurements of the BASELINE.json configurations that are not the bench.py headline (configs[1]):
+  C3  codec decode sweep                     B in {1,4,16,64,256} x T in {13,63,125,375,750} frames
+  C4  MossTTSLocal (assumed 1.7B shape)      B = 128, 96-token prompt, 125 frames, n_vq_for_inference = 32
+  C5  MossTTSDelay n_vq = 16 long context    B = 4, ~512-token prompt, 3765 steps (>= 5 min of audio)
+One JSON line per measurement; device-timed with CUDA events after a warm-up call.
+
+  python scripts/bench_configs.py [--what c3,c4,c5] [--quick]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def timed(fn, reps=1):
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        r = fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps, r
+
+
+def c3(args, dev):
+    from moss_tts_b200.config import CodecConfig
+    from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+    ccfg = CodecConfig.released()
+    codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=24 << 30)
+    Bs = [1, 16, 256] if args.quick else [1, 4, 16, 64, 256]
+    Ts = [13, 125, 750] if args.quick else [13, 63, 125, 375, 750]
+    for B in Bs:
+        for T in Ts:
+            codes = torch.randint(0, 1024, (ccfg.num_quantizers, B, T), device=dev)
+            codec.decode(codes)                                     # warm-up (workspace, attributes)
+            ms, _ = timed(lambda: codec.decode(codes), reps=2 if B * T > 20000 else 5)
+            ms_c, _ = timed(lambda: codec.decode(codes, chunk_duration=8, allow_batched_chunks=True),
+                            reps=2 if B * T > 20000 else 5)
+            print(json.dumps({"config": "C3 codec decode", "B": B, "T_frames": T, "audio_s": B * T / 12.5, "ms": ms,
+                              "audio_s_per_s": B * T / 12.5 / (ms * 1e-3), "ms_chunked_8s": ms_c,
+                              "audio_s_per_s_chunked": B * T / 12.5 / (ms_c * 1e-3)}), flush=True)
+
+
+def c4(args, dev):
+    from moss_tts_b200.config import LocalConfig
+    from moss_tts_b200.modeling_moss_tts_local import MossTTSLocalModel
+    import bench
+    cfg = LocalConfig.local_1p7b(32)
+    model = MossTTSLocalModel.random_init(cfg, device=dev, seed=4321)
+    B = 32 if args.quick else 128
+    frames = 16 if args.quick else 125
+    bench.PROMPT_LEN = 96
+    ids, _ = bench.make_prompts(cfg, B, seed=0)
+    ids = ids.to(dev)
+    kw = dict(max_new_tokens=frames, n_vq_for_inference=cfg.n_vq, eos_token_id=None, record_step_times=True)
+    model.generate(ids, **kw)
+    ms, out = timed(lambda: model.generate(ids, **kw))
+    steps = sorted(model.last_step_ms[2:])
+    print(json.dumps({"config": "C4 MossTTSLocal greedy", "shape": "assumed Qwen3-1.7B backbone + local 4L/1536/8960/2048",
+                      "B": B, "frames": frames, "ms_total": ms, "prefill_plus_first_frame_ms": model.last_step_ms[0],
+                      "ms_per_frame_median": steps[len(steps) // 2], "audio_s_per_s": B * frames / 12.5 / (ms * 1e-3),
+                      "weight_GB": model.weight_bytes() / 1e9}), flush=True)
+
+
+def c5(args, dev):
+    from moss_tts_b200.config import LMConfig
+    from moss_tts_b200.modeling_moss_tts import MossTTSDelayModel
+    import bench
+    cfg = LMConfig.delay_8b(n_vq=16)
+    model = MossTTSDelayModel.random_init(cfg, device=dev, seed=77, never_stop=True)
+    B = 4
+    steps = 400 if args.quick else 3765
+    bench.PROMPT_LEN = 512
+    ids, mask = bench.make_prompts(cfg, B, seed=0)
+    g = torch.Generator().manual_seed(1)
+    ids[:, 100:500, 1:] = torch.randint(0, 1024, (B, 400, cfg.n_vq), generator=g)      # reference codes in the prompt
+    ids, mask = ids.to(dev), mask.to(dev)
+    for name, kw in (("greedy pen=1.0", dict(text_temperature=0, audio_temperature=0)),
+                     ("sampled T=1.1 k=50 p=0.9 pen=1.1", dict(text_temperature=1.1, text_top_k=50, text_top_p=0.9,
+                                                              audio_temperature=1.1, audio_top_k=50, audio_top_p=0.9,
+                                                              audio_repetition_penalty=1.1))):
+        kw = dict(max_new_tokens=steps, record_step_times=True, **kw)
+        model.generate(ids, mask, **dict(kw, max_new_tokens=8))
+        ms, out = timed(lambda: model.generate(ids, mask, **kw))
+        st = model.last_step_ms
+        n = model.last_n_steps
+        tail = sorted(st[-200:])
+        print(json.dumps({"config": "C5 MossTTSDelay n_vq=16 long context", "mode": name, "B": B, "prompt": 512,
+                          "steps_run": n, "ms_total": ms, "prefill_ms": st[0], "ms_per_step_first_200": sorted(st[2:202])[100],
+                          "ms_per_step_last_200": tail[len(tail) // 2], "final_kv_len": 512 + n,
+                          "audio_s_per_s": B * max(n - cfg.n_vq, 0) / 12.5 / (ms * 1e-3)}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--what", default="c3,c4,c5")
+    ap.add_argument("--quick", action="store_true")
+    args = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    for w in args.what.split(","):
+        {"c3": c3, "c4": c4, "c5": c5}[w](args, dev)
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
