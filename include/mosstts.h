@@ -66,6 +66,9 @@ int mt_debug_force_simt(int on);
 /* Debug knob: launch kernels with (1, default) or without (0) the programmatic-dependent-launch
  * attribute.  Results are bit-identical either way; only kernel overlap changes. */
 int mt_debug_set_pdl(int on);
+/* Debug knob: CTAs per (batch row, kv head) of the fused decode attention: 0 = automatic (1 when B * n_kv fills the
+ * GPU, else a thread-block cluster of 2/4/8 CTAs that split the keys), 1/2/4/8 = forced.  Any other value: MT_ERR_ARG. */
+int mt_debug_set_attn_cluster(int cs);
 /* Debug timeline: every decode-GEMM launch issued (or captured into a graph) after this call takes the next
  * 148*8 uint64 slots of the device buffer `buf` and records 8 %globaltimer stamps per CTA (scripts/trace_decode.py).
  * NULL switches it off.  Returns the number of slots handed out since the previous call. */

@@ -2,7 +2,7 @@
 #include "gemm.cuh"
 #include "sampling.cuh"
 
-namespace mt { const char* last_error(); void set_pdl(int on); void set_trace(void* buf, long long words); long long trace_used(); }
+namespace mt { const char* last_error(); void set_pdl(int on); void set_trace(void* buf, long long words); long long trace_used(); void set_attn_cluster(int cs); }
 using namespace mt;
 
 extern "C" int mt_version(void) { return 100; }
@@ -11,6 +11,11 @@ extern "C" long long mt_launch_count(void) { return g_launches; }
 extern "C" int mt_debug_force_simt(int on) { g_force_simt = on != 0; return MT_OK; }
 
 extern "C" int mt_debug_set_pdl(int on) { mt::set_pdl(on); return MT_OK; }
+extern "C" int mt_debug_set_attn_cluster(int cs) {
+  if (cs != 0 && cs != 1 && cs != 2 && cs != 4 && cs != 8) return MT_ERR_ARG;
+  mt::set_attn_cluster(cs);
+  return MT_OK;
+}
 extern "C" long long mt_debug_set_trace(void* buf, long long words) { const long long used = mt::trace_used(); mt::set_trace(buf, words); return used; }
 
 extern "C" int mt_gemm(const mt_gemm_args* a, mt_stream s) {

@@ -8,10 +8,10 @@
 //   a9  (de-)delay pattern                     processing_moss_tts.py:516-537
 // Logits are bf16; every transform returns the value a bf16 PyTorch tensor would hold.
 #include "sampling.cuh"
+#include "sampling_select.cuh"
 
 namespace mt {
 
-constexpr int kSampThreads = 256;
 static size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- uniform hash shared with oracle/sampling.py::uniform_u ----------------------------------
@@ -26,46 +26,6 @@ __host__ __device__ inline float mt_uniform(uint32_t seed, uint32_t step, uint32
   h = mix32(h ^ (channel * 0x27D4EB2Fu));
   return static_cast<float>(h >> 8) * (1.0f / 16777216.0f);
 }
-
-// ---- per-row logit transform -----------------------------------------------------------------
-struct RowXform {
-  const bf16* row; int V;
-  float temp;                 // value = bf16(l / temp)
-  int mode;                   // 0 plain, 1 text outside audio, 2 text inside audio
-  int ban[6]; int nban;       // ids forced to -inf (all modes)
-  int keep0, keep1;           // mode 2: everything else is -inf
-  const uint32_t* bitmap; float penalty;   // repetition penalty on ids whose bit is set
-  int penalty_first;          // HF processor order (MossTTSLocal): penalty on the raw logit, then temperature
-  __device__ __forceinline__ float get(int i) const {
-    float v = bf2f(row[i]);
-    if (penalty_first) {
-      if (bitmap && (bitmap[i >> 5] >> (i & 31) & 1u)) v = v < 0.f ? rbf(v * penalty) : rbf(v / penalty);
-      v = rbf(v / temp);
-#pragma unroll
-      for (int j = 0; j < 6; ++j)
-        if (j < nban && i == ban[j]) return -INFINITY;
-      return v;
-    }
-    v = rbf(v / temp);
-    if (mode == 2 && i != keep0 && i != keep1) return -INFINITY;
-#pragma unroll
-    for (int j = 0; j < 6; ++j)
-      if (j < nban && i == ban[j]) return -INFINITY;
-    if (bitmap && (bitmap[i >> 5] >> (i & 31) & 1u)) v = v > 0.f ? rbf(v / penalty) : rbf(v * penalty);
-    return v;
-  }
-};
-
-__device__ __forceinline__ uint32_t key16(float v) {
-  if (v != v) return 0u;                                  // NaN sorts below everything
-  const uint32_t b = __float_as_uint(v) >> 16;            // v is bf16-representable
-  return (b & 0x8000u) ? (~b & 0xFFFFu) : (b | 0x8000u);
-}
-__device__ __forceinline__ float unkey16(uint32_t k) {
-  const uint32_t b = (k & 0x8000u) ? (k & 0x7FFFu) : (~k & 0xFFFFu);
-  return __uint_as_float(b << 16);
-}
-constexpr uint32_t kKeyNegInf = 0x007Fu;
 
 // ---- greedy: first index of the maximum ------------------------------------------------------
 __device__ int row_argmax(const RowXform& x, uint32_t* s_u32) {
@@ -239,17 +199,96 @@ __device__ int row_sample(const RowXform& x, int top_k, float top_p, float u, Sa
 }
 
 // ---------------------------------------------------------------------------------------------
-// one block per (channel, row)
+// token of one row: one-pass selection (sampling_select.cuh), exact multi-pass fallback
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSampThreads)
+struct BlockSmem {
+  union {
+    SelSmem<BlockG> sel;
+    SampSmem old;
+  };
+};
+union SampleShared {
+  BlockSmem blk;
+  SelSmem<WarpG> warp[kSampThreads / 32];
+};
+
+// mode 2 (text channel inside audio): only the gen / delay slots survive the mask -- two candidates, no row scan.
+// Greedy: the larger one, the lower index on a tie, 0 when both are -inf (what torch.argmax gives on an all -inf row).
+__device__ int two_candidates(const RowXform& x, int k, SelSmem<BlockG>& sm) {
+  if (threadIdx.x == 0) {
+    const int i0 = min(x.keep0, x.keep1), i1 = max(x.keep0, x.keep1);
+    unsigned long long e[2];
+    int n = 0;
+    for (int t = 0; t < 2; ++t) {
+      const int i = t ? i1 : i0;
+      if (t && i1 == i0) break;
+      const uint32_t fk = (i >= 0 && i < x.V) ? key16(x.get(i)) : 0u;
+      if (fk > kKeyNegInf) e[n++] = (static_cast<unsigned long long>(0xFFFFu - fk) << 32) | static_cast<uint32_t>(i);
+    }
+    if (n == 2 && e[1] < e[0]) { const unsigned long long t = e[0]; e[0] = e[1]; e[1] = t; }
+    n = min(n, k);
+    for (int j = 0; j < n; ++j) sm.list[j] = e[j];
+    sm.n = n;
+  }
+  __syncthreads();
+  const int n = sm.n;
+  __syncthreads();
+  return n;
+}
+
+__device__ int block_pick(const RowXform& x, bool do_sample, int top_k, float top_p, float u, BlockSmem& sm) {
+  const int k = do_sample ? min(top_k, x.V) : 1;
+  const int n = x.mode == 2 ? two_candidates(x, k, sm.sel) : select_topk<BlockG>(x, k, sm.sel);
+  if (n < 0) {
+    __syncthreads();
+    return do_sample ? row_sample(x, top_k, top_p, u, sm.old) : row_argmax(x, reinterpret_cast<uint32_t*>(sm.old.red));
+  }
+  if (!do_sample) return n ? static_cast<int>(sm.sel.list[0] & 0xFFFFFFFFu) : 0;
+  return draw_sorted<BlockG>(sm.sel.list, n, top_p, u, sm.sel.ebuf, &sm.sel.result);
+}
+
+// one warp per row (short rows, k <= kWarpMaxK)
+constexpr int kWarpMaxK = 58;          // k + 6 banned ids <= the 64 half-stream maxima of a warp
+constexpr int kWarpMaxV = 4096;
+__device__ int warp_pick(const RowXform& x, bool do_sample, int top_k, float top_p, float u, SelSmem<WarpG>& sm) {
+  const int k = do_sample ? min(top_k, x.V) : 1;
+  int n = select_topk<WarpG>(x, k, sm);
+  if (n < 0) {
+    __syncwarp();
+    n = warp_exact_select(x, k, sm);
+  }
+  if (!do_sample) return n ? static_cast<int>(sm.list[0] & 0xFFFFFFFFu) : 0;
+  return draw_sorted<WarpG>(sm.list, n, top_p, u, sm.ebuf, &sm.result);
+}
+
+// ---------------------------------------------------------------------------------------------
+// WA = true : blocks [0, B) take the text rows (one block per row); every later block takes eight
+//             (row, audio channel) pairs, one per warp
+// WA = false: one block per (channel, row), grid (C, B)   (audio heads too long or top-k too large for a warp)
+// ---------------------------------------------------------------------------------------------
+template <bool WA>
+__global__ void __launch_bounds__(kSampThreads, 3)
 gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
                   const bf16* __restrict__ audio_logits, int audio_head, SampleCfg sc, TokenIds tk) {
-  __shared__ SampSmem sm;
+  __shared__ SampleShared sm;
   pdl_trigger();
   pdl_wait();
   if (*st.done) return;
-  const int ch = blockIdx.x, b = blockIdx.y;
   const int n_vq = st.C - 1;
+  const int warp = threadIdx.x >> 5;
+  int ch, b;
+  bool warp_mode = false;
+  if (WA) {
+    if (static_cast<int>(blockIdx.x) < st.B) { ch = 0; b = blockIdx.x; }
+    else {
+      const int pair = (blockIdx.x - st.B) * (kSampThreads / 32) + warp;
+      if (pair >= st.B * n_vq) return;
+      b = pair / n_vq; ch = 1 + pair % n_vq; warp_mode = true;
+    }
+  } else {
+    ch = blockIdx.x; b = blockIdx.y;
+  }
+  const bool leader = warp_mode ? (threadIdx.x & 31) == 0 : threadIdx.x == 0;
   const int step = *st.step;
   const int delayed = st.delayed[b];
   int64_t* dst = st.next_ids + static_cast<long long>(b) * st.C + ch;
@@ -261,7 +300,7 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
     if (st.stopping[b]) forced = tk.pad;
     else if (delayed >= 0 && delayed < n_vq) forced = tk.delay_slot;
     else if (delayed == n_vq) forced = tk.audio_end;
-    if (forced >= 0) { if (threadIdx.x == 0) *dst = forced; return; }
+    if (forced >= 0) { if (leader) *dst = forced; return; }
     x.row = text_logits + static_cast<long long>(b) * vocab; x.V = vocab; x.temp = sc.text_temperature;
     if (st.is_audio[b]) {
       x.mode = 2; x.keep0 = tk.gen_slot; x.keep1 = tk.delay_slot;
@@ -271,36 +310,21 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
     }
     if (step == 0) x.ban[x.nban++] = 151662;              // hard-coded id in the reference (:462)
     if (step <= n_vq) x.ban[x.nban++] = tk.im_end;
-    int tok;
-    if (x.mode == 2 && !sc.text_do_sample) {
-      // inside audio only the gen/delay slots survive the mask: compare the two logits directly
-      // (first max index on ties; an all -inf row argmaxes to index 0 like torch.argmax)
-      if (threadIdx.x == 0) {
-        const int i0 = min(x.keep0, x.keep1), i1 = max(x.keep0, x.keep1);
-        const float v0 = x.get(i0), v1 = x.get(i1);
-        int t = 0;
-        if (v0 == -INFINITY && v1 == -INFINITY) t = 0;
-        else t = v1 > v0 ? i1 : i0;
-        *dst = t;
-      }
-      return;
-    }
-    if (!sc.text_do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
-    else tok = row_sample(x, sc.text_top_k, sc.text_top_p, mt_uniform(sc.seed, step, b, 0), sm);
-    if (threadIdx.x == 0) *dst = tok;
+    const int tok = block_pick(x, sc.text_do_sample, sc.text_top_k, sc.text_top_p, mt_uniform(sc.seed, step, b, 0), sm.blk);
+    if (leader) *dst = tok;
   } else {
     // ---- audio channel i = ch-1 (modeling_moss_tts.py:475-503); lengths are the pre-update ones
     const int i = ch - 1;
     const bool active = st.audio_len[b] > i && (delayed < 0 || i > delayed - 1);
-    if (!active) { if (threadIdx.x == 0) *dst = tk.audio_pad_code; return; }
+    if (!active) { if (leader) *dst = tk.audio_pad_code; return; }
     x.row = audio_logits + (static_cast<long long>(b) * n_vq + i) * audio_head; x.V = audio_head;
     x.temp = sc.audio_temperature;
     x.ban[0] = tk.audio_pad_code; x.nban = 1;
     if (sc.penalty != 1.0f) { x.bitmap = i == 0 ? st.seen0 : st.seen_rest; x.penalty = sc.penalty; }
-    int tok;
-    if (!sc.audio_do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
-    else tok = row_sample(x, sc.audio_top_k, sc.audio_top_p, mt_uniform(sc.seed, step, b, ch), sm);
-    if (threadIdx.x == 0) *dst = tok;
+    const float u = mt_uniform(sc.seed, step, b, ch);
+    const int tok = warp_mode ? warp_pick(x, sc.audio_do_sample, sc.audio_top_k, sc.audio_top_p, u, sm.warp[warp])
+                              : block_pick(x, sc.audio_do_sample, sc.audio_top_k, sc.audio_top_p, u, sm.blk);
+    if (leader) *dst = tok;
   }
 }
 
@@ -431,8 +455,13 @@ int gen_init(const GenState& st, const int64_t* input_ids, const uint8_t* attn_m
 
 int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, const bf16* audio_logits, int audio_head,
                     const SampleCfg& sc, const TokenIds& tk, cudaStream_t s) {
-  dim3 grid(st.C, st.B);
-  MT_CUDA(launch(gen_sample_kernel, grid, dim3(kSampThreads), 0, s, st, text_logits, vocab, audio_logits, audio_head, sc, tk));
+  const int n_vq = st.C - 1;
+  if (audio_head <= kWarpMaxV && (!sc.audio_do_sample || sc.audio_top_k <= kWarpMaxK)) {
+    const int grid = st.B + cdiv(st.B * n_vq, kSampThreads / 32);
+    MT_CUDA(launch(gen_sample_kernel<true>, dim3(grid), dim3(kSampThreads), 0, s, st, text_logits, vocab, audio_logits, audio_head, sc, tk));
+  } else {
+    MT_CUDA(launch(gen_sample_kernel<false>, dim3(st.C, st.B), dim3(kSampThreads), 0, s, st, text_logits, vocab, audio_logits, audio_head, sc, tk));
+  }
   MT_CUDA(launch(gen_commit_kernel, dim3(1), dim3(1024), 0, s, st, tk));
   count_launch(2);
   return MT_OK;
@@ -441,19 +470,21 @@ int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, cons
 // ---------------------------------------------------------------------------------------------
 // standalone sample_token (inference_utils.py:111-145) on [N,V] bf16 logits
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSampThreads)
-sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int V, float temperature,
+template <bool W>
+__global__ void __launch_bounds__(kSampThreads, 3)
+sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int N, int V, float temperature,
                      const uint32_t* __restrict__ bitmap, float penalty, float top_p, int top_k, int do_sample,
                      const float* __restrict__ uniforms, int64_t* __restrict__ out) {
-  __shared__ SampSmem sm;
-  const int r = blockIdx.x;
+  __shared__ SampleShared sm;
+  const int warp = threadIdx.x >> 5;
+  const int r = W ? blockIdx.x * (kSampThreads / 32) + warp : blockIdx.x;
+  if (r >= N) return;
   RowXform x;
   x.row = logits + r * ld; x.V = V; x.temp = temperature; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
   x.bitmap = penalty != 1.0f ? bitmap : nullptr; x.penalty = penalty; x.penalty_first = 0;
-  int tok;
-  if (!do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
-  else tok = row_sample(x, top_k, top_p, uniforms ? uniforms[r] : 0.f, sm);
-  if (threadIdx.x == 0) out[r] = tok;
+  const float u = uniforms ? uniforms[r] : 0.f;
+  const int tok = W ? warp_pick(x, do_sample, top_k, top_p, u, sm.warp[warp]) : block_pick(x, do_sample, top_k, top_p, u, sm.blk);
+  if (W ? (threadIdx.x & 31) == 0 : threadIdx.x == 0) out[r] = tok;
 }
 
 int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
@@ -463,8 +494,12 @@ int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperat
   if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
     return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
   MT_CHECK(temperature > 0.f, "temperature must be > 0");
-  sample_tokens_kernel<<<N, kSampThreads, 0, s>>>(logits, ld, V, temperature, prev_bitmap, penalty, top_p, top_k,
-                                                  do_sample, uniforms, out);
+  if (V <= kWarpMaxV && (!do_sample || top_k <= kWarpMaxK))
+    sample_tokens_kernel<true><<<cdiv(N, kSampThreads / 32), kSampThreads, 0, s>>>(logits, ld, N, V, temperature, prev_bitmap, penalty,
+                                                                                   top_p, top_k, do_sample, uniforms, out);
+  else
+    sample_tokens_kernel<false><<<N, kSampThreads, 0, s>>>(logits, ld, N, V, temperature, prev_bitmap, penalty, top_p, top_k,
+                                                           do_sample, uniforms, out);
   count_launch();
   MT_LAUNCH_CHECK();
   return MT_OK;
@@ -477,14 +512,17 @@ int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperat
 //                   -> Temperature -> TopK -> TopP (:359-370) and the inverse-CDF draw of this library
 //   local_commit  : EOS / pad substitution for finished rows (:430-433), history append, stop flags
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSampThreads)
+template <bool W>
+__global__ void __launch_bounds__(kSampThreads, 3)
 local_sample_kernel(LocalState st, const bf16* __restrict__ logits, int V, int c, int do_sample, float temperature,
                     float penalty, float top_p, int top_k, unsigned seed) {
-  __shared__ SampSmem sm;
+  __shared__ SampleShared sm;
   pdl_trigger();
   pdl_wait();
   if (*st.done) return;
-  const int b = blockIdx.x;
+  const int warp = threadIdx.x >> 5;
+  const int b = W ? blockIdx.x * (kSampThreads / 32) + warp : blockIdx.x;
+  if (b >= st.B) return;
   RowXform x;
   x.row = logits + static_cast<long long>(b) * V; x.V = V; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
   x.temp = do_sample ? temperature : 1.f; x.bitmap = nullptr; x.penalty = 1.f; x.penalty_first = 1;
@@ -493,10 +531,9 @@ local_sample_kernel(LocalState st, const bf16* __restrict__ logits, int V, int c
     x.bitmap = st.seen + (static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words;
     x.penalty = penalty;
   }
-  int tok;
-  if (!do_sample) tok = row_argmax(x, reinterpret_cast<uint32_t*>(sm.red));
-  else tok = row_sample(x, top_k, top_p, mt_uniform(seed, *st.step, b, c), sm);
-  if (threadIdx.x == 0) st.next_ids[static_cast<long long>(b) * st.C + c] = tok;
+  const float u = mt_uniform(seed, *st.step, b, c);
+  const int tok = W ? warp_pick(x, do_sample, top_k, top_p, u, sm.warp[warp]) : block_pick(x, do_sample, top_k, top_p, u, sm.blk);
+  if (W ? (threadIdx.x & 31) == 0 : threadIdx.x == 0) st.next_ids[static_cast<long long>(b) * st.C + c] = tok;
 }
 
 __global__ void local_commit_kernel(LocalState st, int eos, int pad_code, int n_channels_sampled) {
@@ -583,8 +620,12 @@ int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_
                  float top_p, int top_k, unsigned seed, cudaStream_t s) {
   if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
     return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
-  MT_CUDA(launch(local_sample_kernel, dim3(st.B), dim3(kSampThreads), 0, s, st, logits, V, c, do_sample, temperature,
-                 penalty, top_p, top_k, seed));
+  if (V <= kWarpMaxV && (!do_sample || top_k <= kWarpMaxK))
+    MT_CUDA(launch(local_sample_kernel<true>, dim3(cdiv(st.B, kSampThreads / 32)), dim3(kSampThreads), 0, s, st, logits, V, c,
+                   do_sample, temperature, penalty, top_p, top_k, seed));
+  else
+    MT_CUDA(launch(local_sample_kernel<false>, dim3(st.B), dim3(kSampThreads), 0, s, st, logits, V, c, do_sample, temperature,
+                   penalty, top_p, top_k, seed));
   count_launch();
   return MT_OK;
 }

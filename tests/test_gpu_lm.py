@@ -163,3 +163,27 @@ def test_generate_long_context_n_vq16():
     o_out, trace = oracle.generate(ids, mask, return_trace=True, **kw)
     exact = _check_tokens(out, [o[1].numpy() for o in o_out], trace, [o[0] for o in o_out], "tiny-nvq16-long")
     print(f"[tiny-nvq16-long] greedy ids bit-exact vs oracle: {exact}")
+
+
+@pytest.mark.parametrize("shape,cs", [("tiny", 1), ("tiny", 2), ("tiny", 8), ("mid", 4), ("mid", 8)])
+def test_decode_attention_key_split_clusters(shape, cs):
+    """The fused decode attention split over a thread-block cluster of `cs` CTAs per (row, kv head) (the small-batch /
+    long-context launch shape) must give the oracle's greedy tokens for every cluster size, including contexts
+    shorter than 16 * cs keys (empty CTAs) and ragged left padding."""
+    from moss_tts_b200._lib import lib
+    cfg = LMConfig.tiny(n_vq=4) if shape == "tiny" else LMConfig.mid(n_vq=8)
+    w = make_lm_weights(cfg, seed=33, never_stop=True)
+    model = MossTTSDelayModel(cfg, w, device=DEV)
+    oracle = OracleLM(cfg, w, torch.bfloat16)
+    assert lib().mt_debug_set_attn_cluster(3) != 0          # not a supported size
+    assert lib().mt_debug_set_attn_cluster(cs) == 0
+    try:
+        for S0, left_pad, steps in ((5, [0, 2], 30), (300, [0, 123], 24)):
+            ids, mask = make_prompt(cfg, 2, S0, seed=5 + S0, left_pad=left_pad)
+            kw = dict(max_new_tokens=steps, text_temperature=0, audio_temperature=0)
+            out = model.generate(ids, mask, **kw)
+            o_out, trace = oracle.generate(ids, mask, return_trace=True, **kw)
+            exact = _check_tokens(out, [o[1].numpy() for o in o_out], trace, [o[0] for o in o_out], f"{shape}-cs{cs}-S{S0}")
+            print(f"[{shape} cs={cs} S0={S0}] greedy ids bit-exact vs oracle: {exact}")
+    finally:
+        lib().mt_debug_set_attn_cluster(0)

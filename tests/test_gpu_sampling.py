@@ -89,3 +89,93 @@ def test_delay_pattern_roundtrip(T, n):
     back = MossTTSDelayProcessor.apply_de_delay_pattern(d)
     np.testing.assert_array_equal(back.cpu().numpy(), codes.numpy())
     np.testing.assert_array_equal(back.cpu().numpy(), apply_de_delay_pattern(d.cpu().numpy()))
+
+
+# ---- one-pass selection (sampling_select.cuh): edge cases of the candidate list and its exact fallbacks ----------
+def _native_sample(x, *, temperature=1.0, top_k=0, top_p=1.0, do_sample=True, u=None, bitmap=None, penalty=1.0):
+    import ctypes as C
+    from moss_tts_b200 import _lib as L
+    x = x.to(DEV).contiguous()
+    N, V = x.shape
+    out = torch.empty(N, dtype=torch.int64, device=DEV)
+    uu = None if u is None else u.to(device=DEV, dtype=torch.float32).contiguous()
+    bm = None if bitmap is None else bitmap.to(DEV).contiguous()
+    L.check(L.lib().mt_sample_tokens(L.ptr(x), C.c_longlong(x.stride(0)), N, V, C.c_float(temperature), L.ptr(bm),
+                                     C.c_float(penalty), C.c_float(top_p), int(top_k), int(do_sample), L.ptr(uu),
+                                     L.ptr(out), L.stream_ptr(DEV)), "mt_sample_tokens")
+    return out.cpu()
+
+
+def _quantised_rows(n, V, seed, levels=23):
+    """Few distinct values -> many exact ties, so the top-k boundary always cuts through a tie class."""
+    g = torch.Generator().manual_seed(seed)
+    x = (torch.randint(0, levels, (n, V), generator=g).float() * 0.125 - 1.0).to(torch.bfloat16)
+    x[:, -1] = float("-inf")
+    return x
+
+
+@pytest.mark.parametrize("V,k", [(1025, 25), (1025, 58), (1025, 59), (151936, 50), (151936, 300), (151936, 600),
+                                 (70, 25), (10, 25), (4097, 25)])
+def test_topk_support_with_ties_is_lowest_index_first(V, k):
+    """u -> 0 draws the best candidate and u -> 1 the last one kept: with top_p = 1 those are the first and the k-th
+    entry of the (value desc, index asc) order, which pins the tie handling of every selection path (warp / block,
+    one-pass / exact fallback: 23 levels over a 1025-entry row overflow neither list, over 151936 entries both)."""
+    n = 16 if V < 10000 else 4
+    x = _quantised_rows(n, V, V + k)
+    x[0, :] = 0.5                                                     # a row of nothing but ties
+    for u_val in (0.0, 0.999999):
+        u = torch.full((n,), u_val)
+        got = _native_sample(x, top_k=k, top_p=1.0, u=u)
+        for r in range(n):
+            assert int(got[r]) == S.sample_row(x[r], top_k=k, top_p=1.0, do_sample=True, u=u_val), (r, u_val)
+
+
+@pytest.mark.parametrize("V,k,temp", [(1025, 25, 1.7), (1025, 50, 0.6), (151936, 50, 1.5), (151936, 50, 3.3)])
+def test_temperature_merges_neighbouring_values(V, k, temp):
+    """bf16(l / T) maps neighbouring logits onto one value: the candidate set must be chosen on the transformed
+    values (ties -> lowest index), not on the raw ones."""
+    n = 12 if V < 10000 else 3
+    g = torch.Generator().manual_seed(V + k)
+    x = (torch.randn(n, V, generator=g) * 0.05 + 4.0).to(torch.bfloat16)      # values packed into a few bf16 steps
+    x[:, -1] = float("-inf")
+    xt = (x.float() / temp).to(torch.bfloat16)
+    for u_val in (0.0, 0.37, 0.999999):
+        u = torch.full((n,), u_val)
+        got = _native_sample(x, temperature=temp, top_k=k, top_p=1.0, u=u)
+        for r in range(n):
+            cand, _ = S.filtered_distribution(xt[r], k, 1.0)
+            assert int(got[r]) in set(cand.tolist()), (r, u_val)
+            if u_val != 0.37:
+                assert int(got[r]) == S.sample_row(xt[r], top_k=k, top_p=1.0, do_sample=True, u=u_val), (r, u_val)
+    got = _native_sample(x, temperature=temp, do_sample=False)
+    for r in range(n):
+        assert int(got[r]) == S.sample_row(xt[r], do_sample=False)
+
+
+@pytest.mark.parametrize("V,k", [(1025, 25), (151936, 50)])
+def test_sampling_with_penalty_matches_oracle(V, k):
+    n = 24 if V < 10000 else 4
+    x = _rows(n, V, 77)
+    prev = torch.randint(0, min(V, 1025), (2, 60, 3), generator=torch.Generator().manual_seed(5))
+    ids = S.penalty_set(prev)
+    u = torch.rand(n, generator=torch.Generator().manual_seed(6))
+    got = sample_token(x.to(DEV), prev_tokens=prev.to(DEV), repetition_penalty=1.2, top_k=k, top_p=0.9, do_sample=True,
+                       uniforms=u.to(DEV)).cpu()
+    match = 0
+    for r in range(n):
+        match += int(got[r]) == S.sample_row(x[r], prev_ids=ids, repetition_penalty=1.2, top_k=k, top_p=0.9,
+                                             do_sample=True, u=float(u[r]))
+    assert match >= n - 1, (match, n)
+
+
+def test_rows_with_nan_and_inf_do_not_hang():
+    x = _rows(8, 1025, 3)
+    x[0, 7] = float("nan")
+    x[1, :] = float("-inf")
+    x[2, 100] = float("inf")
+    got = _native_sample(x, top_k=25, top_p=0.8, u=torch.full((8,), 0.5))
+    assert int(got[1]) == 0                              # nothing survives -> 0 (torch.argmax of an all -inf row)
+    g2 = _native_sample(x, do_sample=False)
+    assert int(g2[1]) == 0 and int(g2[2]) == 100
+    for r in range(3, 8):
+        assert int(g2[r]) == S.sample_row(x[r], do_sample=False)
