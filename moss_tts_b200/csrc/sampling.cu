@@ -238,7 +238,8 @@ __device__ int two_candidates(const RowXform& x, int k, SelSmem<BlockG>& sm) {
 
 __device__ int block_pick(const RowXform& x, bool do_sample, int top_k, float top_p, float u, BlockSmem& sm) {
   const int k = do_sample ? min(top_k, x.V) : 1;
-  const int n = x.mode == 2 ? two_candidates(x, k, sm.sel) : select_topk<BlockG>(x, k, sm.sel);
+  const int n = x.mode == 2 ? two_candidates(x, k, sm.sel)
+                            : (x.bitmap == nullptr ? select_topk<BlockG, true>(x, k, sm.sel) : select_topk<BlockG, false>(x, k, sm.sel));
   if (n < 0) {
     __syncthreads();
     return do_sample ? row_sample(x, top_k, top_p, u, sm.old) : row_argmax(x, reinterpret_cast<uint32_t*>(sm.old.red));
@@ -252,7 +253,7 @@ constexpr int kWarpMaxK = 58;          // k + 6 banned ids <= the 64 half-stream
 constexpr int kWarpMaxV = 4096;
 __device__ int warp_pick(const RowXform& x, bool do_sample, int top_k, float top_p, float u, SelSmem<WarpG>& sm) {
   const int k = do_sample ? min(top_k, x.V) : 1;
-  int n = select_topk<WarpG>(x, k, sm);
+  int n = x.bitmap == nullptr ? select_topk<WarpG, true>(x, k, sm) : select_topk<WarpG, false>(x, k, sm);
   if (n < 0) {
     __syncwarp();
     n = warp_exact_select(x, k, sm);

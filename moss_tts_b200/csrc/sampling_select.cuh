@@ -78,7 +78,7 @@ __device__ __forceinline__ uint32_t rawkeys2(uint32_t w) {
 struct BlockG {
   static constexpr int kSize = kSampThreads;
   static constexpr int kCap = 2048;      // list entries
-  static constexpr int kRaise = 256;     // compact the list when it is longer than this at a chunk boundary
+  static constexpr int kRaise = 128;     // compact the list when it is longer than this at a chunk boundary
   __device__ static int tid() { return threadIdx.x; }
   __device__ static void sync() { __syncthreads(); }
   __device__ static int sum(int v, int* scratch) {
@@ -149,24 +149,49 @@ __device__ inline uint32_t class_floor(uint32_t t, float temp, int* flag) {
   return r;
 }
 
+// packed bf16 pair: maximum (a NaN operand is ignored) and >= (0xFFFF per true half, false for NaN)
+__device__ __forceinline__ uint32_t bmax2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ uint32_t bge2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("set.ge.u32.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+constexpr uint32_t kNegInf2 = 0xFF80FF80u;               // (-inf, -inf)
+// key of one raw bf16 (low 16 bits of `half`) with key16's NaN rule
+__device__ __forceinline__ uint32_t rawkey(uint32_t half) {
+  const uint32_t k = rawkeys2(half) & 0xFFFFu;
+  return k > kKeyPosInf ? 0u : k;
+}
+
 // kk-th largest key (high words) among sm.list[0 .. n): a 16-step bisection run by the first warp of the group on
-// registers (n <= 512) or on the shared-memory list; every thread of the group gets the result.  0 if n < kk.
-template <class G>
+// registers (n <= 32 * NR) or on the shared-memory list; every thread of the group gets the result.  0 if n < kk.
+template <class G, int NR>
 __device__ uint32_t kth_listed(SelSmem<G>& sm, int n, int kk) {
   G::sync();
   const int lane = G::tid();
   if (lane < 32) {
     uint32_t prefix = 0u;
-    if (n <= 512) {
-      uint32_t kr[16];
+    if (n <= 32 * NR) {
+      uint32_t kr[NR];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) kr[j] = lane + 32 * j < n ? static_cast<uint32_t>(sm.list[lane + 32 * j] >> 32) : 0u;
-      for (int bit = 15; bit >= 0; --bit) {
-        const uint32_t thr = prefix | (1u << bit);
-        int c = 0;
+      for (int j = 0; j < NR; ++j) kr[j] = lane + 32 * j < n ? static_cast<uint32_t>(sm.list[lane + 32 * j] >> 32) : 0u;
+      if (kk == 1) {
+        uint32_t mx = 0u;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) c += kr[j] >= thr;           // absent entries have key 0 < thr
-        if (__reduce_add_sync(0xffffffffu, c) >= kk) prefix = thr;
+        for (int j = 0; j < NR; ++j) mx = max(mx, kr[j]);
+        prefix = __reduce_max_sync(0xffffffffu, mx);
+      } else {
+        for (int bit = 15; bit >= 0; --bit) {
+          const uint32_t thr = prefix | (1u << bit);
+          int c = 0;
+#pragma unroll
+          for (int j = 0; j < NR; ++j) c += kr[j] >= thr;           // absent entries have key 0 < thr
+          if (__reduce_add_sync(0xffffffffu, c) >= kk) prefix = thr;
+        }
       }
     } else {
       for (int bit = 15; bit >= 0; --bit) {
@@ -206,14 +231,50 @@ __device__ int sort_count(SelSmem<G>& sm, int n2, int k) {
   return G::sum(c, sm.scratch);
 }
 
+// One warp, at most 64 entries with indices below 65536: the same order on 32-bit entries ((0xFFFF - key) << 16 | index),
+// two per lane, sorted in registers with shuffles; the sorted entries go back to sm.list in the 64-bit format.
+__device__ inline int warp_sort64(SelSmem<WarpG>& sm, uint32_t e0, uint32_t e1, int k) {
+  const int lane = threadIdx.x & 31;
+  uint32_t e[2] = {e0, e1};
+#pragma unroll
+  for (int size = 2; size <= 64; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride == 32) {
+        const uint32_t lo = min(e[0], e[1]), hi = max(e[0], e[1]);
+        e[0] = lo; e[1] = hi;
+      } else {
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const uint32_t p = __shfl_xor_sync(0xffffffffu, e[r], stride);
+          const bool up = ((lane + 32 * r) & size) == 0;
+          const bool lower = (lane & stride) == 0;
+          e[r] = (lower == up) ? min(e[r], p) : max(e[r], p);
+        }
+      }
+    }
+  }
+  int c = 0;
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    const bool valid = e[r] != 0xFFFFFFFFu;
+    sm.list[lane + 32 * r] = valid ? (static_cast<unsigned long long>(e[r] >> 16) << 32) | (e[r] & 0xFFFFu) : ~0ull;
+    c += valid && lane + 32 * r < k;
+  }
+  __syncwarp();
+  return __reduce_add_sync(0xffffffffu, c);
+}
+
 // Sorted (value descending, index ascending) top-k candidates of the row in sm.list[0 .. return value); -1 = give up.
 // k == 1 skips the sort and leaves the single best entry in sm.list[0].
-template <class G>
+// FAST (no repetition penalty: the transform is monotone): the stream works on the raw bf16 words -- a packed
+// HMNMX2.BF16 maximum per 8 elements and one packed compare against the threshold; keys exist only for survivors.
+// Otherwise every element goes through RowXform::xf and the stream compares packed 16-bit keys.
+template <class G, bool FAST>
 __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
   constexpr int GS = G::kSize, CAP = G::kCap;
   const int tid = G::tid();
-  const bool fast = x.bitmap == nullptr;                 // monotone transform: stream raw keys
-  const int kk = k + (fast ? x.nban : 0);
+  const int kk = k + (FAST ? x.nban : 0);
   if (kk > 2 * GS || x.mode == 2) return -1;
   const int raise_at = max(G::kRaise, 2 * kk);
   const int V = x.V;
@@ -223,15 +284,23 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
   const int tail0 = head + 8 * nvec;
   const uint4* vrow = reinterpret_cast<const uint4*>(x.row + head);
 
-  auto load = [&](int vec) -> uint4 {
-    return vec < nvec ? __ldg(vrow + vec) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
-  };
-  // packed keys of one vector (lane order: low half = lower index)
-  auto keys = [&](const uint4& w, int vec, uint32_t (&kw)[4]) {
-    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
-    if (fast) {
+  // the four vectors of chunk c owned by this thread: raw words (FAST) or packed keys; absent vectors = lowest
+  auto load_chunk = [&](int c, uint4 (&w)[4]) {
+    const int v0 = c * 4 * GS + tid;
+    if ((c + 1) * 4 * GS <= nvec) {
 #pragma unroll
-      for (int q = 0; q < 4; ++q) kw[q] = rawkeys2(ww[q]);
+      for (int j = 0; j < 4; ++j) w[j] = __ldg(vrow + v0 + j * GS);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        w[j] = v0 + j * GS < nvec ? __ldg(vrow + v0 + j * GS) : make_uint4(kNegInf2, kNegInf2, kNegInf2, kNegInf2);
+    }
+  };
+  auto to_keys = [&](const uint4& w, int vec, uint32_t (&kw)[4]) {
+    const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+    if (FAST) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) kw[q] = ww[q];
     } else {
       const int i0 = head + 8 * vec;
 #pragma unroll
@@ -250,16 +319,29 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
     if (slot < CAP) sm.list[slot] = (static_cast<unsigned long long>(sk) << 32) | static_cast<uint32_t>(idx);
     else sm.flag = 1;
   };
-  auto filter = [&](const uint32_t (&kw)[4], int vec, uint32_t R) {
-    const uint32_t vm = __vmaxu2(__vmaxu2(kw[0], kw[1]), __vmaxu2(kw[2], kw[3]));
-    if (vec < nvec && ((vm >> 16) >= R || (vm & 0xFFFFu) >= R)) {
+  // R: key threshold; Rv2: the same threshold as a packed bf16 pair (FAST)
+  auto filter = [&](const uint32_t (&kw)[4], int vec, uint32_t R, uint32_t Rv2) {
+    bool hit;
+    if (FAST) {
+      hit = bge2(bmax2(bmax2(kw[0], kw[1]), bmax2(kw[2], kw[3])), Rv2) != 0u;
+    } else {
+      const uint32_t vm = __vmaxu2(__vmaxu2(kw[0], kw[1]), __vmaxu2(kw[2], kw[3]));
+      hit = (vm >> 16) >= R || (vm & 0xFFFFu) >= R;
+    }
+    if (hit && vec < nvec) {
       const int i0 = head + 8 * vec;
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        if ((kw[q] & 0xFFFFu) >= R) append(kw[q] & 0xFFFFu, i0 + 2 * q);
-        if ((kw[q] >> 16) >= R) append(kw[q] >> 16, i0 + 2 * q + 1);
+        const uint32_t lo = FAST ? rawkey(kw[q]) : kw[q] & 0xFFFFu;
+        const uint32_t hi = FAST ? rawkey(kw[q] >> 16) : kw[q] >> 16;
+        if (lo >= R) append(lo, i0 + 2 * q);
+        if (hi >= R) append(hi, i0 + 2 * q + 1);
       }
     }
+  };
+  auto pair_of = [&](uint32_t R) -> uint32_t {            // raw bf16 bits of key R in both halves; -inf when R is below it
+    const uint32_t b = R <= kKeyNegInf ? 0xFF80u : ((R & 0x8000u) ? (R & 0x7FFFu) : (~R & 0xFFFFu));
+    return b | (b << 16);
   };
   // kk-th largest of the listed keys -> new threshold, compacted list
   auto raise = [&](int n) {
@@ -267,9 +349,9 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
     unsigned long long e[EPT];
 #pragma unroll
     for (int j = 0; j < EPT; ++j) e[j] = tid + j * GS < n ? sm.list[tid + j * GS] : 0ull;
-    const uint32_t prefix = kth_listed<G>(sm, n, kk);
+    const uint32_t prefix = kth_listed<G, 8>(sm, n, kk);
     if (tid == 0) {
-      sm.thr = fast ? class_floor(prefix, x.temp, &sm.flag) : prefix;
+      sm.thr = FAST ? class_floor(prefix, x.temp, &sm.flag) : prefix;
       sm.n = 0;
     }
     G::sync();
@@ -285,21 +367,29 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
   uint32_t cur[4][4];
   {
     uint4 w[4];
+    load_chunk(0, w);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) w[j] = load(j * GS + tid);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) keys(w[j], j * GS + tid, cur[j]);
+    for (int j = 0; j < 4; ++j) to_keys(w[j], j * GS + tid, cur[j]);
   }
-  uint32_t m = 0u;
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) m = __vmaxu2(m, cur[j][q]);
   {
-    sm.list[2 * tid] = static_cast<unsigned long long>(m & 0xFFFFu) << 32;
-    sm.list[2 * tid + 1] = static_cast<unsigned long long>(m >> 16) << 32;
-    const uint32_t prefix = kth_listed<G>(sm, 2 * GS, kk);
-    if (tid == 0) sm.thr = fast ? class_floor(prefix, x.temp, &sm.flag) : prefix;
+    uint32_t lo, hi;
+    if (FAST) {
+      uint32_t m = kNegInf2;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m = bmax2(m, bmax2(bmax2(cur[j][0], cur[j][1]), bmax2(cur[j][2], cur[j][3])));
+      lo = rawkey(m); hi = rawkey(m >> 16);
+    } else {
+      uint32_t m = 0u;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) m = __vmaxu2(m, cur[j][q]);
+      lo = m & 0xFFFFu; hi = m >> 16;
+    }
+    sm.list[2 * tid] = static_cast<unsigned long long>(lo) << 32;
+    sm.list[2 * tid + 1] = static_cast<unsigned long long>(hi) << 32;
+    const uint32_t prefix = kth_listed<G, 2 * GS / 32>(sm, 2 * GS, kk);
+    if (tid == 0) sm.thr = FAST ? class_floor(prefix, x.temp, &sm.flag) : prefix;
   }
   G::sync();
   // ---- stream: filter the chunk in registers while the next one is in flight
@@ -307,16 +397,14 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
   for (int c = 0; c < nchunks; ++c) {
     uint4 nxt[4];
     const bool more = c + 1 < nchunks;
-    if (more) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) nxt[j] = load((c + 1) * 4 * GS + j * GS + tid);
-    }
+    if (more) load_chunk(c + 1, nxt);
     const uint32_t R = sm.thr;
+    const uint32_t Rv2 = pair_of(R);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) filter(cur[j], c * 4 * GS + j * GS + tid, R);
+    for (int j = 0; j < 4; ++j) filter(cur[j], c * 4 * GS + j * GS + tid, R, Rv2);
     if (more) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) keys(nxt[j], (c + 1) * 4 * GS + j * GS + tid, cur[j]);
+      for (int j = 0; j < 4; ++j) to_keys(nxt[j], (c + 1) * 4 * GS + j * GS + tid, cur[j]);
     }
     G::sync();
     const int n = sm.n;
@@ -336,7 +424,7 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
     if (tid < n_extra) {
       const int i = tid < head ? tid : tail0 + (tid - head);
       const float v = bf2f(x.row[i]);
-      const uint32_t sk = fast ? (rawkeys2(__float_as_uint(v) >> 16) & 0xFFFFu) : key16(x.xf(v, i));
+      const uint32_t sk = FAST ? rawkey(__float_as_uint(v) >> 16) : key16(x.xf(v, i));
       if (sk >= R) append(sk, i);
     }
   }
@@ -350,27 +438,38 @@ __device__ int select_topk(const RowXform& x, int k, SelSmem<G>& sm) {
   }
   const int n = sm.n;
   // ---- listed keys -> final entries
+  auto final_key = [&](unsigned long long l) -> uint32_t {
+    const uint32_t sk = static_cast<uint32_t>(l >> 32);
+    if (!FAST) return sk;
+    return x.banned(static_cast<int>(l & 0xFFFFFFFFu)) ? 0u : key16(rbf(unkey16(sk) / x.temp));
+  };
+  if constexpr (G::kSize == 32) if (k > 1 && n <= 64 && V <= 65536) {
+    uint32_t e32[2];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      e32[r] = 0xFFFFFFFFu;
+      if (tid + 32 * r < n) {
+        const unsigned long long l = sm.list[tid + 32 * r];
+        const uint32_t fk = final_key(l);
+        if (fk > kKeyNegInf) e32[r] = ((0xFFFFu - fk) << 16) | static_cast<uint32_t>(l & 0xFFFFu);
+      }
+    }
+    G::sync();
+    return warp_sort64(reinterpret_cast<SelSmem<WarpG>&>(sm), e32[0], e32[1], k);
+  }
   int n2 = 1;
   while (n2 < n) n2 <<= 1;
-  bool nan_seen = false;
   unsigned long long best = ~0ull;
   for (int i = tid; i < n2; i += GS) {
     unsigned long long e = ~0ull;
     if (i < n) {
       const unsigned long long l = sm.list[i];
-      const uint32_t sk = static_cast<uint32_t>(l >> 32);
-      const int idx = static_cast<int>(l & 0xFFFFFFFFu);
-      uint32_t fk = sk;
-      if (fast) {
-        if (sk > kKeyPosInf) nan_seen = true;
-        fk = x.banned(idx) ? 0u : key16(rbf(unkey16(sk) / x.temp));
-      }
-      if (fk > kKeyNegInf) e = (static_cast<unsigned long long>(0xFFFFu - fk) << 32) | static_cast<uint32_t>(idx);
+      const uint32_t fk = final_key(l);
+      if (fk > kKeyNegInf) e = (static_cast<unsigned long long>(0xFFFFu - fk) << 32) | (l & 0xFFFFFFFFull);
     }
     if (k > 1) sm.list[i] = e;
     best = e < best ? e : best;
   }
-  if (G::sum(nan_seen, sm.scratch)) return -1;
   if (k == 1) {
     best = G::min64(best, sm.red);
     if (tid == 0) sm.list[0] = best;
@@ -435,6 +534,7 @@ __device__ int draw_sorted(const unsigned long long* cand, int n, float top_p, f
   if (top_p < 1.0f) {
     if (tid == 0) {
       float sum = 0.f;
+#pragma unroll 4
       for (int j = 0; j < n; ++j) sum += ebuf[j];
       pbuf[n] = sum;
     }
@@ -460,6 +560,7 @@ __device__ int draw_sorted(const unsigned long long* cand, int n, float top_p, f
   }
   if (tid == 0) {
     float sum2 = 0.f;
+#pragma unroll 4
     for (int j = 0; j < keep; ++j) sum2 += ebuf[j];
     pbuf[n] = sum2;
   }
@@ -469,6 +570,7 @@ __device__ int draw_sorted(const unsigned long long* cand, int n, float top_p, f
   G::sync();
   if (tid == 0) {
     float total = 0.f;
+#pragma unroll 4
     for (int j = 0; j < keep; ++j) total += pbuf[j];
     const float target = u * total;
     float run2 = 0.f;
