@@ -155,9 +155,10 @@ def cpu_baseline(decode_steps: int = 3):
 # dominant kernel: the decode-orientation tcgen05 GEMM streaming one layer's gate/up weights
 # ------------------------------------------------------------------------------------------------
 def time_dominant_kernel(model, batch, iters=3):
-    """Times gemm_tc_kernel on the largest per-layer decode GEMM (gate|up: [2I, H] weights, M = batch),
-    cycling over all layers' weights so every launch streams from HBM (36 x 201 MB >> 126 MB L2).
-    Returns (avg ms per launch, algorithmic bytes per launch)."""
+    """Times gemm_dec_kernel on the largest per-layer decode GEMM (gate|up: [2I, H] weights, M = batch) the way the
+    engine launches it (mt_gemm with out_splits: fp32 split-K partials left for the consumer kernel, ONE kernel per
+    call), cycling over all layers' weights so every launch streams from HBM (36 x 201 MB >> 126 MB L2).
+    Returns (avg ms per launch, algorithmic bytes per launch, splits, avg ms incl. the stand-alone reduce kernel)."""
     import ctypes as C
     from moss_tts_b200 import _lib as L
     cfg = model.config
@@ -167,27 +168,33 @@ def time_dominant_kernel(model, batch, iters=3):
     out = torch.empty(batch, N, dtype=torch.bfloat16, device=dev)
     ws = torch.empty(96 << 20, dtype=torch.uint8, device=dev)
     sp = L.stream_ptr(dev)
+    splits = C.c_int(0)
 
-    def launch(w):
+    def launch(w, partial):
         a = L.GemmArgs(L.MT_DTYPE_BF16, L.MT_DTYPE_BF16, batch, N, H, x.data_ptr(), H, w.data_ptr(), H, out.data_ptr(), N,
                        None, 0, None, 0, None, 0, ws.data_ptr(), ws.numel(),
-                       L.MT_GEMM_W_STATIC | (L.MT_GEMM_W_TILED if model.weights_tiled else 0))
+                       L.MT_GEMM_W_STATIC | (L.MT_GEMM_W_TILED if model.weights_tiled else 0),
+                       C.pointer(splits) if partial else None)
         L.check(L.lib().mt_gemm(C.byref(a), sp), "mt_gemm")
-    for w in model._w["gu"]:
-        launch(w)                                  # warm-up pass
-    torch.cuda.synchronize(dev)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    n = 0
-    for _ in range(iters):
+
+    def run(partial):
         for w in model._w["gu"]:
-            launch(w)
-            n += 1
-    e1.record()
-    torch.cuda.synchronize(dev)
-    ms = e0.elapsed_time(e1) / n                  # includes the split-K reduce kernel of each call
-    alg = N * H * 2 + batch * H * 2 + batch * N * 2
-    return ms, alg
+            launch(w, partial)                         # warm-up pass
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        n = 0
+        for _ in range(iters):
+            for w in model._w["gu"]:
+                launch(w, partial)
+                n += 1
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / n
+    ms_full = run(False)                               # finished bf16 tensor: GEMM + split-K reduce kernel
+    ms = run(True)                                     # the kernel alone, as inside a decode step
+    alg = N * H * 2 + batch * H * 2 + splits.value * batch * N * 4
+    return ms, alg, splits.value, ms_full
 
 
 def ncu_traffic():
@@ -296,7 +303,7 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     hbm, tflops, src = measured_peaks()
-    k_ms, k_bytes = time_dominant_kernel(model, B)
+    k_ms, k_bytes, k_splits, k_ms_full = time_dominant_kernel(model, B)
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
     weight_bytes = sum(t.numel() for k in ("qkv", "o", "gu", "down") for t in model._w[k]) * 2 + \
         (model._w["text_head"].numel() + model._w["audio_heads"].numel()) * 2
@@ -319,8 +326,10 @@ def run_ours(args):
         "decode_ms_per_step": dec_med, "prefill_ms": prefill_ms, "codec_ms": codec_ms,
         "decode_weight_stream_gbs": weight_bytes / (dec_med * 1e-3) / 1e9 if dec_med == dec_med else None,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                     "traffic": ncu_traffic(), "kernel": "gemm_dec_kernel<BN=64,bf16> gate|up decode GEMM (M=%d,N=%d,K=%d) through mt_gemm, incl. its split-K reduce kernel" % (B, 2 * cfg.intermediate_size, cfg.hidden_size),
-                     "ms_per_launch": k_ms, "algorithmic_bytes": k_bytes, "peak_source": src},
+                     "traffic": ncu_traffic(), "kernel": "gemm_dec_kernel<BN=64,bf16> gate|up decode GEMM (M=%d,N=%d,K=%d) through mt_gemm as the engine "
+                               "launches it: %d split-K fp32 partial slabs left for the fused consumer" % (B, 2 * cfg.intermediate_size, cfg.hidden_size, k_splits),
+                     "ms_per_launch": k_ms, "algorithmic_bytes": k_bytes, "peak_source": src,
+                     "ms_per_call_with_own_reduce_kernel": k_ms_full},
         "clocks": clocks,
     }
     if not args.no_cpu:

@@ -94,6 +94,10 @@ typedef struct {
   int round_bf16;                  /* round v to bf16 before the residual add */
   float* workspace; long long workspace_bytes; /* split-K partials; may be NULL (no split-K) */
   int impl;                        /* MT_GEMM_AUTO | MT_GEMM_SIMT */
+  int* out_splits;                 /* NULL: `out` receives the finished tensor (a split-K GEMM runs its own reduce kernel).
+                                    * non-NULL (host int): the way the engines call it - the kernel leaves fp32 partials
+                                    * [splits][M][N] in `workspace`, *out_splits = splits (>= 1), `out` is not written and
+                                    * the consumer kernel (add_rmsnorm / silu_mul / attention) sums the slabs. */
 } mt_gemm_args;
 int mt_gemm(const mt_gemm_args* a, mt_stream s);
 

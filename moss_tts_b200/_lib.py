@@ -37,7 +37,8 @@ class GemmArgs(C.Structure):
                 ("x", C.c_void_p), ("ldx", C.c_longlong), ("w", C.c_void_p), ("ldw", C.c_longlong),
                 ("out", C.c_void_p), ("ldo", C.c_longlong), ("bias", C.c_void_p), ("act", C.c_int),
                 ("residual", C.c_void_p), ("ldr", C.c_longlong), ("scale", C.c_void_p), ("round_bf16", C.c_int),
-                ("workspace", C.c_void_p), ("workspace_bytes", C.c_longlong), ("impl", C.c_int)]
+                ("workspace", C.c_void_p), ("workspace_bytes", C.c_longlong), ("impl", C.c_int),
+                ("out_splits", C.POINTER(C.c_int))]
 
 
 class LMConfigC(C.Structure):

@@ -28,6 +28,8 @@ extern "C" int mt_gemm(const mt_gemm_args* a, mt_stream s) {
   p.bias = a->bias; p.act = a->act; p.residual = a->residual; p.ldr = a->ldr; p.scale = a->scale;
   p.round_bf16 = a->round_bf16; p.workspace = a->workspace; p.workspace_bytes = a->workspace_bytes;
   p.impl = a->impl & MT_GEMM_SIMT;
+  p.out_splits = a->out_splits;
+  MT_CHECK(!a->out_splits || (a->M <= 256 && a->workspace), "mt_gemm: out_splits needs M <= 256 and a workspace");
   p.w_static = (a->impl & MT_GEMM_W_STATIC) != 0;
   p.w_tiled = (a->impl & MT_GEMM_W_TILED) != 0;
   return linear(p, reinterpret_cast<cudaStream_t>(s));

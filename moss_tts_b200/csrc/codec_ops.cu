@@ -46,57 +46,97 @@ int rvq_fold_tables(const float* codebook, const float* q_g, const float* q_v, c
 
 // ---------------------------------------------------------------------------------------------
 // out[frame, :] = bias + sum_{q<nq} table[q][codes[q, frame]][:]     (quantizer order, fp32)
-// One block per frame, float4 lanes over the channel dim: every table row read is a coalesced
-// 16 B/lane gather; the table (nq*cs*code_dim*4 B ~ 100 MB) lives in L2/HBM.
+// HBM/L2-bound gather-sum: nq * code_dim * 4 B gathered + code_dim * 4 B written per frame (101,376 B at nq = 32,
+// code_dim = 768).  One block = kRvqFrames consecutive frames, one float4 lane per 4 channels.  The block's
+// nq x kRvqFrames codes are staged once into shared memory (each quantizer's codes for the block are one 32 B
+// sector), then every thread keeps 8 independent 16 B table gathers in flight per frame (the table rows of 8
+// quantizers), summed in quantizer order.  Channel-major output ([B, code_dim, T], the reference's layout for
+// decode_codes) writes one float4 of 4 consecutive frames per channel when T % 4 == 0.
 // ---------------------------------------------------------------------------------------------
-__global__ void rvq_dequant_kernel(const int64_t* __restrict__ codes, const float* __restrict__ table,
-                                   const float* __restrict__ bias, int nq, long long q_stride, int T, int cs,
-                                   int code_dim, int channel_major, float* __restrict__ out) {
-  const long long f = blockIdx.x;
+constexpr int kRvqFrames = 4;
+__global__ void __launch_bounds__(256)
+rvq_dequant_kernel(const int64_t* __restrict__ codes, const float* __restrict__ table, const float* __restrict__ bias,
+                   int nq, long long q_stride, long long frames, int T, int cs, int code_dim, int channel_major,
+                   float* __restrict__ out) {
+  extern __shared__ int s_code[];   // [nq][kRvqFrames]
+  const long long f0 = blockIdx.x * static_cast<long long>(kRvqFrames);
+  const int nf = frames - f0 < kRvqFrames ? static_cast<int>(frames - f0) : kRvqFrames;
+  for (int i = threadIdx.x; i < nq * kRvqFrames; i += blockDim.x) {
+    const int q = i / kRvqFrames, j = i % kRvqFrames;
+    long long code = j < nf ? codes[q * q_stride + f0 + j] : 0;
+    code = code < 0 ? 0 : (code >= cs ? cs - 1 : code);
+    s_code[i] = static_cast<int>(code);
+  }
+  __syncthreads();
   const int c4 = threadIdx.x;
   if (c4 * 4 >= code_dim) return;
-  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-  for (int q = 0; q < nq; ++q) {
-    long long code = codes[q * q_stride + f];
-    code = code < 0 ? 0 : (code >= cs ? cs - 1 : code);
-    const float4 v = *reinterpret_cast<const float4*>(table + (static_cast<long long>(q) * cs + code) * code_dim + c4 * 4);
-    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-  }
   const float4 b = *reinterpret_cast<const float4*>(bias + c4 * 4);
-  acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
-  if (!channel_major) {
-    *reinterpret_cast<float4*>(out + f * code_dim + c4 * 4) = acc;
-  } else {
-    const long long bidx = f / T, t = f % T;
-    float* o = out + (bidx * code_dim + c4 * 4) * T + t;
-    o[0] = acc.x; o[T] = acc.y; o[2 * static_cast<long long>(T)] = acc.z; o[3 * static_cast<long long>(T)] = acc.w;
+  const float* tcol = table + c4 * 4;
+  float4 acc[kRvqFrames];
+#pragma unroll
+  for (int j = 0; j < kRvqFrames; ++j) {
+    acc[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (j >= nf) continue;
+    for (int q0 = 0; q0 < nq; q0 += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int q = q0 + u;
+        v[u] = q < nq ? __ldg(reinterpret_cast<const float4*>(
+                            tcol + (static_cast<long long>(q) * cs + s_code[q * kRvqFrames + j]) * code_dim))
+                      : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { acc[j].x += v[u].x; acc[j].y += v[u].y; acc[j].z += v[u].z; acc[j].w += v[u].w; }
+    }
+    acc[j].x += b.x; acc[j].y += b.y; acc[j].z += b.z; acc[j].w += b.w;
   }
+  if (!channel_major) {
+#pragma unroll
+    for (int j = 0; j < kRvqFrames; ++j)
+      if (j < nf) __stcs(reinterpret_cast<float4*>(out + (f0 + j) * code_dim + c4 * 4), acc[j]);
+  } else if ((T & 3) == 0 && nf == kRvqFrames) {      // 4 consecutive frames of one utterance: 16 B per channel
+    const long long bidx = f0 / T, t = f0 % T;
+    float* o = out + (bidx * code_dim + c4 * 4) * T + t;
+    __stcs(reinterpret_cast<float4*>(o), make_float4(acc[0].x, acc[1].x, acc[2].x, acc[3].x));
+    __stcs(reinterpret_cast<float4*>(o + T), make_float4(acc[0].y, acc[1].y, acc[2].y, acc[3].y));
+    __stcs(reinterpret_cast<float4*>(o + 2ll * T), make_float4(acc[0].z, acc[1].z, acc[2].z, acc[3].z));
+    __stcs(reinterpret_cast<float4*>(o + 3ll * T), make_float4(acc[0].w, acc[1].w, acc[2].w, acc[3].w));
+  } else {
+#pragma unroll
+    for (int j = 0; j < kRvqFrames; ++j) {
+      if (j >= nf) continue;
+      const long long bidx = (f0 + j) / T, t = (f0 + j) % T;
+      float* o = out + (bidx * code_dim + c4 * 4) * T + t;
+      o[0] = acc[j].x; o[T] = acc[j].y; o[2ll * T] = acc[j].z; o[3ll * T] = acc[j].w;
+    }
+  }
+}
+
+static int rvq_launch(const int64_t* codes, const float* table, const float* bias, int nq, long long q_stride,
+                      long long frames, int T, int cs, int code_dim, int channel_major, float* out, cudaStream_t s) {
+  MT_CHECK(code_dim % 4 == 0 && code_dim / 4 <= 256, "rvq_dequant: code_dim must be a multiple of 4 and <= 1024");
+  MT_CHECK(nq > 0 && nq <= 1024, "rvq_dequant: bad quantizer count %d", nq);
+  if (frames == 0) return MT_OK;
+  const int threads = ((code_dim / 4 + 31) / 32) * 32;
+  const long long blocks = (frames + kRvqFrames - 1) / kRvqFrames;
+  rvq_dequant_kernel<<<static_cast<unsigned>(blocks), threads, nq * kRvqFrames * sizeof(int), s>>>(
+      codes, table, bias, nq, q_stride, frames, T, cs, code_dim, channel_major, out);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
 }
 
 int rvq_dequant(const int64_t* codes, const float* table, const float* bias, int nq, int B, int T, int cs, int code_dim,
                 int channel_major, float* out, cudaStream_t s) {
-  MT_CHECK(code_dim % 4 == 0 && code_dim / 4 <= 1024, "rvq_dequant: code_dim must be a multiple of 4 and <= 4096");
   const long long frames = static_cast<long long>(B) * T;
-  if (frames == 0) return MT_OK;
-  const int threads = ((code_dim / 4 + 31) / 32) * 32;
-  rvq_dequant_kernel<<<static_cast<unsigned>(frames), threads, 0, s>>>(codes, table, bias, nq, frames, T, cs, code_dim,
-                                                                       channel_major, out);
-  count_launch();
-  MT_LAUNCH_CHECK();
-  return MT_OK;
+  return rvq_launch(codes, table, bias, nq, frames, frames, T, cs, code_dim, channel_major, out, s);
 }
 
 // token-major output for `frames` consecutive frames of a [nq, q_stride] code matrix
 int rvq_dequant_strided(const int64_t* codes, const float* table, const float* bias, int nq, long long q_stride,
                         long long frames, int cs, int code_dim, float* out, cudaStream_t s) {
-  MT_CHECK(code_dim % 4 == 0 && code_dim / 4 <= 1024, "rvq_dequant: code_dim must be a multiple of 4 and <= 4096");
-  if (frames == 0) return MT_OK;
-  const int threads = ((code_dim / 4 + 31) / 32) * 32;
-  rvq_dequant_kernel<<<static_cast<unsigned>(frames), threads, 0, s>>>(codes, table, bias, nq, q_stride, 1, cs,
-                                                                       code_dim, 0, out);
-  count_launch();
-  MT_LAUNCH_CHECK();
-  return MT_OK;
+  return rvq_launch(codes, table, bias, nq, q_stride, frames, 1, cs, code_dim, 0, out, s);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -1,5 +1,6 @@
-"""Standalone roofline of the sampler (SURVEY.md §8d "sampling"): mt_sample_tokens over many rows so that the
-logits (one read, the algorithmic bytes) exceed L2.  Prints one JSON line per case.
+"""Standalone rooflines of the HBM-bound small kernels (SURVEY.md §8d "sampling", "RVQ dequant"):
+mt_sample_tokens over many rows so that the logits (one read, the algorithmic bytes) exceed L2, and mt_rvq_dequant at
+the released codec shape over config 3's largest case (B = 256, T = 750).  Prints one JSON line per case.
 
   python scripts/bench_sampling.py [--rows 2048] [--iters 5]
 """
@@ -20,7 +21,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=2048)
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--what", default="all", choices=["all", "sampling", "rvq"])
     args = ap.parse_args()
+    if args.what in ("all", "rvq"):
+        rvq(args)
+    if args.what == "rvq":
+        return
     from moss_tts_b200 import _lib as L
     from moss_tts_b200.inference_utils import sample_token
     import bench
@@ -67,6 +73,45 @@ def main():
                           "note": "logits larger than L2 (%.0f MB); mt_sample_tokens called through the C ABI, bitmap / uniforms prepared once" % (logits.numel() * 2 / 1e6)}),
               flush=True)
         del logits
+
+
+def rvq(args):
+    """a10: gather-sum over the folded [nq, 1024, 768] fp32 table (folded-table formulation: nq*768*4 B gathered +
+    768*4 B written + nq*8 B of codes per frame)."""
+    import ctypes as C
+    from moss_tts_b200 import _lib as L
+    from moss_tts_b200.config import CodecConfig
+    from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+    import bench
+    hbm, _, src = bench.measured_peaks()
+    dev = torch.device("cuda", 0)
+    ccfg = CodecConfig.released()
+    codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=1 << 30)
+    nq, D = ccfg.num_quantizers, ccfg.code_dim
+    for B, T in ((64, 125), (256, 750)):
+        codes = torch.randint(0, 1024, (nq, B, T), device=dev)
+        out = torch.empty(B * T * D, dtype=torch.float32, device=dev)
+        for cm, name in ((0, "token-major [B*T,768] (the decoder's input)"), (1, "channel-major [B,768,T] (decode_codes)")):
+            def call():
+                L.check(L.lib().mt_rvq_dequant(codec._engine, L.ptr(codes), nq, B, T, cm, L.ptr(out), L.stream_ptr(dev)),
+                        "mt_rvq_dequant")
+            for _ in range(2):
+                call()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.iters):
+                call()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / args.iters
+            nbytes = B * T * (nq * D * 4 + D * 4 + nq * 8)
+            print(json.dumps({"case": "rvq dequant " + name, "B": B, "T": T, "nq": nq, "ms": ms, "algorithmic_bytes": nbytes,
+                              "achieved_gbs": nbytes / (ms * 1e-3) / 1e9, "peak_gbs": hbm,
+                              "frac": nbytes / (ms * 1e-3) / 1e9 / hbm, "peak_source": src,
+                              "note": "folded table 100.7 MB (fits the 126 MB L2 only partly next to %.0f MB of output per call); "
+                                      "gather bytes are algorithmic, an L2 hit is not an HBM read" % (B * T * D * 4 / 1e6)}),
+                  flush=True)
 
 
 if __name__ == "__main__":

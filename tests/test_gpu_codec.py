@@ -43,7 +43,7 @@ def test_rvq_dequant(mini):
     assert np.abs(emb3 - g["emb_nq3"]).max() <= RVQ_TOL * max(1.0, scale)
 
 
-@pytest.mark.parametrize("B,T", [(1, 1), (3, 13), (2, 125), (1, 300)])
+@pytest.mark.parametrize("B,T", [(1, 1), (3, 13), (2, 125), (1, 300), (2, 64), (5, 6)])
 def test_rvq_dequant_shapes(mini, B, T):
     g, cfg, w, model, oracle = mini
     codes = torch.randint(0, cfg.codebook_size, (cfg.num_quantizers, B, T), generator=torch.Generator().manual_seed(T))

@@ -54,6 +54,27 @@ def test_gemm_bf16_splitk_matches_unsplit(M, N, K):
     assert (b - ref).abs().max().item() <= 2e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(64, 24576, 4096), (8, 512, 12288), (64, 384, 512)])
+def test_gemm_partials_for_fused_consumer(M, N, K):
+    """mt_gemm_args.out_splits: the engines' calling form - fp32 slabs [splits][M][N] in the workspace, no reduce kernel."""
+    import ctypes as C
+    g = torch.Generator(device=DEV).manual_seed(5)
+    x = torch.randn(M, K, device=DEV, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(torch.bfloat16)
+    ws = torch.zeros(96 << 20, dtype=torch.uint8, device=DEV)
+    out = torch.full((M, N), 7.0, dtype=torch.bfloat16, device=DEV)
+    splits = C.c_int(0)
+    n0 = L.launch_count()
+    a = L.GemmArgs(L.MT_DTYPE_BF16, L.MT_DTYPE_BF16, M, N, K, x.data_ptr(), K, w.data_ptr(), K, out.data_ptr(), N,
+                   None, 0, None, 0, None, 0, ws.data_ptr(), ws.numel(), L.MT_GEMM_AUTO, C.pointer(splits))
+    L.check(L.lib().mt_gemm(C.byref(a), L.stream_ptr(torch.device(DEV))), "mt_gemm")
+    torch.cuda.synchronize()
+    assert L.launch_count() - n0 == 1 and splits.value >= 1
+    part = ws.view(torch.float32)[: splits.value * M * N].view(splits.value, M, N)
+    assert (part.sum(0) - _ref(x, w)).abs().max().item() <= 2e-3
+    assert (out == 7.0).all()                      # `out` is left to the consumer
+
+
 @pytest.mark.parametrize("M,N,K", [(32, 768, 512), (250, 1280, 768), (1000, 3072, 768), (700, 240, 768)])
 @pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
 def test_gemm_tf32_epilogues(M, N, K, impl):
