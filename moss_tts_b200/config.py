@@ -124,6 +124,9 @@ class CodecConfig:
     codebook_dim: int = 8
     max_period: float = 10000.0
     stages: List[CodecStage] = field(default_factory=list)
+    # encoder side: same CodecStage record, but `patch_size` is the DOWNsample applied BEFORE the
+    # stage (PatchedPretransform.encode :936-944) and `input_dim` the width after it.  Empty = decode-only codec.
+    enc_stages: List[CodecStage] = field(default_factory=list)
 
     @property
     def frame_rate(self) -> float:
@@ -131,6 +134,22 @@ class CodecConfig:
 
     def to_dict(self):
         return asdict(self)
+
+    @staticmethod
+    def from_dict(d: dict) -> "CodecConfig":
+        d = dict(d)
+        stages = [CodecStage(**s) for s in d.pop("stages")]
+        enc = [CodecStage(**s) for s in d.pop("enc_stages", [])]
+        return CodecConfig(stages=stages, enc_stages=enc, **d)
+
+    def with_encoder(self, dims, patch_sizes) -> "CodecConfig":
+        """Adds encoder stages; dims = (input_dim after the patch, d_model, heads, layers, ff, output_dim) per stage."""
+        rate = float(self.sampling_rate)
+        self.enc_stages = []
+        for (inp, d, h, L, ff, out), p in zip(dims, patch_sizes):
+            rate /= p
+            self.enc_stages.append(CodecStage(inp, d, h, L, ff, out, p, int(rate * self.context_duration)))
+        return self
 
     @staticmethod
     def _build(dims, sampling_rate, context_duration, code_dim, rvq_dim, num_quantizers, patch_sizes):
@@ -154,7 +173,11 @@ class CodecConfig:
                 (640, 768, 12, 12, 3072, 768),
                 (384, 768, 12, 12, 3072, 768),
                 (384, 768, 12, 12, 3072, 240)]
-        return CodecConfig._build(dims, 24000, 10.0, 768, 512, 32, [2, 2, 2, 240])
+        enc = [(240, 768, 12, 12, 3072, 384),        # encoder_kwargs of config.json:93-176
+               (768, 768, 12, 12, 3072, 384),
+               (768, 768, 12, 12, 3072, 640),
+               (1280, 1280, 20, 32, 5120, 768)]
+        return CodecConfig._build(dims, 24000, 10.0, 768, 512, 32, [2, 2, 2, 240]).with_encoder(enc, [240, 2, 2, 2])
 
     @staticmethod
     def mini(context_duration: float = 1.0, num_quantizers: int = 8) -> "CodecConfig":
@@ -164,4 +187,9 @@ class CodecConfig:
                 (64, 128, 2, 1, 256, 128),
                 (64, 64, 1, 1, 128, 64),
                 (32, 64, 1, 1, 128, 240)]
-        return CodecConfig._build(dims, 24000, context_duration, 96, 64, num_quantizers, [2, 2, 2, 240])
+        enc = [(240, 64, 1, 1, 128, 32),
+               (64, 64, 1, 1, 128, 64),
+               (128, 128, 2, 1, 256, 64),
+               (128, 128, 2, 2, 256, 96)]
+        return CodecConfig._build(dims, 24000, context_duration, 96, 64, num_quantizers,
+                                  [2, 2, 2, 240]).with_encoder(enc, [240, 2, 2, 2])

@@ -1,5 +1,5 @@
-"""Oracle for MOSS-Audio-Tokenizer's decode side and the processor's de-delay glue
-(TEST INFRASTRUCTURE ONLY).
+"""Oracle for MOSS-Audio-Tokenizer (decode side; encode side = SURVEY.md §8f rank 1) and the processor's
+de-delay glue (TEST INFRASTRUCTURE ONLY).
 
 Restates reference moss_audio_tokenizer/modeling_moss_audio_tokenizer.py
   ResidualLFQ.decode_codes :1276-1283, LFQ.decode_code :1065-1074, WNConv1d :967-969
@@ -8,6 +8,8 @@ Restates reference moss_audio_tokenizer/modeling_moss_audio_tokenizer.py
   LayerScale :230-234, PatchedPretransform.decode :947-953,
   _decode_frame :1513-1534, decode :1650-1755 (incl. the chunked path's RingKVCache
   :413-480 semantics), batch_decode :1431-1475
+  encode side: PatchedPretransform.encode :936-944, _encode_frame :1478-1511, ResidualLFQ.forward :1238-1274,
+  LFQ.forward / decode_latents :1055-1092, encode :1536-1648, batch_encode :1403-1429
 and reference moss_tts_delay/processing_moss_tts.py
   apply_delay_pattern :516-525, apply_de_delay_pattern :528-537,
   _parse_audio_codes :668-709, decode_audio_codes :880-930.
@@ -133,10 +135,10 @@ class OracleCodec:
             vis = vis & (kp >= start + ln - context)      # ring capacity == context (:597-600)
         return vis
 
-    def _stage(self, s: int, x: torch.Tensor, chunk_frames: Optional[int], up: int) -> torch.Tensor:
+    def _stage(self, s: int, x: torch.Tensor, chunk_frames: Optional[int], up: int, enc: bool = False) -> torch.Tensor:
         """x [B, input_dim, T] -> [B, output_dim, T]."""
-        st = self.cfg.stages[s]
-        base = f"decoder.{2 * s}."
+        st = self.cfg.enc_stages[s] if enc else self.cfg.stages[s]
+        base = f"encoder.{2 * s + 1}." if enc else f"decoder.{2 * s}."
         x = x.transpose(1, 2)
         if st.input_dim != st.d_model:
             x = x @ self.w[base + "input_proj.weight"].T
@@ -170,6 +172,86 @@ class OracleCodec:
         for j in range(h):
             out[:, :, j::h] = x[:, j::h, :]
         return out
+
+    @staticmethod
+    def _patch(x: torch.Tensor, h: int) -> torch.Tensor:
+        """PatchedPretransform.encode :936-944: out[b, d*h + j, l] = in[b, d, l*h + j]."""
+        B, d, Lh = x.shape
+        out = torch.empty(B, d * h, Lh // h)
+        for j in range(h):
+            out[:, j::h, :] = x[:, :, j::h]
+        return out
+
+    @torch.no_grad()
+    def quantize(self, e: torch.Tensor, lengths: torch.Tensor, nq: Optional[int] = None, return_margins: bool = False):
+        """ResidualLFQ.forward :1238-1274 with LFQ.forward / decode_latents :1055-1092.
+        e [B, code_dim, T] fp32, lengths [B] (frames) -> codes [nq, B, T] int64 (+ per-code margin between the best and
+        the second-best negative distance, for near-tie classification in the GPU tests)."""
+        c = self.cfg
+        nq = nq or c.num_quantizers
+        p = "quantizer.input_proj."
+        Wi = self._wn(self.w[p + "parametrizations.weight.original0"], self.w[p + "parametrizations.weight.original1"])
+        z = torch.einsum("oc,bct->bot", Wi, e.float()) + self.w[p + "bias"][None, :, None]
+        B, _, T = z.shape
+        mask = (torch.arange(T)[None, :] < lengths[:, None]).unsqueeze(1).float()
+        residual = z.clone()
+        codes, margins = [], []
+        for q in range(nq):
+            p = f"quantizer.quantizers.{q}."
+            Win = self._wn(self.w[p + "in_proj.parametrizations.weight.original0"],
+                           self.w[p + "in_proj.parametrizations.weight.original1"])     # [cb_dim, rvq]
+            Wout = self._wn(self.w[p + "out_proj.parametrizations.weight.original0"],
+                            self.w[p + "out_proj.parametrizations.weight.original1"])   # [rvq, cb_dim]
+            z_e = torch.einsum("oc,bct->bot", Win, residual * mask) + self.w[p + "in_proj.bias"][None, :, None]
+            enc = F.normalize(z_e.transpose(1, 2).reshape(-1, c.codebook_dim))
+            cb = self.w[p + "codebook.weight"]
+            cbn = F.normalize(cb)
+            dist = enc.pow(2).sum(1, keepdim=True) - 2 * enc @ cbn.t() + cbn.pow(2).sum(1, keepdim=True).t()
+            neg = -dist
+            idx = neg.max(1)[1]
+            if return_margins:
+                top2 = neg.topk(2, dim=1).values
+                margins.append((top2[:, 0] - top2[:, 1]).reshape(B, T))
+            idx = idx.reshape(B, T)
+            z_q = cb[idx].transpose(1, 2)                                                 # [B, cb_dim, T]
+            z_q = torch.einsum("oc,bct->bot", Wout, z_q) + self.w[p + "out_proj.bias"][None, :, None]
+            residual = residual - z_q * mask
+            codes.append(idx)
+        codes = torch.stack(codes) if codes else torch.empty(0, B, T, dtype=torch.long)
+        return (codes, torch.stack(margins)) if return_margins else codes
+
+    @torch.no_grad()
+    def encode_hidden(self, wav: torch.Tensor, chunk_frames: Optional[int] = None) -> torch.Tensor:
+        """Encoder stack of _encode_frame :1490-1500.  wav [B, 1, T] with T a multiple of downsample_rate
+        -> encoder_hidden_states [B, code_dim, T / downsample_rate]."""
+        c = self.cfg
+        x = wav.float()
+        down = c.downsample_rate
+        for s, st in enumerate(c.enc_stages):
+            x = self._patch(x, st.patch_size)
+            down //= st.patch_size
+            x = self._stage(s, x, chunk_frames, down, enc=True)
+        return x
+
+    @torch.no_grad()
+    def encode_frame(self, wav: torch.Tensor, lengths: Optional[torch.Tensor] = None, nq: Optional[int] = None,
+                     chunk_frames: Optional[int] = None, return_margins: bool = False):
+        """_encode_frame :1478-1511.  wav [B,1,T] or [B,T]; lengths in samples.
+        Returns (codes [nq,B,Tf], code_lengths [B], hidden [B,code_dim,Tf][, margins])."""
+        c = self.cfg
+        if wav.dim() == 2:
+            wav = wav[:, None, :]
+        B, _, T = wav.shape
+        if lengths is None:
+            lengths = torch.full((B,), T, dtype=torch.long)
+        if T % c.downsample_rate:
+            wav = F.pad(wav, (0, c.downsample_rate - T % c.downsample_rate))
+        e = self.encode_hidden(wav, chunk_frames)
+        el = lengths.clone()
+        for st in c.enc_stages:
+            el = el // st.patch_size                    # floor at every stage (:943)
+        q = self.quantize(e, el, nq, return_margins)
+        return (q[0], el, e, q[1]) if return_margins else (q, el, e)
 
     @torch.no_grad()
     def decode_frames(self, codes: torch.Tensor, chunk_frames: Optional[int] = None,

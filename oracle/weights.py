@@ -121,8 +121,20 @@ def make_codec_weights(cfg: CodecConfig, seed: int = 0, layer_scale: float = 0.3
     w[p + "parametrizations.weight.original0"] = _normal(seed, p + "g", (cfg.code_dim, 1, 1), 0.2, 1.0)
     w[p + "parametrizations.weight.original1"] = _normal(seed, p + "v", (cfg.code_dim, cfg.rvq_dim, 1), 0.05)
     w[p + "bias"] = _normal(seed, p + "b", (cfg.code_dim,), 0.05)
-    for s, st in enumerate(cfg.stages):
-        base = f"decoder.{2 * s}."
+    if cfg.enc_stages:
+        # encode-side quantiser parameters (ResidualLFQ.input_proj :1217-1219, LFQ.in_proj :1047)
+        p = "quantizer.input_proj."
+        w[p + "parametrizations.weight.original0"] = _normal(seed, p + "g", (cfg.rvq_dim, 1, 1), 0.2, 1.0)
+        w[p + "parametrizations.weight.original1"] = _normal(seed, p + "v", (cfg.rvq_dim, cfg.code_dim, 1), 0.05)
+        w[p + "bias"] = _normal(seed, p + "b", (cfg.rvq_dim,), 0.05)
+        for q in range(cfg.num_quantizers):
+            p = f"quantizer.quantizers.{q}.in_proj."
+            w[p + "parametrizations.weight.original0"] = _normal(seed, p + "g", (cfg.codebook_dim, 1, 1), 0.2, 1.0)
+            w[p + "parametrizations.weight.original1"] = _normal(seed, p + "v", (cfg.codebook_dim, cfg.rvq_dim, 1), 0.1)
+            w[p + "bias"] = _normal(seed, p + "b", (cfg.codebook_dim,), 0.05)
+    stage_list = [(f"decoder.{2 * s}.", st) for s, st in enumerate(cfg.stages)] + \
+                 [(f"encoder.{2 * s + 1}.", st) for s, st in enumerate(cfg.enc_stages)]
+    for base, st in stage_list:
         d = st.d_model
         if st.input_dim != d:
             w[base + "input_proj.weight"] = _normal(seed, base + "ip", (d, st.input_dim), st.input_dim ** -0.5)
