@@ -254,7 +254,8 @@ int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, int S0, cons
                       int64_t* gen_ids, int* n_steps, float* step_ms, mt_stream s);
 
 /* ------------------------------------------------------------------------------------------
- * MOSS-Audio-Tokenizer decode side
+ * MOSS-Audio-Tokenizer: decode side (mt_rvq_dequant, mt_codec_decode) and encode side (mt_rlfq_quantize,
+ * mt_codec_encode).  A handle is either a decoder (config.encoder = 0) or an encoder (1).
  * ------------------------------------------------------------------------------------------ */
 #define MT_CODEC_MAX_STAGES 8
 typedef struct {
@@ -264,6 +265,8 @@ typedef struct {
   int patch[MT_CODEC_MAX_STAGES], context[MT_CODEC_MAX_STAGES];
   int code_dim, rvq_dim, num_quantizers, codebook_size, codebook_dim;
   float max_period;
+  int encoder;   /* 0: decoder stages, patch[s] = upsample AFTER stage s.  1: encoder stages (encoder_kwargs order),
+                  * patch[s] = downsample BEFORE stage s and input_dim[s] the width after it. */
 } mt_codec_config;
 
 typedef struct {            /* one transformer layer, all fp32 */
@@ -275,6 +278,20 @@ typedef struct {            /* one transformer layer, all fp32 */
   const float *scale1, *scale2;   /* LayerScale [d] */
 } mt_codec_layer;
 
+/* Encode-side quantiser parameters (ResidualLFQ :1217-1236, LFQ :1046-1053), fp32 on device, weight-norm
+ * (W = g * v / ||v||, WNConv1d :967-969) already applied by the caller. */
+typedef struct {
+  const float* in_w;          /* [rvq_dim, code_dim]   quantizer.input_proj */
+  const float* in_b;          /* [rvq_dim] */
+  const float* q_in_w;        /* [nq, codebook_dim, rvq_dim]   quantizers[q].in_proj */
+  const float* q_in_b;        /* [nq, codebook_dim] */
+  const float* codebook;      /* [nq, codebook_size, codebook_dim] raw rows (what z_q is built from, :1089) */
+  const float* codebook_n;    /* [nq, codebook_size, codebook_dim] F.normalize'd rows (:1082) */
+  const float* codebook_nsq;  /* [nq, codebook_size] sum of squares of the normalised rows (:1087) */
+  const float* q_out_w;       /* [nq, rvq_dim, codebook_dim]   quantizers[q].out_proj */
+  const float* q_out_b;       /* [nq, rvq_dim] */
+} mt_codec_quant_weights;
+
 typedef struct {
   /* RVQ: folded per-quantizer tables, table[q][code][c] = W_out * (W_q * C_q[code] + b_q)   (see
    * mt_rvq_fold_tables); out_bias [code_dim]. */
@@ -283,6 +300,7 @@ typedef struct {
   const float* input_proj[MT_CODEC_MAX_STAGES];   /* [d_model, input_dim] or NULL (Identity) */
   const float* output_proj[MT_CODEC_MAX_STAGES];  /* [output_dim, d_model] or NULL */
   const mt_codec_layer* layers[MT_CODEC_MAX_STAGES];  /* host array per stage */
+  const mt_codec_quant_weights* quant;                /* encoder handles only (host struct, copied); else NULL */
 } mt_codec_weights;
 
 typedef struct mt_codec mt_codec;
@@ -309,6 +327,19 @@ int mt_rvq_dequant(const mt_codec* h, const int64_t* codes, int nq, int B, int T
  * gemm_impl: MT_GEMM_AUTO | MT_GEMM_SIMT. */
 int mt_codec_decode(mt_codec* h, const int64_t* codes, int nq, int B, int T, int chunk_frames,
                     float* wav, void* workspace, long long workspace_bytes, mt_stream s);
+
+/* ResidualLFQ.forward (:1238-1274) on encoder hidden states: hidden [B, T, code_dim] fp32 token-major,
+ * code_lengths [B] int64 device (valid frames per sample; NULL = all T) -> codes [nq, B, T] int64.
+ * The 768 -> 512 input projection and every distance run in fp32 FMA arithmetic (no TF32), ties -> lowest index.
+ * workspace: >= B*T*rvq_dim*4 bytes. */
+int mt_rlfq_quantize(mt_codec* h, const float* hidden, int B, int T, const int64_t* code_lengths, int nq,
+                     int64_t* codes, void* workspace, long long workspace_bytes, mt_stream s);
+
+/* _encode_frame (:1478-1511): wav [B, T*downsample] fp32 (zero-padded to whole frames by the caller) ->
+ * codes [nq, B, T] int64 and, if hidden != NULL, encoder_hidden_states [B, T, code_dim] fp32 token-major.
+ * chunk_frames > 0 reproduces encode(chunk_duration=...)'s streaming ring-cache visibility in one pass. */
+int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, const int64_t* code_lengths, int nq, int chunk_frames,
+                    int64_t* codes, float* hidden, void* workspace, long long workspace_bytes, mt_stream s);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -23,7 +23,7 @@ EXPORTS = [
     "mt_lm_query_sizes", "mt_lm_create", "mt_lm_destroy", "mt_lm_forward", "mt_lm_generate",
     "mt_sample_tokens", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
     "mt_codec_create", "mt_codec_destroy", "mt_codec_workspace_bytes", "mt_rvq_fold_tables",
-    "mt_rvq_dequant", "mt_codec_decode",
+    "mt_rvq_dequant", "mt_codec_decode", "mt_rlfq_quantize", "mt_codec_encode",
     "mt_local_query_sizes", "mt_local_create", "mt_local_destroy", "mt_local_forward", "mt_local_generate",
 ]
 
@@ -96,7 +96,12 @@ class CodecConfigC(C.Structure):
                [(n, _IntArr) for n in ("input_dim", "d_model", "num_heads", "num_layers", "dim_ff", "output_dim",
                                        "patch", "context")] + \
                [(n, C.c_int) for n in ("code_dim", "rvq_dim", "num_quantizers", "codebook_size", "codebook_dim")] + \
-               [("max_period", C.c_float)]
+               [("max_period", C.c_float), ("encoder", C.c_int)]
+
+
+class CodecQuantWeightsC(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("in_w", "in_b", "q_in_w", "q_in_b", "codebook", "codebook_n", "codebook_nsq",
+                                          "q_out_w", "q_out_b")]
 
 
 class CodecLayerC(C.Structure):
@@ -107,7 +112,8 @@ class CodecLayerC(C.Structure):
 class CodecWeightsC(C.Structure):
     _fields_ = [("rvq_table", C.c_void_p), ("rvq_out_bias", C.c_void_p),
                 ("input_proj", C.c_void_p * MT_CODEC_MAX_STAGES), ("output_proj", C.c_void_p * MT_CODEC_MAX_STAGES),
-                ("layers", C.POINTER(CodecLayerC) * MT_CODEC_MAX_STAGES)]
+                ("layers", C.POINTER(CodecLayerC) * MT_CODEC_MAX_STAGES),
+                ("quant", C.POINTER(CodecQuantWeightsC))]
 
 
 _lib = None

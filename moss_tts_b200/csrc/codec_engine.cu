@@ -12,7 +12,9 @@ struct mt_codec {
   mt_codec_config cfg;
   mt_codec_weights w;
   std::vector<std::vector<mt_codec_layer>> layers;
-  int upsample_total = 1;
+  int upsample_total = 1;      // product of the patch sizes (samples per frame)
+  mt_codec_quant_weights quant{};
+  bool has_quant = false;
 };
 
 namespace mt {
@@ -24,6 +26,21 @@ static void per_sample_floats(const mt_codec_config& c, int T, long long* xs, lo
                               long long* ys, long long* es) {
   long long tx = 0, tq = 0, tf = 0, ty = 0, te = static_cast<long long>(T) * c.code_dim;
   long long Ts = T;
+  if (c.encoder) {
+    // encoder: Ts shrinks; `e` holds a stage's patched input, `y` its projected output, x also the quantiser's z
+    for (int s = 0; s < c.num_stages; ++s) Ts *= c.patch[s];
+    tx = static_cast<long long>(T) * c.rvq_dim;
+    for (int s = 0; s < c.num_stages; ++s) {
+      Ts /= c.patch[s];
+      tx = std::max(tx, Ts * c.d_model[s]);
+      tq = std::max(tq, Ts * 3 * c.d_model[s]);
+      tf = std::max(tf, Ts * c.dim_ff[s]);
+      ty = std::max(ty, std::max(Ts * c.output_dim[s], Ts * 64));
+      te = std::max(te, Ts * c.input_dim[s]);
+    }
+    *xs = tx; *qkvs = tq; *ffs = tf; *ys = ty; *es = te;
+    return;
+  }
   for (int s = 0; s < c.num_stages; ++s) {
     tx = std::max(tx, Ts * c.d_model[s]);
     tq = std::max(tq, Ts * 3 * c.d_model[s]);
@@ -59,14 +76,20 @@ extern "C" int mt_codec_create(const mt_codec_config* cfg, const mt_codec_weight
       delete h;
       return fail(MT_ERR_UNSUPPORTED, "codec stage %d: head_dim must be 64", s);
     }
-    if (cfg->output_dim[s] % cfg->patch[s] != 0 || cfg->d_model[s] % 32 != 0 || cfg->input_dim[s] % 32 != 0 ||
-        cfg->dim_ff[s] % 32 != 0) {
+    // K dims of the TF32 GEMMs: rows must be 16-byte aligned for TMA; a ragged last 32-float k-block is zero-filled
+    const bool dims_ok = cfg->d_model[s] % 32 == 0 && cfg->dim_ff[s] % 32 == 0 && cfg->input_dim[s] % 4 == 0 &&
+                         (cfg->encoder ? cfg->input_dim[s] % cfg->patch[s] == 0
+                                       : (cfg->input_dim[s] % 32 == 0 && cfg->output_dim[s] % cfg->patch[s] == 0));
+    if (!dims_ok) {
       delete h;
-      return fail(MT_ERR_ARG, "codec stage %d: dims must be multiples of 32 and output_dim divisible by patch", s);
+      return fail(MT_ERR_ARG, "codec stage %d: d_model/dim_ff must be multiples of 32, input_dim of %d, and the patched "
+                              "width divisible by patch", s, cfg->encoder ? 4 : 32);
     }
     h->layers[s].assign(w->layers[s], w->layers[s] + cfg->num_layers[s]);
     h->upsample_total *= cfg->patch[s];
   }
+  if (w->quant) { h->quant = *w->quant; h->has_quant = true; h->w.quant = &h->quant; }
+  if (cfg->encoder && !h->has_quant) { delete h; return fail(MT_ERR_ARG, "mt_codec_create: an encoder handle needs quant weights"); }
   *out = h;
   return MT_OK;
 }
@@ -90,9 +113,43 @@ extern "C" int mt_rvq_fold_tables(const float* codebook, const float* q_g, const
 extern "C" int mt_rvq_dequant(const mt_codec* h, const int64_t* codes, int nq, int B, int T, int channel_major,
                               float* out, mt_stream s) {
   MT_CHECK(h && codes && out, "null argument");
+  MT_CHECK(h->w.rvq_table, "mt_rvq_dequant: this handle has no folded RVQ table (encoder handle?)");
   MT_CHECK(nq >= 0 && nq <= h->cfg.num_quantizers, "nq %d exceeds the %d quantizers of the codec", nq, h->cfg.num_quantizers);
   return rvq_dequant(codes, h->w.rvq_table, h->w.rvq_out_bias, nq, B, T, h->cfg.codebook_size, h->cfg.code_dim,
                      channel_major, out, reinterpret_cast<cudaStream_t>(s));
+}
+
+// input_proj + the transformer layers of stage `st` for nb samples x Ts tokens (M = nb*Ts rows of `in`); the stage's
+// activations are left in x [M, d_model].  `y` (y_floats floats) parks the stage's RoPE table while the layers run.
+static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, int nb, long long Ts, int chunk,
+                          float* x, float* hbuf, float* qkv, float* ff, float* y, long long y_floats, cudaStream_t s) {
+  const mt_codec_config& c = h->cfg;
+  const int d = c.d_model[st], heads = c.num_heads[st], ffd = c.dim_ff[st];
+  MT_CHECK(M < (1ll << 31), "codec: too many tokens in one group");
+  if (h->w.input_proj[st]) MT_TRY(codec_linear(in, M, c.input_dim[st], h->w.input_proj[st], d, x, d, 0, nullptr, nullptr, s));
+  else MT_CUDA(cudaMemcpyAsync(x, in, M * d * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel (+ the separate RoPE pass) as a cross-check of the TF32 one
+  static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
+  // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
+  const bool table_fits = static_cast<long long>(Ts) * 64 <= y_floats;
+  if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
+  for (int l = 0; l < c.num_layers[st]; ++l) {
+    const mt_codec_layer& L = h->layers[st][l];
+    MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s));
+    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s));
+    if (simt_attn || !table_fits) {
+      MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
+      if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+    } else {
+      MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
+    }
+    MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s));
+    MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s));
+    MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s));
+    MT_TRY(codec_linear(ff, M, ffd, L.linear2, d, x, d, 0, x, L.scale2, s));
+  }
+  return MT_OK;
 }
 
 // decode `nb` samples starting at batch offset b0 (codes are [nq, B, T]: sample stride T, quantizer stride B*T)
@@ -118,33 +175,10 @@ static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T,
   long long Ts = T;
   const float* in = e;
   for (int st = 0; st < c.num_stages; ++st) {
-    const int d = c.d_model[st], heads = c.num_heads[st], ffd = c.dim_ff[st];
+    const int d = c.d_model[st];
     const long long M = Ts * nb;
-    MT_CHECK(M < (1ll << 31), "codec: too many tokens in one group");
-    if (h->w.input_proj[st]) MT_TRY(codec_linear(in, M, c.input_dim[st], h->w.input_proj[st], d, x, d, 0, nullptr, nullptr, s));
-    else MT_CUDA(cudaMemcpyAsync(x, in, M * d * sizeof(float), cudaMemcpyDeviceToDevice, s));
-    const int chunk = chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0;
-    // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel (+ the separate RoPE pass) as a cross-check of the TF32 one
-    static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
-    // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
-    const bool table_fits = static_cast<long long>(Ts) * 64 <= ys * nb;
-    if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
-    for (int l = 0; l < c.num_layers[st]; ++l) {
-      const mt_codec_layer& L = h->layers[st][l];
-      MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s));
-      MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s));
-      if (simt_attn || !table_fits) {
-        MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
-        if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
-        else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
-      } else {
-        MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
-      }
-      MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s));
-      MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s));
-      MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s));
-      MT_TRY(codec_linear(ff, M, ffd, L.linear2, d, x, d, 0, x, L.scale2, s));
-    }
+    MT_TRY(run_stage_layers(h, st, in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
+                            x, hbuf, qkv, ff, y, ys * nb, s));
     const bool last = st + 1 == c.num_stages;
     const int od = c.output_dim[st], p = c.patch[st];
     const bool identity_patch = od == p;           // one output channel: the reshape is the identity
@@ -168,6 +202,7 @@ static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T,
 extern "C" int mt_codec_decode(mt_codec* h, const int64_t* codes, int nq, int B, int T, int chunk_frames, float* wav,
                                void* workspace, long long workspace_bytes, mt_stream stream) {
   MT_CHECK(h && codes && wav && workspace, "mt_codec_decode: null argument");
+  MT_CHECK(!h->cfg.encoder, "mt_codec_decode: this handle is an encoder");
   MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
   MT_CHECK(B > 0 && T > 0, "mt_codec_decode: empty input B=%d T=%d", B, T);
   long long per = 0;
@@ -178,6 +213,105 @@ extern "C" int mt_codec_decode(mt_codec* h, const int64_t* codes, int nq, int B,
   for (int b0 = 0; b0 < B; b0 += static_cast<int>(group)) {
     const int nb = static_cast<int>(std::min<long long>(group, B - b0));
     MT_TRY(decode_group(h, codes, nq, B, T, b0, nb, chunk_frames, wav, reinterpret_cast<float*>(workspace), s));
+  }
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// encode side
+// ---------------------------------------------------------------------------------------------
+// hidden [M, code_dim] token-major (M = nb*T rows) -> codes[q*q_stride + m]; z: scratch of M*rvq_dim floats
+static int quantize_rows(mt_codec* h, const float* hidden, long long M, int T, const int64_t* lengths, int nq,
+                         int64_t* codes, long long q_stride, float* z, cudaStream_t s) {
+  const mt_codec_config& c = h->cfg;
+  MT_CHECK(M < (1ll << 31), "quantise: too many frames in one group");
+  const float* zin = hidden;
+  if (h->quant.in_w) {
+    // fp32 FMA arithmetic on purpose (CUDA-core GEMM): the code index is an argmax over distances of this projection;
+    // TF32 inputs would flip near-ties that the reference's fp32 conv1d resolves
+    LinearPlan p;
+    p.dtype_in = MT_DTYPE_F32; p.dtype_out = MT_DTYPE_F32;
+    p.M = static_cast<int>(M); p.N = c.rvq_dim; p.K = c.code_dim;
+    p.x = hidden; p.ldx = c.code_dim; p.w = h->quant.in_w; p.ldw = c.code_dim; p.out = z; p.ldo = c.rvq_dim;
+    p.bias = h->quant.in_b; p.impl = MT_GEMM_SIMT;
+    MT_TRY(linear(p, s));
+    zin = z;
+  } else {
+    MT_CHECK(c.rvq_dim == c.code_dim, "quantise: no input_proj but rvq_dim != code_dim");
+  }
+  return rlfq_quantize(zin, M, T, lengths, nq, c.rvq_dim, c.codebook_size, c.codebook_dim, h->quant, codes, q_stride, s);
+}
+
+extern "C" int mt_rlfq_quantize(mt_codec* h, const float* hidden, int B, int T, const int64_t* code_lengths, int nq,
+                                int64_t* codes, void* workspace, long long workspace_bytes, mt_stream stream) {
+  MT_CHECK(h && hidden && codes && workspace, "mt_rlfq_quantize: null argument");
+  MT_CHECK(h->has_quant, "mt_rlfq_quantize: this handle has no quantiser weights");
+  MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
+  MT_CHECK(B > 0 && T > 0, "mt_rlfq_quantize: empty input B=%d T=%d", B, T);
+  const long long M = static_cast<long long>(B) * T;
+  MT_CHECK(workspace_bytes >= M * h->cfg.rvq_dim * 4, "mt_rlfq_quantize: workspace too small (%lld bytes needed)",
+           M * h->cfg.rvq_dim * 4);
+  return quantize_rows(h, hidden, M, T, code_lengths, nq, codes, M, reinterpret_cast<float*>(workspace),
+                       reinterpret_cast<cudaStream_t>(stream));
+}
+
+// encode `nb` samples starting at batch offset b0: wav [B, T*samples_per_frame] -> codes [nq, B, T]
+static int encode_group(mt_codec* h, const float* wav, int B, int T, int b0, int nb, const int64_t* lengths, int nq,
+                        int chunk_frames, int64_t* codes, float* hidden_out, float* ws, cudaStream_t s) {
+  const mt_codec_config& c = h->cfg;
+  long long xs, qs, fs, ys, es;
+  per_sample_floats(c, T, &xs, &qs, &fs, &ys, &es);
+  float* x = ws;
+  float* hbuf = x + xs * nb;
+  float* qkv = hbuf + xs * nb;
+  float* ff = qkv + qs * nb;
+  float* y = ff + fs * nb;
+  float* e = y + ys * nb;
+  long long Ts = static_cast<long long>(T) * h->upsample_total;
+  const float* in = wav + static_cast<long long>(b0) * Ts;     // [nb*Ts, 1]
+  int width = 1;
+  for (int st = 0; st < c.num_stages; ++st) {
+    const int p = c.patch[st], d = c.d_model[st], od = c.output_dim[st];
+    Ts /= p;
+    const long long M = Ts * nb;
+    MT_CHECK(width * p == c.input_dim[st], "encoder stage %d: input_dim %d != %d channels x patch %d", st, c.input_dim[st], width, p);
+    const float* stage_in = in;
+    if (width != 1 && p != 1) { MT_TRY(patchify(in, e, M, width, p, s)); stage_in = e; }   // one channel: the reshape is the identity
+    MT_TRY(run_stage_layers(h, st, stage_in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
+                            x, hbuf, qkv, ff, y, ys * nb, s));
+    const bool last = st + 1 == c.num_stages;
+    float* direct = last && hidden_out ? hidden_out + static_cast<long long>(b0) * T * od : nullptr;
+    if (h->w.output_proj[st]) {
+      float* dst = direct ? direct : y;
+      MT_TRY(codec_linear(x, M, d, h->w.output_proj[st], od, dst, od, 0, nullptr, nullptr, s));
+      in = dst;
+    } else {
+      if (direct) MT_CUDA(cudaMemcpyAsync(direct, x, M * od * sizeof(float), cudaMemcpyDeviceToDevice, s));
+      in = x;
+    }
+    width = od;
+  }
+  MT_CHECK(width == c.code_dim && Ts == T, "encoder: last stage must produce code_dim channels at the frame rate");
+  return quantize_rows(h, in, static_cast<long long>(nb) * T, T, lengths ? lengths + b0 : nullptr, nq,
+                       codes + static_cast<long long>(b0) * T, static_cast<long long>(B) * T, hbuf, s);
+}
+
+extern "C" int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, const int64_t* code_lengths, int nq,
+                               int chunk_frames, int64_t* codes, float* hidden, void* workspace, long long workspace_bytes,
+                               mt_stream stream) {
+  MT_CHECK(h && wav && codes && workspace, "mt_codec_encode: null argument");
+  MT_CHECK(h->cfg.encoder && h->has_quant, "mt_codec_encode: this handle is not an encoder");
+  MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
+  MT_CHECK(B > 0 && T > 0, "mt_codec_encode: empty input B=%d T=%d", B, T);
+  long long per = 0;
+  MT_TRY(mt_codec_workspace_bytes(h, 1, T, &per));
+  const long long group = (workspace_bytes - 4096) / (per - 4096);
+  MT_CHECK(group >= 1, "codec workspace too small: need %lld bytes per sample, have %lld", per, workspace_bytes);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  for (int b0 = 0; b0 < B; b0 += static_cast<int>(group)) {
+    const int nb = static_cast<int>(std::min<long long>(group, B - b0));
+    MT_TRY(encode_group(h, wav, B, T, b0, nb, code_lengths, nq, chunk_frames, codes, hidden,
+                        reinterpret_cast<float*>(workspace), s));
   }
   return MT_OK;
 }

@@ -21,4 +21,9 @@ int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                        cudaStream_t s, const float* rope_table = nullptr);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
+// encode side (codec_enc.cu)
+using QuantWeights = mt_codec_quant_weights;
+int patchify(const float* x, float* y, long long tokens_out, int d, int h, cudaStream_t s);
+int rlfq_quantize(const float* z, long long M, int T, const int64_t* lengths, int nq, int R, int CS, int CD,
+                  const QuantWeights& w, int64_t* codes, long long q_stride, cudaStream_t s);
 }  // namespace mt

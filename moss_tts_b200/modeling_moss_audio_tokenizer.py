@@ -1,13 +1,18 @@
-"""Host-side mirror of `MossAudioTokenizerModel`'s decode side (reference
+"""Host-side mirror of `MossAudioTokenizerModel` (reference
 moss_audio_tokenizer/modeling_moss_audio_tokenizer.py:1312-1755): `decode`, `batch_decode`,
-`_decode_frame`, `quantizer.decode_codes`.  Arithmetic runs in libmosstts_sm100.
+`_decode_frame`, `quantizer.decode_codes`, and the encode side `encode`, `batch_encode`, `_encode_frame`,
+`quantizer(hidden, lengths, n)` (:1403-1429, :1478-1511, :1536-1648, :1238-1274) when the
+config carries encoder stages.  Arithmetic runs in libmosstts_sm100.
 
 Differences from the reference, all output-preserving:
   * decode(chunk_duration=...) does not loop over chunks: the streaming ring cache's visibility
     rule is applied as a mask in one pass (see oracle/codec.py), so the waveform equals the
     reference's chunked output.  The reference's B==1 restriction is kept as the same ValueError
     unless `allow_batched_chunks=True` is passed (used by the processor to batch requests).
-  * the encoder / quantise-forward side is out of scope.
+  * encode(chunk_duration=...) likewise applies the ring rule in one pass and returns what the reference's chunk loop
+    returns: floor(len_chunk / downsample_rate) frames per chunk (the ragged tail frame of the last chunk is dropped).
+  * the quantiser returns codes (and lengths); the straight-through `quantized_out` tensor of ResidualLFQ.forward
+    equals `decode_codes(codes)` on the valid frames and is not materialised.
 """
 from __future__ import annotations
 
@@ -27,8 +32,33 @@ class MossAudioTokenizerDecoderOutput:
     audio_lengths: Optional[torch.Tensor] = None
 
 
+@dataclass
+class MossAudioTokenizerEncoderOutput:
+    audio_codes: Optional[torch.Tensor] = None
+    audio_codes_lengths: Optional[torch.Tensor] = None
+    encoder_hidden_states: Optional[torch.Tensor] = None
+
+
 class _Quantizer:
-    """`model.quantizer` facade: decode_codes only (reference :1276-1283)."""
+    """`model.quantizer` facade: decode_codes (reference :1276-1283) and the inference forward (:1238-1274)."""
+
+    @torch.inference_mode()
+    def __call__(self, z: torch.Tensor, input_length: torch.Tensor, n_quantizers: Optional[int] = None):
+        """z [B, code_dim, T] fp32 -> (None, codes [nq, B, T], input_length)."""
+        o = self._o
+        if o._enc_engine is None:
+            raise L.MossTTSNativeError("this codec was built without encoder / quantiser weights")
+        B, D, T = z.shape
+        nq = n_quantizers or self.num_quantizers
+        hidden = z.to(device=o.device, dtype=torch.float32).transpose(1, 2).contiguous()      # token-major
+        lens = input_length.to(device=o.device, dtype=torch.int64).contiguous()
+        codes = torch.empty(nq, B, T, dtype=torch.int64, device=o.device)
+        if B * T > 0:
+            ws = torch.empty(B * T * o.config.rvq_dim, dtype=torch.float32, device=o.device)
+            with torch.cuda.device(o.device):
+                L.check(L.lib().mt_rlfq_quantize(o._enc_engine, L.ptr(hidden), B, T, L.ptr(lens), nq, L.ptr(codes), L.ptr(ws),
+                                                 C.c_longlong(ws.numel() * 4), L.stream_ptr(o.device)), "mt_rlfq_quantize")
+        return None, codes, input_length
 
     def __init__(self, owner: "MossAudioTokenizerModel"):
         self._o = owner
@@ -62,7 +92,10 @@ class MossAudioTokenizerModel:
         self.causal_transformer_context_duration = config.context_duration
         self._ws_cap = workspace_bytes
         self._ws = None
+        self._enc_engine = None
         self._build(state_dict)
+        if config.enc_stages and "quantizer.input_proj.bias" in state_dict:
+            self._build_encoder(state_dict)
         self.quantizer = _Quantizer(self)
 
     @classmethod
@@ -86,8 +119,20 @@ class MossAudioTokenizerModel:
         sd[p + "parametrizations.weight.original0"] = rn(c.code_dim, 1, 1, s=0.1, mean=1.0)
         sd[p + "parametrizations.weight.original1"] = rn(c.code_dim, c.rvq_dim, 1, s=0.05)
         sd[p + "bias"] = rn(c.code_dim, s=0.05)
-        for s_, st in enumerate(c.stages):
-            base = f"decoder.{2 * s_}."
+        if kw.pop("encoder", False) and c.enc_stages:
+            p = "quantizer.input_proj."
+            sd[p + "parametrizations.weight.original0"] = rn(c.rvq_dim, 1, 1, s=0.1, mean=1.0)
+            sd[p + "parametrizations.weight.original1"] = rn(c.rvq_dim, c.code_dim, 1, s=0.05)
+            sd[p + "bias"] = rn(c.rvq_dim, s=0.05)
+            for q in range(c.num_quantizers):
+                p = f"quantizer.quantizers.{q}.in_proj."
+                sd[p + "parametrizations.weight.original0"] = rn(c.codebook_dim, 1, 1, s=0.1, mean=1.0)
+                sd[p + "parametrizations.weight.original1"] = rn(c.codebook_dim, c.rvq_dim, 1, s=0.1)
+                sd[p + "bias"] = rn(c.codebook_dim, s=0.05)
+            enc = [(f"encoder.{2 * s_ + 1}.", st) for s_, st in enumerate(c.enc_stages)]
+        else:
+            enc = []
+        for base, st in [(f"decoder.{2 * s_}.", st) for s_, st in enumerate(c.stages)] + enc:
             d = st.d_model
             if st.input_dim != d:
                 sd[base + "input_proj.weight"] = rn(d, st.input_dim, s=st.input_dim ** -0.5)
@@ -137,11 +182,24 @@ class MossAudioTokenizerModel:
         wc.rvq_table = self._rvq_table.data_ptr()
         wc.rvq_out_bias = self._rvq_bias.data_ptr()
         self._layer_arrays = []
-        for s, st in enumerate(c.stages):
+        self._fill_stages(sd, c.stages, "decoder.{}.", 0, cc, wc)
+        cc.code_dim, cc.rvq_dim, cc.num_quantizers = c.code_dim, c.rvq_dim, c.num_quantizers
+        cc.codebook_size, cc.codebook_dim, cc.max_period = c.codebook_size, c.codebook_dim, c.max_period
+        h = C.c_void_p()
+        L.check(L.lib().mt_codec_create(C.byref(cc), C.byref(wc), C.byref(h)), "mt_codec_create")
+        self._engine = h
+
+    def _fill_stages(self, sd, stages, base_fmt: str, index_offset: int, cc, wc):
+        """Stage shapes -> cc, device pointers -> wc (tensors kept alive in self._keep)."""
+        dev = self.device
+
+        def g(name):
+            return sd[name].to(device=dev, dtype=torch.float32).contiguous()
+        for s, st in enumerate(stages):
             cc.input_dim[s], cc.d_model[s], cc.num_heads[s] = st.input_dim, st.d_model, st.num_heads
             cc.num_layers[s], cc.dim_ff[s], cc.output_dim[s] = st.num_layers, st.dim_feedforward, st.output_dim
             cc.patch[s], cc.context[s] = st.patch_size, st.context
-            base = f"decoder.{2 * s}."
+            base = base_fmt.format(2 * s + index_offset)
             ip = g(base + "input_proj.weight") if st.input_dim != st.d_model else None
             op = g(base + "output_proj.weight") if st.output_dim != st.d_model else None
             self._keep += [ip, op]
@@ -160,25 +218,66 @@ class MossAudioTokenizerModel:
                     setattr(arr[l], field, t.data_ptr())
             self._layer_arrays.append(arr)
             wc.layers[s] = C.cast(arr, C.POINTER(L.CodecLayerC))
+
+    def _build_encoder(self, sd: Dict[str, torch.Tensor]):
+        """Encoder handle: encoder_kwargs stages + the quantiser's encode-side parameters (weight-norm applied once
+        here, W = g * v / ||v||, reference WNConv1d :967-969; codebook rows normalised as decode_latents :1082 does on
+        every call)."""
+        c, dev = self.config, self.device
+
+        def g(name):
+            return sd[name].to(device=dev, dtype=torch.float32).contiguous()
+
+        def wn(prefix):
+            gg = g(prefix + "parametrizations.weight.original0")
+            v = g(prefix + "parametrizations.weight.original1")
+            n = v.reshape(v.shape[0], -1).norm(dim=1).reshape(-1, 1, 1)
+            return (gg * v / n).squeeze(-1).contiguous()
+        nq = c.num_quantizers
+        cb = torch.stack([g(f"quantizer.quantizers.{q}.codebook.weight") for q in range(nq)]).contiguous()
+        cbn = torch.nn.functional.normalize(cb, dim=-1).contiguous()
+        qt = {
+            "in_w": wn("quantizer.input_proj.") if c.code_dim != c.rvq_dim else None,
+            "in_b": g("quantizer.input_proj.bias") if c.code_dim != c.rvq_dim else None,
+            "q_in_w": torch.stack([wn(f"quantizer.quantizers.{q}.in_proj.") for q in range(nq)]).contiguous(),
+            "q_in_b": torch.stack([g(f"quantizer.quantizers.{q}.in_proj.bias") for q in range(nq)]).contiguous(),
+            "codebook": cb, "codebook_n": cbn, "codebook_nsq": cbn.pow(2).sum(-1).contiguous(),
+            "q_out_w": torch.stack([wn(f"quantizer.quantizers.{q}.out_proj.") for q in range(nq)]).contiguous(),
+            "q_out_b": torch.stack([g(f"quantizer.quantizers.{q}.out_proj.bias") for q in range(nq)]).contiguous(),
+        }
+        self._quant_tensors = qt
+        qc = L.CodecQuantWeightsC()
+        for k, t in qt.items():
+            setattr(qc, k, None if t is None else t.data_ptr())
+        cc = L.CodecConfigC()
+        cc.num_stages = len(c.enc_stages)
+        cc.encoder = 1
+        wc = L.CodecWeightsC()
+        wc.quant = C.pointer(qc)
+        self._fill_stages(sd, c.enc_stages, "encoder.{}.", 1, cc, wc)
         cc.code_dim, cc.rvq_dim, cc.num_quantizers = c.code_dim, c.rvq_dim, c.num_quantizers
         cc.codebook_size, cc.codebook_dim, cc.max_period = c.codebook_size, c.codebook_dim, c.max_period
         h = C.c_void_p()
-        L.check(L.lib().mt_codec_create(C.byref(cc), C.byref(wc), C.byref(h)), "mt_codec_create")
-        self._engine = h
+        L.check(L.lib().mt_codec_create(C.byref(cc), C.byref(wc), C.byref(h)), "mt_codec_create (encoder)")
+        self._enc_engine = h
 
     def __del__(self):
         try:
+            if getattr(self, "_enc_engine", None) is not None:
+                L.lib().mt_codec_destroy(self._enc_engine)
+                self._enc_engine = None
             if getattr(self, "_engine", None) is not None:
                 L.lib().mt_codec_destroy(self._engine)
                 self._engine = None
         except Exception:
             pass
 
-    def _workspace(self, B: int, T: int) -> torch.Tensor:
+    def _workspace(self, B: int, T: int, engine=None) -> torch.Tensor:
+        engine = self._engine if engine is None else engine
         need = C.c_longlong(0)
-        L.check(L.lib().mt_codec_workspace_bytes(self._engine, B, T, C.byref(need)), "mt_codec_workspace_bytes")
+        L.check(L.lib().mt_codec_workspace_bytes(engine, B, T, C.byref(need)), "mt_codec_workspace_bytes")
         one = C.c_longlong(0)
-        L.check(L.lib().mt_codec_workspace_bytes(self._engine, 1, T, C.byref(one)), "mt_codec_workspace_bytes")
+        L.check(L.lib().mt_codec_workspace_bytes(engine, 1, T, C.byref(one)), "mt_codec_workspace_bytes")
         want = max(min(need.value, self._ws_cap), one.value)
         if self._ws is None or self._ws.numel() < want:
             self._ws = None
@@ -201,6 +300,97 @@ class MossAudioTokenizerModel:
                                                 L.ptr(ws), C.c_longlong(ws.numel()), L.stream_ptr(self.device)),
                         "mt_codec_decode")
         return MossAudioTokenizerDecoderOutput(audio=wav, audio_lengths=codes_lengths.to(self.device) * self.downsample_rate)
+
+    # ---- encode side ---------------------------------------------------------
+    @torch.inference_mode()
+    def _encode_frame(self, input_values: torch.Tensor, input_lengths: Optional[torch.Tensor] = None,
+                      n_quantizers: Optional[int] = None, chunk_frames: int = 0) -> MossAudioTokenizerEncoderOutput:
+        """reference :1478-1511.  input_values [B,1,T] or [B,T] fp32; lengths in samples."""
+        if self._enc_engine is None:
+            raise L.MossTTSNativeError("this codec was built without encoder / quantiser weights")
+        if input_values.dim() == 2:
+            input_values = input_values.unsqueeze(1)
+        B, _, T = input_values.shape
+        D = self.downsample_rate
+        if input_lengths is None:
+            input_lengths = torch.full((B,), T, device=self.device, dtype=torch.long)
+        Tf = (T + D - 1) // D
+        nq = n_quantizers or self.config.num_quantizers
+        wav = torch.zeros(B, Tf * D, dtype=torch.float32, device=self.device)          # pad to whole frames (:1494-1496)
+        wav[:, :T] = input_values[:, 0].to(device=self.device, dtype=torch.float32)
+        code_lens = input_lengths.to(device=self.device, dtype=torch.int64)
+        for st in self.config.enc_stages:                                              # floor at every stage (:943)
+            code_lens = code_lens // st.patch_size
+        code_lens = code_lens.contiguous()
+        codes = torch.empty(nq, B, Tf, dtype=torch.int64, device=self.device)
+        hidden = torch.empty(B, Tf, self.config.code_dim, dtype=torch.float32, device=self.device)
+        if B * Tf > 0:
+            ws = self._workspace(B, Tf, self._enc_engine)
+            with torch.cuda.device(self.device):
+                L.check(L.lib().mt_codec_encode(self._enc_engine, L.ptr(wav), B, Tf, L.ptr(code_lens), nq, int(chunk_frames),
+                                                L.ptr(codes), L.ptr(hidden), L.ptr(ws), C.c_longlong(ws.numel()),
+                                                L.stream_ptr(self.device)), "mt_codec_encode")
+        return MossAudioTokenizerEncoderOutput(audio_codes=codes, audio_codes_lengths=code_lens,
+                                               encoder_hidden_states=hidden.transpose(1, 2))
+
+    @torch.inference_mode()
+    def encode(self, input_values: torch.Tensor, padding_mask: Optional[torch.Tensor] = None,
+               num_quantizers: Optional[int] = None, return_dict: Optional[bool] = None,
+               chunk_duration: Optional[float] = None):
+        """reference :1536-1648 (same argument checks and messages)."""
+        return_dict = True if return_dict is None else return_dict
+        if input_values.dim() == 2:
+            input_values = input_values.unsqueeze(1)
+        B, _, T = input_values.shape
+        if padding_mask is not None:
+            input_lengths = padding_mask.sum(dim=-1).long().to(self.device)
+        else:
+            input_lengths = torch.full((B,), T, device=self.device, dtype=torch.long)
+        if chunk_duration is None:
+            out = self._encode_frame(input_values, input_lengths, num_quantizers)
+        else:
+            if chunk_duration <= 0:
+                raise ValueError("`chunk_duration` must be > 0 when provided.")
+            if chunk_duration > self.causal_transformer_context_duration:
+                raise ValueError("`chunk_duration` must be <= `config.causal_transformer_context_duration` "
+                                 f"({self.causal_transformer_context_duration}), got {chunk_duration}.")
+            if B != 1:
+                raise ValueError("Streaming encode via `chunk_duration` currently only supports batch_size=1.")
+            chunk_length = int(round(chunk_duration * self.sampling_rate))
+            if chunk_length <= 0:
+                raise ValueError("`chunk_duration` is too small and results in chunk_length <= 0.")
+            if chunk_length % self.downsample_rate != 0:
+                raise ValueError("`chunk_duration * config.sampling_rate` must be divisible by `config.downsample_rate`. "
+                                 f"Got chunk_length={chunk_length}, downsample_rate={self.downsample_rate}.")
+            n = int(input_lengths[0].item())
+            if n <= chunk_length:
+                out = self._encode_frame(input_values[..., :n], input_lengths, num_quantizers)
+            else:
+                cf = chunk_length // self.downsample_rate
+                full = self._encode_frame(input_values[..., :n], input_lengths, num_quantizers, chunk_frames=cf)
+                # the reference's chunk loop keeps floor(len_i / downsample_rate) frames of every chunk (:1624-1626)
+                keep = (n // chunk_length) * cf + (n % chunk_length) // self.downsample_rate
+                out = MossAudioTokenizerEncoderOutput(
+                    audio_codes=full.audio_codes[:, :, :keep],
+                    audio_codes_lengths=torch.tensor([keep], device=self.device, dtype=torch.long),
+                    encoder_hidden_states=full.encoder_hidden_states[:, :, :keep])
+        if not return_dict:
+            return out.audio_codes, out.audio_codes_lengths
+        return out
+
+    @torch.inference_mode()
+    def batch_encode(self, wav_list: List[torch.Tensor], num_quantizers: Optional[int] = None):
+        """reference :1403-1429."""
+        if len(wav_list) == 0:
+            raise ValueError("`wav_list` must contain at least one waveform.")
+        B = len(wav_list)
+        max_length = max(int(w.shape[-1]) for w in wav_list)
+        x = torch.zeros(B, 1, max_length, device=self.device)
+        lens = torch.zeros(B, device=self.device, dtype=torch.long)
+        for i, w in enumerate(wav_list):
+            x[i, 0, : w.shape[-1]] = w.to(self.device)
+            lens[i] = w.shape[-1]
+        return self._encode_frame(x, lens, n_quantizers=num_quantizers)
 
     @torch.inference_mode()
     def decode(self, audio_codes: torch.Tensor, padding_mask: Optional[torch.Tensor] = None,

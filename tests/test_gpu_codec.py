@@ -115,6 +115,7 @@ def test_processor_glue_matches_reference(mini):
 def test_released_stage_shapes_one_layer():
     """The released widths (1280/768, ff 5120/3072, windows 125..1000) with 1 layer per stage."""
     cfg = CodecConfig.released()
+    cfg.enc_stages = []                      # encode side: tests/test_gpu_codec_encode.py
     for st in cfg.stages:
         st.num_layers = 1
     w = make_codec_weights(cfg, seed=9)

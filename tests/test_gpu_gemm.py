@@ -75,7 +75,7 @@ def test_gemm_partials_for_fused_consumer(M, N, K):
     assert (out == 7.0).all()                      # `out` is left to the consumer
 
 
-@pytest.mark.parametrize("M,N,K", [(32, 768, 512), (250, 1280, 768), (1000, 3072, 768), (700, 240, 768)])
+@pytest.mark.parametrize("M,N,K", [(32, 768, 512), (250, 1280, 768), (1000, 3072, 768), (700, 240, 768), (700, 768, 240), (40, 64, 240)])
 @pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
 def test_gemm_tf32_epilogues(M, N, K, impl):
     g = torch.Generator(device=DEV).manual_seed(N)
