@@ -341,6 +341,22 @@ int mt_rlfq_quantize(mt_codec* h, const float* hidden, int B, int T, const int64
 int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, const int64_t* code_lengths, int nq, int chunk_frames,
                     int64_t* codes, float* hidden, void* workspace, long long workspace_bytes, mt_stream s);
 
+/* ------------------------------------------------------------------------------------------
+ * Prompt side of MossTTSDelayProcessor (moss_tts_delay/processing_moss_tts.py)
+ * ------------------------------------------------------------------------------------------ */
+/* loudness_normalize (:736-748) of B zero-padded rows wav[b*ld .. b*ld+lengths[b]) in place (rows of length 0 untouched). */
+int mt_loudness_normalize(float* wav, long long ld, const int64_t* lengths, int B, float target_dbfs, float gain_lo,
+                          float gain_hi, mt_stream s);
+/* _get_unified_codes (:588-641): out[r] = (text_codes[r], audio channels).  blocks [n_blocks][4] int32 on device, in row
+ * order: {first row, rows, T, first code row}; T >= 0: the delay pattern (:516-525) of codes[first code row .. +T) [.., n_vq],
+ * T = -1: pad rows.  Rows outside every block are pad_code. */
+int mt_pack_unified_codes(const int64_t* text_codes, const int* blocks, int n_blocks, const int64_t* codes, int n_vq,
+                          long long pad_code, int rows, int64_t* out, mt_stream s);
+/* _pad (:410-431): rows[b] -> device pointer to [lens[b], C] int64; out [B, Lmax, C] left-padded with
+ * (pad_token, pad_code, ...), mask [B, Lmax] uint8 (1 = real row). */
+int mt_pad_left(const int64_t* const* rows, const int* lens, int B, int Lmax, int C, long long pad_token,
+                long long pad_code, int64_t* out, uint8_t* mask, mt_stream s);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif
