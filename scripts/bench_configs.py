@@ -2,6 +2,7 @@
   C3  codec decode sweep                     B in {1,4,16,64,256} x T in {13,63,125,375,750} frames
   C4  MossTTSLocal (assumed 1.7B shape)      B = 128, 96-token prompt, 125 frames, n_vq_for_inference = 32
   C5  MossTTSDelay n_vq = 16 long context    B = 4, ~512-token prompt, 3765 steps (>= 5 min of audio)
+  enc codec ENCODE sweep B in {1,16,64} x {1,10,30} s of 24 kHz audio -> 32 codebooks
 One JSON line per measurement; device-timed with CUDA events after a warm-up call.
 
   python scripts/bench_configs.py [--what c3,c4,c5] [--quick]
@@ -47,6 +48,22 @@ def c3(args, dev):
             print(json.dumps({"config": "C3 codec decode", "B": B, "T_frames": T, "audio_s": B * T / 12.5, "ms": ms,
                               "audio_s_per_s": B * T / 12.5 / (ms * 1e-3), "ms_chunked_8s": ms_c,
                               "audio_s_per_s_chunked": B * T / 12.5 / (ms_c * 1e-3)}), flush=True)
+
+
+def enc(args, dev):
+    from moss_tts_b200.config import CodecConfig
+    from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+    ccfg = CodecConfig.released()
+    codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=24 << 30, encoder=True)
+    for B in ([1, 16] if args.quick else [1, 16, 64]):
+        for sec in ([1, 10] if args.quick else [1, 10, 30]):
+            wav = torch.randn(B, 1, sec * ccfg.sampling_rate, device=dev) * 0.1
+            codec.encode(wav)
+            ms, out = timed(lambda: codec.encode(wav), reps=3)
+            ms_q, _ = timed(lambda: codec.quantizer(out.encoder_hidden_states, out.audio_codes_lengths), reps=3)
+            print(json.dumps({"config": "codec encode (released shape, 68 layers + 32-codebook RLFQ)", "B": B, "audio_s": B * sec,
+                              "frames": int(out.audio_codes.shape[-1]), "ms": ms, "audio_s_per_s": B * sec / (ms * 1e-3),
+                              "ms_quantiser_alone": ms_q}), flush=True)
 
 
 def c4(args, dev):
@@ -107,7 +124,7 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     for w in args.what.split(","):
-        {"c3": c3, "c4": c4, "c5": c5}[w](args, dev)
+        {"c3": c3, "c4": c4, "c5": c5, "enc": enc}[w](args, dev)
         torch.cuda.empty_cache()
 
 
