@@ -43,6 +43,7 @@ extern "C" {
 
 #define MT_DTYPE_BF16 0
 #define MT_DTYPE_F32 1 /* as a GEMM input type: fp32 storage, TF32 tensor-core math */
+#define MT_DTYPE_F16 2 /* IEEE half storage (x and w), fp32 accumulate: the TF32 mantissa at half the operand bytes */
 
 #define MT_GEMM_AUTO 0   /* tcgen05/TMA kernel (the product path) */
 #define MT_GEMM_SIMT 1   /* plain CUDA-core kernel, used by tests to cross-check the tcgen05 kernel */
@@ -81,8 +82,8 @@ long long mt_debug_set_trace(void* buf, long long words);
  * epilogue: v = acc (+bias[n]) ; act ; (round to bf16) ; out = residual[m,n] + (scale ? scale[n]*v : v)
  * ------------------------------------------------------------------------------------------ */
 typedef struct {
-  int dtype_in;          /* MT_DTYPE_BF16 | MT_DTYPE_F32 (x and w) */
-  int dtype_out;         /* MT_DTYPE_BF16 | MT_DTYPE_F32 (out and residual) */
+  int dtype_in;          /* MT_DTYPE_BF16 | MT_DTYPE_F32 | MT_DTYPE_F16 (x and w) */
+  int dtype_out;         /* MT_DTYPE_BF16 | MT_DTYPE_F32 | MT_DTYPE_F16 (out and residual) */
   int M, N, K;
   const void* x;  long long ldx;   /* row stride in elements */
   const void* w;  long long ldw;
@@ -267,14 +268,19 @@ typedef struct {
   float max_period;
   int encoder;   /* 0: decoder stages, patch[s] = upsample AFTER stage s.  1: encoder stages (encoder_kwargs order),
                   * patch[s] = downsample BEFORE stage s and input_dim[s] the width after it. */
+  int layer_gemm_f16;  /* 0: the four Linear weights of every transformer layer are fp32 and run as TF32 tensor-core GEMMs.
+                        * 1: they are IEEE half (converted once by the caller) and LayerNorm / attention / GELU hand their
+                        *    outputs to the next GEMM as half: kind::f16 MMAs with fp32 accumulation - the same 10-bit operand
+                        *    mantissa as TF32 (round-to-nearest instead of truncation) at half the operand bytes.  The residual
+                        *    stream, q/k/v, softmax, LayerNorm statistics and every stage input/output projection stay fp32. */
 } mt_codec_config;
 
-typedef struct {            /* one transformer layer, all fp32 */
+typedef struct {            /* one transformer layer; fp32, except the four matrices when layer_gemm_f16 = 1 (half) */
   const float *norm1_w, *norm1_b, *norm2_w, *norm2_b;
-  const float *in_proj;     /* [3d, d] */
-  const float *out_proj;    /* [d, d] */
-  const float *linear1;     /* [ff, d] */
-  const float *linear2;     /* [d, ff] */
+  const void *in_proj;      /* [3d, d] */
+  const void *out_proj;     /* [d, d] */
+  const void *linear1;      /* [ff, d] */
+  const void *linear2;      /* [d, ff] */
   const float *scale1, *scale2;   /* LayerScale [d] */
 } mt_codec_layer;
 

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libmosstts_sm100.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 MT_OK, MT_ERR_ARG, MT_ERR_CUDA, MT_ERR_UNSUPPORTED = 0, -1, -2, -3
-MT_DTYPE_BF16, MT_DTYPE_F32 = 0, 1
+MT_DTYPE_BF16, MT_DTYPE_F32, MT_DTYPE_F16 = 0, 1, 2
 MT_GEMM_AUTO, MT_GEMM_SIMT, MT_GEMM_W_STATIC, MT_GEMM_W_TILED = 0, 1, 2, 4
 MT_CODEC_MAX_STAGES = 8
 
@@ -97,7 +97,7 @@ class CodecConfigC(C.Structure):
                [(n, _IntArr) for n in ("input_dim", "d_model", "num_heads", "num_layers", "dim_ff", "output_dim",
                                        "patch", "context")] + \
                [(n, C.c_int) for n in ("code_dim", "rvq_dim", "num_quantizers", "codebook_size", "codebook_dim")] + \
-               [("max_period", C.c_float), ("encoder", C.c_int)]
+               [("max_period", C.c_float), ("encoder", C.c_int), ("layer_gemm_f16", C.c_int)]
 
 
 class CodecQuantWeightsC(C.Structure):

@@ -20,8 +20,8 @@ extern "C" long long mt_debug_set_trace(void* buf, long long words) { const long
 
 extern "C" int mt_gemm(const mt_gemm_args* a, mt_stream s) {
   MT_CHECK(a, "mt_gemm: null args");
-  MT_CHECK(a->dtype_in == MT_DTYPE_BF16 || a->dtype_in == MT_DTYPE_F32, "mt_gemm: bad dtype_in");
-  MT_CHECK(a->dtype_out == MT_DTYPE_BF16 || a->dtype_out == MT_DTYPE_F32, "mt_gemm: bad dtype_out");
+  MT_CHECK(a->dtype_in == MT_DTYPE_BF16 || a->dtype_in == MT_DTYPE_F32 || a->dtype_in == MT_DTYPE_F16, "mt_gemm: bad dtype_in");
+  MT_CHECK(a->dtype_out == MT_DTYPE_BF16 || a->dtype_out == MT_DTYPE_F32 || a->dtype_out == MT_DTYPE_F16, "mt_gemm: bad dtype_out");
   LinearPlan p;
   p.dtype_in = a->dtype_in; p.dtype_out = a->dtype_out; p.M = a->M; p.N = a->N; p.K = a->K;
   p.x = a->x; p.ldx = a->ldx; p.w = a->w; p.ldw = a->ldw; p.out = a->out; p.ldo = a->ldo;

@@ -43,7 +43,7 @@ __device__ __forceinline__ int vis_lo(int t, int T, int context, int chunk) {
 
 __global__ void __launch_bounds__(kWarps * 32)
 codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out, int T, int heads, int context,
-                          int chunk, float scale, const float4* __restrict__ rope) {
+                          int chunk, float scale, const float4* __restrict__ rope, int out_f16) {
   __shared__ __align__(16) uint32_t sk[kK * kPitch];
   __shared__ __align__(16) uint32_t sv[kK * kPitch];
   pdl_trigger();
@@ -168,21 +168,26 @@ codec_attention_tc_kernel(const float* __restrict__ qkv, float* __restrict__ out
   const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
 #pragma unroll
   for (int n = 0; n < kD / 8; ++n) {
-    if (row0 < T)
-      *reinterpret_cast<float2*>(out + (tok0 + row0) * d + h * kD + 8 * n + 2 * t4) = make_float2(o[n][0] * i0, o[n][1] * i0);
-    if (row1 < T)
-      *reinterpret_cast<float2*>(out + (tok0 + row1) * d + h * kD + 8 * n + 2 * t4) = make_float2(o[n][2] * i1, o[n][3] * i1);
+    const int col = h * kD + 8 * n + 2 * t4;
+    if (out_f16) {
+      __half* oh = reinterpret_cast<__half*>(out);
+      if (row0 < T) *reinterpret_cast<uint32_t*>(oh + (tok0 + row0) * d + col) = pack_f16(o[n][0] * i0, o[n][1] * i0);
+      if (row1 < T) *reinterpret_cast<uint32_t*>(oh + (tok0 + row1) * d + col) = pack_f16(o[n][2] * i1, o[n][3] * i1);
+    } else {
+      if (row0 < T) *reinterpret_cast<float2*>(out + (tok0 + row0) * d + col) = make_float2(o[n][0] * i0, o[n][1] * i0);
+      if (row1 < T) *reinterpret_cast<float2*>(out + (tok0 + row1) * d + col) = make_float2(o[n][2] * i1, o[n][3] * i1);
+    }
   }
 }
 
 }  // namespace
 
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
-                       cudaStream_t s, const float* rope_table) {
+                       cudaStream_t s, const float* rope_table, int out_f16) {
   if (hd != kD) return fail(MT_ERR_UNSUPPORTED, "codec attention supports head_dim 64 only (got %d)", hd);
   dim3 grid(cdiv(T, kQ), heads, B);
   MT_CUDA(launch(codec_attention_tc_kernel, grid, dim3(kWarps * 32), 0, s, qkv, out, T, heads, context, chunk,
-                 1.0f / sqrtf(static_cast<float>(hd)), reinterpret_cast<const float4*>(rope_table)));
+                 1.0f / sqrtf(static_cast<float>(hd)), reinterpret_cast<const float4*>(rope_table), out_f16));
   count_launch();
   return MT_OK;
 }

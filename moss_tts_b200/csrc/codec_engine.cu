@@ -52,10 +52,11 @@ static void per_sample_floats(const mt_codec_config& c, int T, long long* xs, lo
   *xs = tx; *qkvs = tq; *ffs = tf; *ys = ty; *es = te;
 }
 
-static int codec_linear(const float* x, long long M, int K, const float* w, int N, float* out, long long ldo,
-                        int act, const float* residual, const float* scale, cudaStream_t s) {
+static int codec_linear(const void* x, long long M, int K, const void* w, int N, void* out, long long ldo,
+                        int act, const float* residual, const float* scale, cudaStream_t s, int din = MT_DTYPE_F32,
+                        int dout = MT_DTYPE_F32) {
   LinearPlan p;
-  p.dtype_in = MT_DTYPE_F32; p.dtype_out = MT_DTYPE_F32;
+  p.dtype_in = din; p.dtype_out = dout;
   p.M = static_cast<int>(M); p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = ldo;
   p.act = act; p.residual = residual; p.ldr = ldo; p.scale = scale;
   return linear(p, s);
@@ -133,21 +134,25 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
   const bool table_fits = static_cast<long long>(Ts) * 64 <= y_floats;
   if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
+  // layer_gemm_f16: hbuf and ff hold IEEE half values (the operands of the next GEMM); x, qkv stay fp32
+  const int h16 = c.layer_gemm_f16 ? 1 : 0;
+  const int din = h16 ? MT_DTYPE_F16 : MT_DTYPE_F32;
+  MT_CHECK(!(h16 && simt_attn), "MT_CODEC_ATTN_SIMT=1 needs a codec built with layer_gemm_f16 = 0");
   for (int l = 0; l < c.num_layers[st]; ++l) {
     const mt_codec_layer& L = h->layers[st][l];
-    MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s));
-    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s));
+    MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
+    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din));
     if (simt_attn || !table_fits) {
       MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
       if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
-      else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
+      else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, nullptr, h16));
     } else {
-      MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
+      MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y, h16));
     }
-    MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s));
-    MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s));
-    MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s));
-    MT_TRY(codec_linear(ff, M, ffd, L.linear2, d, x, d, 0, x, L.scale2, s));
+    MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s, din));
+    MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s, h16));
+    MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s, din, din));
+    MT_TRY(codec_linear(ff, M, ffd, L.linear2, d, x, d, 0, x, L.scale2, s, din));
   }
   return MT_OK;
 }

@@ -143,7 +143,7 @@ int rvq_dequant_strided(const int64_t* codes, const float* table, const float* b
 // LayerNorm (eps 1e-5, affine), one block per token, two-pass in fp32
 // ---------------------------------------------------------------------------------------------
 __global__ void layernorm_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                                 float* __restrict__ out, int d, float eps) {
+                                 float* __restrict__ out, int d, float eps, int out_f16) {
   extern __shared__ float srow[];
   float* scratch = srow + d;
   const long long m = blockIdx.x;
@@ -153,7 +153,11 @@ __global__ void layernorm_kernel(const float* __restrict__ x, const float* __res
   float ss = 0.f;
   for (int c = threadIdx.x; c < d; c += blockDim.x) { const float t = srow[c] - mean; ss += t * t; }
   const float rstd = rsqrtf(block_sum(ss, scratch) / d + eps);
-  for (int c = threadIdx.x; c < d; c += blockDim.x) out[m * d + c] = (srow[c] - mean) * rstd * w[c] + b[c];
+  for (int c = threadIdx.x; c < d; c += blockDim.x) {
+    const float y = (srow[c] - mean) * rstd * w[c] + b[c];
+    if (out_f16) reinterpret_cast<__half*>(out)[m * d + c] = __float2half_rn(y);
+    else out[m * d + c] = y;
+  }
 }
 // Warp-per-token form for d <= 32 * 4 * kLnVec (the codec's 768 / 1280): the row lives in registers (float4 loads, all
 // issued before the first use), mean / variance by warp shuffles, no shared memory and no block barriers; 8 tokens per
@@ -162,7 +166,7 @@ constexpr int kLnVec = 10;
 template <int NV>
 __global__ void __launch_bounds__(256)
 layernorm_warp_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                      float* __restrict__ out, long long M, int d, float eps) {
+                      float* __restrict__ out, long long M, int d, float eps, int out_f16) {
   const int lane = threadIdx.x & 31;
   const long long m = blockIdx.x * 8ll + (threadIdx.x >> 5);
   pdl_trigger();
@@ -197,20 +201,22 @@ layernorm_warp_kernel(const float* __restrict__ x, const float* __restrict__ w, 
     const int c = lane + 32 * i;
     if (c < nvec) {
       const float4 ww = w4[c], bb = b4[c];
-      orow[c] = make_float4((v[i].x - mean) * rstd * ww.x + bb.x, (v[i].y - mean) * rstd * ww.y + bb.y,
-                            (v[i].z - mean) * rstd * ww.z + bb.z, (v[i].w - mean) * rstd * ww.w + bb.w);
+      const float4 y = make_float4((v[i].x - mean) * rstd * ww.x + bb.x, (v[i].y - mean) * rstd * ww.y + bb.y,
+                                   (v[i].z - mean) * rstd * ww.z + bb.z, (v[i].w - mean) * rstd * ww.w + bb.w);
+      if (out_f16) reinterpret_cast<uint2*>(reinterpret_cast<__half*>(out) + m * d)[c] = make_uint2(pack_f16(y.x, y.y), pack_f16(y.z, y.w));
+      else orow[c] = y;
     }
   }
 }
-int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s) {
+int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s, int out_f16) {
   if (d % 4 == 0 && d <= 32 * 4 * kLnVec) {
     const unsigned blocks = static_cast<unsigned>((M + 7) / 8);
-    if (d <= 32 * 4 * 6) MT_CUDA(launch(layernorm_warp_kernel<6>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f));
-    else MT_CUDA(launch(layernorm_warp_kernel<kLnVec>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f));
+    if (d <= 32 * 4 * 6) MT_CUDA(launch(layernorm_warp_kernel<6>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f, out_f16));
+    else MT_CUDA(launch(layernorm_warp_kernel<kLnVec>, dim3(blocks), dim3(256), 0, s, x, w, b, out, M, d, 1e-5f, out_f16));
     count_launch();
     return MT_OK;
   }
-  layernorm_kernel<<<static_cast<unsigned>(M), 256, (d + 40) * sizeof(float), s>>>(x, w, b, out, d, 1e-5f);
+  layernorm_kernel<<<static_cast<unsigned>(M), 256, (d + 40) * sizeof(float), s>>>(x, w, b, out, d, 1e-5f, out_f16);
   count_launch();
   MT_LAUNCH_CHECK();
   return MT_OK;

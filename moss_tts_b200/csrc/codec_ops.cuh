@@ -10,7 +10,8 @@ int rvq_dequant(const int64_t* codes, const float* table, const float* bias, int
                 int channel_major, float* out, cudaStream_t s);
 int rvq_dequant_strided(const int64_t* codes, const float* table, const float* bias, int nq, long long q_stride,
                         long long frames, int cs, int code_dim, float* out, cudaStream_t s);
-int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s);
+// out_f16 = 1: `out` receives IEEE half values (the fp16 operand of the next GEMM) instead of fp32
+int layernorm(const float* x, const float* w, const float* b, float* out, long long M, int d, cudaStream_t s, int out_f16 = 0);
 int codec_rope(float* qkv, long long M, int T, int d, int hd, float max_period, cudaStream_t s);
 int codec_attention(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                     cudaStream_t s);
@@ -19,7 +20,7 @@ int codec_attention(const float* qkv, float* out, int B, int T, int heads, int h
 int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s);
 // rope_table != nullptr: q and k are rotated while they are staged (no separate codec_rope pass over qkv)
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
-                       cudaStream_t s, const float* rope_table = nullptr);
+                       cudaStream_t s, const float* rope_table = nullptr, int out_f16 = 0);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
 // encode side (codec_enc.cu)
 using QuantWeights = mt_codec_quant_weights;

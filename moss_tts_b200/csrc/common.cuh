@@ -7,6 +7,7 @@
 #include <string>
 #include <utility>
 
+#include <cuda_fp16.h>
 #include "../../include/mosstts.h"
 
 namespace mt {
@@ -79,6 +80,11 @@ __device__ __forceinline__ float bits_hi(uint32_t u) { return __uint_as_float(u 
 __device__ __forceinline__ float bits_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  __half2 v = __floats2half2_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 

@@ -1,5 +1,6 @@
 // Internal interface of the Linear-layer GEMMs (gemm_tc.cu).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda.h>
 #include "common.cuh"
 
@@ -47,7 +48,7 @@ struct LinearPlan {
 // epilogue description shared by the tcgen05 kernel, the SIMT kernel and the split-K reducer
 // ---------------------------------------------------------------------------------------------
 struct Epi {
-  void* out; long long ldo; int out_f32;
+  void* out; long long ldo; int out_f32;   // element type of out / residual: 1 fp32, 0 bf16, 2 fp16
   const float* bias; int act;
   const void* residual; long long ldr;
   const float* scale; int round_bf16;
@@ -62,8 +63,9 @@ __device__ __forceinline__ float epi_apply(const Epi& e, int m, int n, float v) 
   if (e.act == 1) v = gelu_erf(v);
   if (e.round_bf16) v = rbf(v);
   if (e.residual) {
-    float r = e.out_f32 ? reinterpret_cast<const float*>(e.residual)[m * e.ldr + n]
-                        : bf2f(reinterpret_cast<const bf16*>(e.residual)[m * e.ldr + n]);
+    float r = e.out_f32 == 1 ? reinterpret_cast<const float*>(e.residual)[m * e.ldr + n]
+              : e.out_f32 == 2 ? __half2float(reinterpret_cast<const __half*>(e.residual)[m * e.ldr + n])
+                               : bf2f(reinterpret_cast<const bf16*>(e.residual)[m * e.ldr + n]);
     v = r + (e.scale ? e.scale[n] * v : v);
   } else if (e.scale) {
     v = e.scale[n] * v;
@@ -71,9 +73,15 @@ __device__ __forceinline__ float epi_apply(const Epi& e, int m, int n, float v) 
   return v;
 }
 __device__ __forceinline__ void epi_store(const Epi& e, long long m, long long n, float v) {
-  if (e.out_f32) reinterpret_cast<float*>(e.out)[m * e.ldo + n] = v;
+  if (e.out_f32 == 1) reinterpret_cast<float*>(e.out)[m * e.ldo + n] = v;
+  else if (e.out_f32 == 2) reinterpret_cast<__half*>(e.out)[m * e.ldo + n] = __float2half_rn(v);
   else reinterpret_cast<bf16*>(e.out)[m * e.ldo + n] = f2bf(v);
 }
+
+static inline int dtype_bytes(int dtype) { return dtype == MT_DTYPE_F32 ? 4 : 2; }
+static inline int out_kind(int dtype) { return dtype == MT_DTYPE_F32 ? 1 : (dtype == MT_DTYPE_F16 ? 2 : 0); }
+// tcgen05 kernel flavour of an input dtype: 1 bf16 (kind::f16), 2 tf32 (kind::tf32, fp32 storage), 3 fp16 (kind::f16)
+static inline int mma_kind(int dtype) { return dtype == MT_DTYPE_BF16 ? 1 : (dtype == MT_DTYPE_F32 ? 2 : 3); }
 
 // Persistent 128x256-tile kernel for token-major problems (M > 256): prefill and the codec (gemm_big.cu).
 int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s);

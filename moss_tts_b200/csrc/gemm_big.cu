@@ -24,7 +24,7 @@ constexpr int kABytes = kBM * kKBytes, kBBytes = kBN * kKBytes, kStageBytes = kA
 constexpr int kBarOffset = kStages * kStageBytes;
 constexpr int kSmemTotal = kBarOffset + (2 * kStages + 4) * 8 + 16 + 1024;
 
-template <int KIND /*1 bf16, 2 tf32*/>
+template <int KIND /*1 bf16, 2 tf32, 3 fp16*/>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int M, int N,
                 int k_blocks, int m_tiles, int n_tiles, int w_early, int w_tiled) {
@@ -35,7 +35,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tmem_full = empty + kStages;     // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  constexpr int kKElems = KIND == 1 ? 64 : 32;
+  constexpr int kKElems = KIND == 2 ? 32 : 64;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = m_tiles * n_tiles;
@@ -107,7 +107,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc(KIND, kBM, kBN);
+      constexpr uint32_t idesc = ptx::make_idesc(KIND == 3 ? 0 : KIND, kBM, kBN);   // a/b format: 0 F16, 1 BF16, 2 TF32
       int it = 0, i = 0;
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
         const int buf = i & 1;
@@ -123,7 +123,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + kABytes);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            if (KIND == 1) ptx::mma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            if (KIND != 2) ptx::mma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);   // kind::f16
             else ptx::mma_tf32(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
           ptx::mma_commit(&empty[st]);
@@ -172,7 +172,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
             for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] *= ep.scale[n0 + j];
           }
           if (ep.residual) {
-            if (ep.out_f32) {
+            if (ep.out_f32 == 1) {
               const float* rr = reinterpret_cast<const float*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
               if (full_chunk && (ep.ldr & 3) == 0) {
 #pragma unroll
@@ -183,12 +183,15 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
               } else {
                 for (int j = 0; j < 32; ++j) if (n0 + j < N) v[j] = rr[j] + v[j];
               }
+            } else if (ep.out_f32 == 2) {
+              const __half* rr = reinterpret_cast<const __half*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
+              for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] = __half2float(rr[j]) + v[j];
             } else {
               const bf16* rr = reinterpret_cast<const bf16*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
               for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] = bf2f(rr[j]) + v[j];
             }
           }
-          if (ep.out_f32) {
+          if (ep.out_f32 == 1) {
             float* dst = reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
             if (full_chunk && (ep.ldo & 3) == 0) {
 #pragma unroll
@@ -196,6 +199,19 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
             } else {
               for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = v[j];
+            }
+          } else if (ep.out_f32 == 2) {
+            __half* dst = reinterpret_cast<__half*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
+            if (full_chunk && (ep.ldo & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                pk.x = pack_f16(v[j], v[j + 1]); pk.y = pack_f16(v[j + 2], v[j + 3]);
+                pk.z = pack_f16(v[j + 4], v[j + 5]); pk.w = pack_f16(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(dst + j) = pk;
+              }
+            } else {
+              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = __float2half_rn(v[j]);
             }
           } else {
             bf16* dst = reinterpret_cast<bf16*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
@@ -228,7 +244,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
 }  // namespace
 
 int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s) {
-  const int esz = p.dtype_in == MT_DTYPE_BF16 ? 2 : 4;
+  const int esz = dtype_bytes(p.dtype_in);
   const int k_elems = 128 / esz;
   const int k_blocks = cdiv(p.K, k_elems);
   CUtensorMap tmA, tmB;
@@ -243,19 +259,23 @@ int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s) {
   const int m_tiles = cdiv(p.M, kBM), n_tiles = cdiv(p.N, kBN);
   const int total = m_tiles * n_tiles;
   const int grid = total < kNumSMs ? total : kNumSMs;
-  static bool attr_set[3] = {false, false, false};
-  const int kind = p.dtype_in == MT_DTYPE_BF16 ? 1 : 2;
+  static bool attr_set[4] = {false, false, false, false};
+  const int kind = mma_kind(p.dtype_in);
   if (!attr_set[kind]) {
     if (kind == 1) MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    else MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    else if (kind == 2) MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    else MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
     attr_set[kind] = true;
   }
   const int w_early = p.w_static ? 1 : 0, w_tiled = p.w_tiled ? 1 : 0;
   if (kind == 1)
     MT_CUDA(launch(gemm_big_kernel<1>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
                    n_tiles, w_early, w_tiled));
-  else
+  else if (kind == 2)
     MT_CUDA(launch(gemm_big_kernel<2>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
+                   n_tiles, w_early, w_tiled));
+  else
+    MT_CUDA(launch(gemm_big_kernel<3>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
                    n_tiles, w_early, w_tiled));
   count_launch();
   return MT_OK;

@@ -35,7 +35,7 @@ struct DecCfg {
   static constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulators, power of two >= 32
 };
 
-template <int BN, int KIND /*1 bf16, 2 tf32*/>
+template <int BN, int KIND /*1 bf16, 2 tf32, 3 fp16*/>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int rowsA,
                 int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled, int exp_nox,
@@ -50,7 +50,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tmem_full = empty + S;           // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  constexpr int kKElems = KIND == 1 ? 64 : 32;
+  constexpr int kKElems = KIND == 2 ? 32 : 64;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int units = tiles * splits;
@@ -151,7 +151,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc(KIND, kTileA, BN);
+      constexpr uint32_t idesc = ptx::make_idesc(KIND == 3 ? 0 : KIND, kTileA, BN);
       bool restricted = false;
       if (full_flag) { pdl_wait(); restricted = *full_flag == 0; }
       int it = 0, i = 0;
@@ -173,7 +173,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const uint64_t bdesc = ptx::make_smem_desc_sw128(sa + C::kABytes);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            if (KIND == 1) ptx::mma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (j | k) != 0);
+            if (KIND != 2) ptx::mma_bf16(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (j | k) != 0);
             else ptx::mma_tf32(tacc, adesc + 2 * k, bdesc + 2 * k, idesc, (j | k) != 0);
           }
           ptx::mma_commit(&empty[st]);
@@ -292,7 +292,7 @@ int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long lon
 }
 
 int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
-  const int esz = p.dtype_in == MT_DTYPE_BF16 ? 2 : 4;
+  const int esz = dtype_bytes(p.dtype_in);
   const int k_elems = 128 / esz;
   const int k_blocks = cdiv(p.K, k_elems);
   int BN = 16;
@@ -325,11 +325,12 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   const int w_early = p.w_static && !p.tile_filter_flag ? early_depth : 0;
   const int keep_lo = p.tile_lo / kTileA, keep_hi = p.tile_hi / kTileA;
   if (p.tile_filter_flag) MT_CHECK(splits == 1 && !p.out_splits, "linear_dec: the row-tile filter needs an unsplit GEMM");
-  const bool bf = p.dtype_in == MT_DTYPE_BF16;
+  const int kind = mma_kind(p.dtype_in);
 #define MT_DEC(BNV)                                                                                               \
   case BNV:                                                                                                       \
-    if (bf) MT_TRY((launch_dec<BNV, 1>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));    \
-    else MT_TRY((launch_dec<BNV, 2>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));       \
+    if (kind == 1) MT_TRY((launch_dec<BNV, 1>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));    \
+    else if (kind == 2) MT_TRY((launch_dec<BNV, 2>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));       \
+    else MT_TRY((launch_dec<BNV, 3>(tmA, tmB, ep, p.N, p.M, k_blocks, tiles, splits, w_early, w_tiled, p.tile_filter_flag, keep_lo, keep_hi, s)));       \
     break;
   switch (BN) {
     MT_DEC(32) MT_DEC(64) MT_DEC(128) MT_DEC(256)

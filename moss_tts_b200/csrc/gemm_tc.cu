@@ -53,14 +53,15 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, 
                  int box_rows) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return fail(MT_ERR_CUDA, "cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
-  const int esz = dtype == MT_DTYPE_BF16 ? 2 : 4;
+  const int esz = dtype_bytes(dtype);
   if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld_elems * esz) & 15))
     return fail(MT_ERR_ARG, "TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch (ld=%lld)", ld_elems);
   cuuint64_t dims[2] = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
   cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld_elems) * esz};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(128 / esz), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, dtype == MT_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+  CUresult r = fn(out, dtype == MT_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                         : (dtype == MT_DTYPE_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32), 2,
                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(MT_ERR_CUDA, "cuTensorMapEncodeTiled failed with %d", static_cast<int>(r));
@@ -71,7 +72,7 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int dtype, long long rows, 
 // tile is one contiguous 16 KB run in HBM (a TMA box then reads 16 KB of consecutive addresses instead
 // of 128 runs of 128 B at a K*esz pitch).  Rows beyond N in the last tile are zero padding.
 int make_tmap_tiled(CUtensorMap* out, const void* base, int dtype, long long N, long long K) {
-  const int k_elems = dtype == MT_DTYPE_BF16 ? 64 : 32;
+  const int k_elems = 128 / dtype_bytes(dtype);
   const long long rows = ((N + 127) / 128) * (K / k_elems) * 128;
   return make_tmap_2d(out, base, dtype, rows, k_elems, k_elems, 128);
 }
@@ -254,7 +255,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             for (int j = 0; j < CH; ++j)
               v[j] = (b_row0 + j < rowsB) ? epi_apply(ep, m, b_row0 + j, __uint_as_float(r[j])) : 0.f;
             const bool full_chunk = b_row0 + CH <= rowsB;
-            if (ep.out_f32) {
+            if (ep.out_f32 == 1) {
               float* dst = reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + b_row0;
               if (full_chunk && (ep.ldo & 3) == 0) {
 #pragma unroll
@@ -401,7 +402,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   MT_CHECK(p.M > 0 && p.N > 0 && p.K > 0, "linear: empty problem M=%d N=%d K=%d", p.M, p.N, p.K);
   MT_CHECK(p.x && p.w, "linear: null operand");
   Epi ep{};
-  ep.out = p.out; ep.ldo = p.ldo; ep.out_f32 = p.dtype_out == MT_DTYPE_F32;
+  ep.out = p.out; ep.ldo = p.ldo; ep.out_f32 = out_kind(p.dtype_out);
   ep.bias = p.bias; ep.act = p.act; ep.residual = p.residual; ep.ldr = p.ldr; ep.scale = p.scale;
   ep.round_bf16 = p.round_bf16; ep.M = p.M; ep.N = p.N; ep.partial = nullptr;
 
@@ -411,6 +412,9 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     if (p.dtype_in == MT_DTYPE_BF16)
       MT_CUDA(launch(gemm_simt_kernel<bf16>, grid, block, 0, s, reinterpret_cast<const bf16*>(p.x), p.ldx,
                      reinterpret_cast<const bf16*>(p.w), p.ldw, p.K, ep, static_cast<int>(p.w_tiled)));
+    else if (p.dtype_in == MT_DTYPE_F16)
+      MT_CUDA(launch(gemm_simt_kernel<__half>, grid, block, 0, s, reinterpret_cast<const __half*>(p.x), p.ldx,
+                     reinterpret_cast<const __half*>(p.w), p.ldw, p.K, ep, static_cast<int>(p.w_tiled)));
     else
       MT_CUDA(launch(gemm_simt_kernel<float>, grid, block, 0, s, reinterpret_cast<const float*>(p.x), p.ldx,
                      reinterpret_cast<const float*>(p.w), p.ldw, p.K, ep, static_cast<int>(p.w_tiled)));
@@ -418,7 +422,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     return MT_OK;
   }
 
-  const int esz = p.dtype_in == MT_DTYPE_BF16 ? 2 : 4;
+  const int esz = dtype_bytes(p.dtype_in);
   const int k_elems = 128 / esz;
   const int k_blocks = cdiv(p.K, k_elems);
   const bool swapped = p.M <= 256;
@@ -426,6 +430,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   if (!swapped && !old_big) return linear_big(p, ep, s);
   static const bool old_dec = [] { const char* e = getenv("MT_OLD_DEC"); return e && e[0] == '1'; }();
   if (swapped && !old_dec) return linear_dec(p, ep, s);
+  MT_CHECK(p.dtype_in != MT_DTYPE_F16, "linear: the legacy kernel (MT_OLD_BIG / MT_OLD_DEC) has no fp16 flavour");
   int BN, rowsA, rowsB;
   CUtensorMap tmA, tmB;
   if (p.w_tiled) MT_CHECK(p.K % k_elems == 0, "linear: tile-major weights need K %% %d == 0 (K=%d)", k_elems, p.K);

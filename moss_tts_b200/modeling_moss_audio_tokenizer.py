@@ -82,7 +82,10 @@ class _Quantizer:
 
 class MossAudioTokenizerModel:
     def __init__(self, config: CodecConfig, state_dict: Dict[str, torch.Tensor], device="cuda:0",
-                 workspace_bytes: int = 8 << 30):
+                 workspace_bytes: int = 8 << 30, layer_gemm: Optional[str] = None):
+        """layer_gemm: "fp16" (default; MT_CODEC_GEMM overrides) runs the four Linear layers of every transformer block
+        as fp16-operand / fp32-accumulate tensor-core GEMMs (TF32's mantissa at half the operand bytes, DESIGN.md §4);
+        "tf32" keeps fp32 storage with TF32 math (fp32 exponent range for weights outside fp16's +-65504)."""
         if not torch.cuda.is_available():
             raise L.MossTTSNativeError("MossAudioTokenizerModel needs a CUDA (sm_100) device; there is no CPU path")
         self.config = config
@@ -93,6 +96,11 @@ class MossAudioTokenizerModel:
         self._ws_cap = workspace_bytes
         self._ws = None
         self._enc_engine = None
+        import os
+        layer_gemm = layer_gemm or os.environ.get("MT_CODEC_GEMM", "fp16")
+        if layer_gemm not in ("fp16", "tf32"):
+            raise ValueError(f"layer_gemm must be 'fp16' or 'tf32', got {layer_gemm!r}")
+        self.layer_gemm = layer_gemm
         self._build(state_dict)
         if config.enc_stages and "quantizer.input_proj.bias" in state_dict:
             self._build_encoder(state_dict)
@@ -178,6 +186,7 @@ class MossAudioTokenizerModel:
         self._keep = []
         cc = L.CodecConfigC()
         cc.num_stages = len(c.stages)
+        cc.layer_gemm_f16 = 1 if self.layer_gemm == "fp16" else 0
         wc = L.CodecWeightsC()
         wc.rvq_table = self._rvq_table.data_ptr()
         wc.rvq_out_bias = self._rvq_bias.data_ptr()
@@ -212,6 +221,11 @@ class MossAudioTokenizerModel:
                          "self_attn.out_projs.0.weight", "linear1.weight", "linear2.weight", "layer_scale_1.scale",
                          "layer_scale_2.scale"]
                 ts = [g(p + n) for n in names]
+                if self.layer_gemm == "fp16":                 # in_proj, out_proj, linear1, linear2 -> half, once
+                    for k in range(4, 8):
+                        if ts[k].abs().max().item() > 6.0e4:
+                            raise ValueError(f"{p + names[k]} exceeds the fp16 range; build the codec with layer_gemm='tf32'")
+                        ts[k] = ts[k].half().contiguous()
                 self._keep += ts
                 for field, t in zip(("norm1_w", "norm1_b", "norm2_w", "norm2_b", "in_proj", "out_proj", "linear1",
                                      "linear2", "scale1", "scale2"), ts):
@@ -252,6 +266,7 @@ class MossAudioTokenizerModel:
         cc = L.CodecConfigC()
         cc.num_stages = len(c.enc_stages)
         cc.encoder = 1
+        cc.layer_gemm_f16 = 1 if self.layer_gemm == "fp16" else 0
         wc = L.CodecWeightsC()
         wc.quant = C.pointer(qc)
         self._fill_stages(sd, c.enc_stages, "encoder.{}.", 1, cc, wc)

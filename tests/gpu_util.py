@@ -15,9 +15,10 @@ def gemm(x, w, *, out_dtype=None, bias=None, act=0, residual=None, scale=None, r
          workspace_mb=64, N=None):
     M, K = x.shape
     N = w.shape[0] if N is None else N       # N must be given for a flat tile-major weight buffer
-    din = L.MT_DTYPE_BF16 if x.dtype == torch.bfloat16 else L.MT_DTYPE_F32
+    code = {torch.bfloat16: L.MT_DTYPE_BF16, torch.float32: L.MT_DTYPE_F32, torch.float16: L.MT_DTYPE_F16}
+    din = code[x.dtype]
     out_dtype = out_dtype or x.dtype
-    dout = L.MT_DTYPE_BF16 if out_dtype == torch.bfloat16 else L.MT_DTYPE_F32
+    dout = code[out_dtype]
     out = torch.empty(M, N, dtype=out_dtype, device=x.device)
     ws = torch.empty(workspace_mb << 20, dtype=torch.uint8, device=x.device) if workspace_mb else None
     a = L.GemmArgs(din, dout, M, N, K, x.data_ptr(), x.stride(0), w.data_ptr(), w.stride(0) if w.dim() == 2 else K, out.data_ptr(), N,

@@ -53,6 +53,18 @@ def test_rvq_dequant_shapes(mini, B, T):
     assert (got - ref).abs().max().item() <= RVQ_TOL * max(1.0, ref.abs().max().item())
 
 
+def test_decode_tf32_layer_gemms_match_reference_golden(mini):
+    """layer_gemm="tf32" (fp32 storage, TF32 math) stays selectable next to the default fp16-operand GEMMs."""
+    g, cfg, w, model, oracle = mini
+    m32 = MossAudioTokenizerModel(cfg, w, device=DEV, layer_gemm="tf32")
+    assert model.layer_gemm == "fp16" and m32.layer_gemm == "tf32"
+    codes = torch.from_numpy(g["codes"]).to(DEV)
+    s16 = snr_db(torch.from_numpy(g["wav"]), model.decode(codes).audio.cpu())
+    s32 = snr_db(torch.from_numpy(g["wav"]), m32.decode(codes).audio.cpu())
+    print(f"[codec mini] SNR vs reference: fp16-operand layer GEMMs {s16:.1f} dB, TF32 {s32:.1f} dB")
+    assert s16 >= SNR_DB and s32 >= SNR_DB
+
+
 def test_decode_matches_reference_golden(mini):
     g, cfg, w, model, oracle = mini
     codes = torch.from_numpy(g["codes"]).to(DEV)
@@ -130,3 +142,7 @@ def test_released_stage_shapes_one_layer():
     one = model.decode(codes[:, :1].to(DEV), chunk_duration=8).audio.cpu()
     refc, _ = oracle.decode(codes[:, :1], chunk_duration=8)
     assert snr_db(refc, one) >= SNR_DB
+    m32 = MossAudioTokenizerModel(cfg, w, device=DEV, layer_gemm="tf32")
+    s32 = snr_db(ref, m32.decode(codes.to(DEV)).audio.cpu())
+    print(f"[codec released-width, 1 layer/stage] TF32 layer GEMMs: SNR {s32:.1f} dB")
+    assert s32 >= SNR_DB

@@ -54,6 +54,25 @@ def test_gemm_bf16_splitk_matches_unsplit(M, N, K):
     assert (b - ref).abs().max().item() <= 2e-3
 
 
+@pytest.mark.parametrize("M,N,K", [(32, 768, 512), (250, 1280, 768), (1000, 3072, 768), (6000, 2304, 768), (700, 768, 3072)])
+@pytest.mark.parametrize("impl", [L.MT_GEMM_SIMT, L.MT_GEMM_AUTO])
+def test_gemm_fp16_operands(M, N, K, impl):
+    """MT_DTYPE_F16 inputs (the codec's layer GEMMs): fp32 / fp16 outputs, GELU, LayerScale + fp32 residual."""
+    g = torch.Generator(device=DEV).manual_seed(M + N)
+    x = torch.randn(M, K, device=DEV, generator=g).half()
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).half()
+    res = torch.randn(M, N, device=DEV, generator=g)
+    scale = torch.rand(N, device=DEV, generator=g)
+    ref = x.float() @ w.float().T
+    out = gemm(x, w, out_dtype=torch.float32, impl=impl)
+    assert (out - ref).abs().max().item() <= 2e-3
+    out = gemm(x, w, out_dtype=torch.float32, residual=res, scale=scale, impl=impl)
+    assert (out - (res + scale * ref)).abs().max().item() <= 2e-3
+    out = gemm(x, w, out_dtype=torch.float16, act=1, impl=impl)
+    gref = torch.nn.functional.gelu(ref)
+    assert out.dtype == torch.float16 and (out.float() - gref).abs().max().item() <= 4e-3
+
+
 @pytest.mark.parametrize("M,N,K", [(64, 24576, 4096), (8, 512, 12288), (64, 384, 512)])
 def test_gemm_partials_for_fused_consumer(M, N, K):
     """mt_gemm_args.out_splits: the engines' calling form - fp32 slabs [splits][M][N] in the workspace, no reduce kernel."""
