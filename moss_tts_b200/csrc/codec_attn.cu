@@ -193,3 +193,201 @@ int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, in
 }
 
 }  // namespace mt
+
+// =============================================================================================
+// fp16 flavour (layer_gemm_f16 codecs): q/k/v arrive as IEEE half from the in_proj GEMM's epilogue, the output
+// leaves as half for the out_proj GEMM.  FlashAttention-2 structure on mma.sync.m16n8k16 (fp32 accumulate):
+// CTA = 8 warps = 128 consecutive queries of one (batch, head), 16 query rows per warp; 64-key K / V tiles are
+// staged once per CTA in shared memory (row pitch 72 halves = 144 B: every ldmatrix phase touches 8 rows that
+// fall into 8 different 16-byte bank groups), K with the interleaved-pair RoPE applied in fp32 on the way in.
+// B fragments come from ldmatrix.x4 (K: two k-steps per instruction; V: .trans, two 8-dim column groups per
+// instruction) -- 32 ldmatrix per warp and tile instead of the 256 LDS.32 of the TF32 kernel -- and half as
+// many MMAs, each doing twice the work.  Same mantissa as the TF32 path (10 explicit bits), same online softmax.
+// =============================================================================================
+namespace mt {
+namespace {
+
+constexpr int kHQ = 128, kHWarps = 8, kHPitch = 72;
+
+__device__ __forceinline__ void mma_f16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const __half* p) {
+  const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], const __half* p) {
+  const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(p));
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+// 8 halves (dims 8c .. 8c+7 of one head row) rotated by the interleaved-pair RoPE of position `pos`, times `mul`
+__device__ __forceinline__ uint4 rope8(uint4 raw, const float4* __restrict__ rope, long long pos, int c, float mul) {
+  const float4 cs0 = rope[pos * (kD / 4) + 2 * c], cs1 = rope[pos * (kD / 4) + 2 * c + 1];
+  const float2 p0 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+  const float2 p1 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+  const float2 p2 = __half22float2(*reinterpret_cast<const __half2*>(&raw.z));
+  const float2 p3 = __half22float2(*reinterpret_cast<const __half2*>(&raw.w));
+  uint4 o;
+  o.x = pack_f16((p0.x * cs0.x - p0.y * cs0.y) * mul, (p0.x * cs0.y + p0.y * cs0.x) * mul);
+  o.y = pack_f16((p1.x * cs0.z - p1.y * cs0.w) * mul, (p1.x * cs0.w + p1.y * cs0.z) * mul);
+  o.z = pack_f16((p2.x * cs1.x - p2.y * cs1.y) * mul, (p2.x * cs1.y + p2.y * cs1.x) * mul);
+  o.w = pack_f16((p3.x * cs1.z - p3.y * cs1.w) * mul, (p3.x * cs1.w + p3.y * cs1.z) * mul);
+  return o;
+}
+
+__global__ void __launch_bounds__(kHWarps * 32, 2)
+codec_attention_f16_kernel(const __half* __restrict__ qkv, __half* __restrict__ out, int T, int heads, int context,
+                           int chunk, float scale, const float4* __restrict__ rope) {
+  __shared__ __align__(16) __half sm[2 * kK * kHPitch];        // K tile | V tile (both: the 128-row Q tile first)
+  __half* sk = sm;
+  __half* sv = sm + kK * kHPitch;
+  pdl_trigger();
+  pdl_wait();
+  const int q0 = blockIdx.x * kHQ, h = blockIdx.y, b = blockIdx.z;
+  const int d = heads * kD;
+  const long long tok0 = static_cast<long long>(b) * T;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+
+  // ---- Q tile (RoPE, 1/sqrt(d) folded in) -> smem -> A fragments
+  for (int i = threadIdx.x; i < kHQ * (kD / 8); i += kHWarps * 32) {
+    const int r = i / (kD / 8), c = i % (kD / 8);
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (q0 + r < T) {
+      v = *reinterpret_cast<const uint4*>(qkv + (tok0 + q0 + r) * 3 * d + h * kD + 8 * c);
+      v = rope8(v, rope, q0 + r, c, scale);
+    }
+    *reinterpret_cast<uint4*>(sm + r * kHPitch + 8 * c) = v;
+  }
+  __syncthreads();
+  uint32_t qa[kD / 16][4];
+  {
+    // A fragment of k-step s: a0 (row g, cols 16s+2t4), a1 (row g+8), a2 (row g, cols +8), a3 (row g+8, cols +8)
+    const __half* base = sm + (warp * 16 + (lane & 15)) * kHPitch + 8 * (lane >> 4);
+#pragma unroll
+    for (int s = 0; s < kD / 16; ++s) ldsm_x4(qa[s], base + 16 * s);
+  }
+  const int row0 = q0 + warp * 16 + g, row1 = row0 + 8;
+  const int lo0 = vis_lo(min(row0, T - 1), T, context, chunk), lo1 = vis_lo(min(row1, T - 1), T, context, chunk);
+  const int wfirst = q0 + warp * 16, wlast = min(wfirst + 15, T - 1);      // this warp's query rows
+  const int wlo = vis_lo(min(wfirst, T - 1), T, context, chunk);           // lowest key any of them sees (lo is monotone)
+  float o[kD / 8][4];
+#pragma unroll
+  for (int n = 0; n < kD / 8; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  const int last_q = min(q0 + kHQ, T) - 1;
+  const int k_begin = (vis_lo(q0, T, context, chunk) / kK) * kK;
+  const int lo_last = vis_lo(last_q, T, context, chunk);
+  for (int k0 = k_begin; k0 <= last_q; k0 += kK) {
+    __syncthreads();                                            // previous tile (or the Q staging) is consumed
+    for (int i = threadIdx.x; i < kK * (kD / 8); i += kHWarps * 32) {
+      const int r = i / (kD / 8), c = i % (kD / 8);
+      uint4 kv = make_uint4(0u, 0u, 0u, 0u), vv = kv;
+      if (k0 + r < T) {
+        const __half* base = qkv + (tok0 + k0 + r) * 3 * d + h * kD + 8 * c;
+        kv = rope8(*reinterpret_cast<const uint4*>(base + d), rope, k0 + r, c, 1.f);
+        vv = *reinterpret_cast<const uint4*>(base + 2 * d);
+      }
+      *reinterpret_cast<uint4*>(sk + r * kHPitch + 8 * c) = kv;
+      *reinterpret_cast<uint4*>(sv + r * kHPitch + 8 * c) = vv;
+    }
+    __syncthreads();
+    if (wfirst >= T || k0 > wlast || k0 + kK - 1 < wlo) continue;      // nothing visible to this warp in this tile
+
+    // ---- S = Q.K^T for 16 rows x 64 keys
+    float sc[kK / 8][4];
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      sc[n][0] = sc[n][1] = sc[n][2] = sc[n][3] = 0.f;
+      // matrices: keys 8n..8n+7 x dims {0-7, 8-15, 16-23, 24-31} (+32 for the second instruction)
+      const __half* kr = sk + (8 * n + (lane & 7)) * kHPitch + 8 * (lane >> 3);
+      uint32_t kb[4];
+      ldsm_x4(kb, kr);
+      mma_f16_16816(sc[n], qa[0], kb[0], kb[1]);
+      mma_f16_16816(sc[n], qa[1], kb[2], kb[3]);
+      ldsm_x4(kb, kr + 32);
+      mma_f16_16816(sc[n], qa[2], kb[0], kb[1]);
+      mma_f16_16816(sc[n], qa[3], kb[2], kb[3]);
+    }
+    // ---- mask (edge tiles only), row max
+    const bool interior = k0 + kK - 1 <= q0 && k0 >= lo_last;
+    float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      if (!interior) {
+        const int ka = k0 + 8 * n + 2 * t4, kb2 = ka + 1;
+        if (ka < lo0 || ka > row0) sc[n][0] = -INFINITY;
+        if (kb2 < lo0 || kb2 > row0) sc[n][1] = -INFINITY;
+        if (ka < lo1 || ka > row1) sc[n][2] = -INFINITY;
+        if (kb2 < lo1 || kb2 > row1) sc[n][3] = -INFINITY;
+      }
+      mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
+      mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float nm0 = fmaxf(m0, mx0), nm1 = fmaxf(m1, mx1);
+    const float c0 = nm0 == -INFINITY ? 1.f : __expf(m0 - nm0), c1 = nm1 == -INFINITY ? 1.f : __expf(m1 - nm1);
+    const float b0 = nm0 == -INFINITY ? 0.f : nm0, b1 = nm1 == -INFINITY ? 0.f : nm1;
+    m0 = nm0; m1 = nm1;
+    l0 *= c0; l1 *= c1;
+#pragma unroll
+    for (int n = 0; n < kD / 8; ++n) { o[n][0] *= c0; o[n][1] *= c0; o[n][2] *= c1; o[n][3] *= c1; }
+    // ---- P = exp(S - m) as half A fragments: key groups 2j, 2j+1 of S are k-step j of P.V
+    float s0 = 0.f, s1 = 0.f;
+    uint32_t pa[kK / 16][4];
+#pragma unroll
+    for (int n = 0; n < kK / 8; ++n) {
+      const float p0 = __expf(sc[n][0] - b0), p1 = __expf(sc[n][1] - b0);
+      const float p2 = __expf(sc[n][2] - b1), p3 = __expf(sc[n][3] - b1);
+      s0 += p0 + p1; s1 += p2 + p3;
+      pa[n >> 1][(n & 1) * 2 + 0] = pack_f16(p0, p1);
+      pa[n >> 1][(n & 1) * 2 + 1] = pack_f16(p2, p3);
+    }
+    l0 += s0; l1 += s1;
+    // ---- O += P.V: matrices (keys 16j..+7 | 16j+8..+15) x (dims 8n..+7 | 8n+8..+15), transposed on load
+#pragma unroll
+    for (int j = 0; j < kK / 16; ++j) {
+      const __half* vr = sv + (16 * j + (lane & 15)) * kHPitch + 8 * (lane >> 4);
+#pragma unroll
+      for (int n = 0; n < kD / 8; n += 2) {
+        uint32_t vb[4];
+        ldsm_x4_trans(vb, vr + 8 * n);
+        mma_f16_16816(o[n], pa[j], vb[0], vb[1]);
+        mma_f16_16816(o[n + 1], pa[j], vb[2], vb[3]);
+      }
+    }
+  }
+  // ---- normalise and store
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float i0 = l0 > 0.f ? 1.f / l0 : 0.f, i1 = l1 > 0.f ? 1.f / l1 : 0.f;
+#pragma unroll
+  for (int n = 0; n < kD / 8; ++n) {
+    const int col = h * kD + 8 * n + 2 * t4;
+    if (row0 < T) *reinterpret_cast<uint32_t*>(out + (tok0 + row0) * d + col) = pack_f16(o[n][0] * i0, o[n][1] * i0);
+    if (row1 < T) *reinterpret_cast<uint32_t*>(out + (tok0 + row1) * d + col) = pack_f16(o[n][2] * i1, o[n][3] * i1);
+  }
+}
+
+}  // namespace
+
+int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk,
+                        cudaStream_t s, const float* rope_table) {
+  if (hd != kD) return fail(MT_ERR_UNSUPPORTED, "codec attention supports head_dim 64 only (got %d)", hd);
+  MT_CHECK(rope_table, "codec_attention_f16: the RoPE table is required");
+  dim3 grid(cdiv(T, kHQ), heads, B);
+  MT_CUDA(launch(codec_attention_f16_kernel, grid, dim3(kHWarps * 32), 0, s, reinterpret_cast<const __half*>(qkv),
+                 reinterpret_cast<__half*>(out), T, heads, context, chunk, 1.0f / sqrtf(static_cast<float>(hd)),
+                 reinterpret_cast<const float4*>(rope_table)));
+  count_launch();
+  return MT_OK;
+}
+
+}  // namespace mt

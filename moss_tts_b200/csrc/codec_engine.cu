@@ -134,15 +134,21 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
   const bool table_fits = static_cast<long long>(Ts) * 64 <= y_floats;
   if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
-  // layer_gemm_f16: hbuf and ff hold IEEE half values (the operands of the next GEMM); x, qkv stay fp32
+  // layer_gemm_f16: hbuf, qkv and ff hold IEEE half values (GEMM / attention operands); the residual stream x stays fp32
   const int h16 = c.layer_gemm_f16 ? 1 : 0;
   const int din = h16 ? MT_DTYPE_F16 : MT_DTYPE_F32;
   MT_CHECK(!(h16 && simt_attn), "MT_CODEC_ATTN_SIMT=1 needs a codec built with layer_gemm_f16 = 0");
+  MT_CHECK(!h16 || table_fits, "codec: no room for the RoPE table of stage %d", st);
+  // MT_CODEC_ATTN_TF32=1: keep q/k/v in fp32 and run the TF32 attention kernel inside an fp16-GEMM codec (A/B switch)
+  static const bool attn_tf32 = [] { const char* e = getenv("MT_CODEC_ATTN_TF32"); return e && e[0] == '1'; }();
+  const bool a16 = h16 && !attn_tf32;
   for (int l = 0; l < c.num_layers[st]; ++l) {
     const mt_codec_layer& L = h->layers[st][l];
     MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
-    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din));
-    if (simt_attn || !table_fits) {
+    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32));
+    if (a16) {
+      MT_TRY(codec_attention_f16(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
+    } else if (simt_attn || !table_fits) {
       MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
       if (simt_attn) MT_TRY(codec_attention(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s));
       else MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, nullptr, h16));

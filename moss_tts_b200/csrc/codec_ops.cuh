@@ -21,6 +21,9 @@ int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t
 // rope_table != nullptr: q and k are rotated while they are staged (no separate codec_rope pass over qkv)
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                        cudaStream_t s, const float* rope_table = nullptr, int out_f16 = 0);
+// fp16 flavour (codec_attn.cu): qkv [B*T, 3*heads*64] and out [B*T, heads*64] are IEEE half; RoPE table required
+int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk,
+                        cudaStream_t s, const float* rope_table);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
 // encode side (codec_enc.cu)
 using QuantWeights = mt_codec_quant_weights;
