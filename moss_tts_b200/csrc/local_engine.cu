@@ -303,8 +303,13 @@ extern "C" int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, i
 
   int frames_launched = 1;
   int* done_host = nullptr;
-  MT_CUDA(cudaMallocHost(&done_host, 2 * sizeof(int)));
-  done_host[0] = 0;
+  MT_CUDA(cudaMallocHost(&done_host, 4 * sizeof(int)));
+  done_host[0] = done_host[1] = 0;
+  // pipelined stop polling (see mt_lm_generate): the host waits for poll c-1 only after poll c is enqueued, so the GPU
+  // never drains while a ~1,700-node frame graph is being launched
+  cudaEvent_t poll_ev[2] = {nullptr, nullptr};
+  for (auto& e : poll_ev) MT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  int polls = 0;
   const int check_every = p->check_stop_every > 0 ? p->check_stop_every : 4;
   cudaGraphExec_t exec = nullptr;
   long long per_replay = 0;
@@ -335,16 +340,21 @@ extern "C" int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, i
     ++frames_launched;
     if (step_ms) cudaEventRecord(ev[frames_launched], s);
     if (step % check_every == 0) {
-      cudaMemcpyAsync(done_host, st.done, sizeof(int), cudaMemcpyDeviceToHost, s);
-      if (cudaStreamSynchronize(s) != cudaSuccess) { status = fail(MT_ERR_CUDA, "frame failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
-      if (done_host[0]) break;
+      const int slot = polls & 1;
+      cudaMemcpyAsync(done_host + slot, st.done, sizeof(int), cudaMemcpyDeviceToHost, s);
+      cudaEventRecord(poll_ev[slot], s);
+      if (polls > 0) {
+        if (cudaEventSynchronize(poll_ev[slot ^ 1]) != cudaSuccess) { status = fail(MT_ERR_CUDA, "frame failed: %s", cudaGetErrorString(cudaGetLastError())); break; }
+        if (done_host[slot ^ 1]) break;
+      }
+      ++polls;
     }
   }
   if (status == MT_OK) {
-    cudaMemcpyAsync(done_host + 1, st.step, sizeof(int), cudaMemcpyDeviceToHost, s);
+    cudaMemcpyAsync(done_host + 2, st.step, sizeof(int), cudaMemcpyDeviceToHost, s);
     cudaError_t e = cudaStreamSynchronize(s);
     if (e != cudaSuccess) status = fail(MT_ERR_CUDA, "generate failed: %s", cudaGetErrorString(e));
-    else *n_steps = done_host[1];
+    else *n_steps = done_host[2];
   }
   if (step_ms && status == MT_OK) {
     for (int i = 0; i < p->max_new_tokens; ++i) step_ms[i] = -1.f;
@@ -352,6 +362,7 @@ extern "C" int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, i
   }
   for (auto& e : ev) cudaEventDestroy(e);
   if (exec) cudaGraphExecDestroy(exec);
+  for (auto& e : poll_ev) if (e) cudaEventDestroy(e);
   cudaFreeHost(done_host);
   return status;
 }
