@@ -50,6 +50,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tmem_full = empty + S;           // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  volatile int* gu_last = reinterpret_cast<volatile int*>(tmem_holder + 2);     // fused-SwiGLU "last arriver" flag
   constexpr int kKElems = KIND == 2 ? 32 : 64;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -236,6 +237,70 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
       ++i;
+      if (ep.gu_counters) {
+        // ---- fused SwiGLU consumer: the last of the 2 * splits contributors of a (gate, up) tile pair finishes it.
+        // bar.sync orders the eight epilogue warps' partial stores before the elected thread's gpu-scope acq_rel
+        // atomic (the CUTLASS semaphore pattern); the slabs are then read through L2 (ld.cg), never through L1.
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const int pair = tile % (tiles >> 1);
+        if (warp == 2 && lane == 0) {
+          int old;
+          asm volatile("atom.add.acq_rel.gpu.global.s32 %0, [%1], 1;" : "=r"(old) : "l"(ep.gu_counters + pair) : "memory");
+          const int last = old == 2 * splits - 1;
+          if (last) ep.gu_counters[pair] = 0;          // nobody touches it again before the next launch
+          *gu_last = last;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (*gu_last) {
+          const int I = ep.N >> 1;
+          const int e = threadIdx.x - 64;               // 0..255 over the epilogue warps
+          const int f4 = e & 31;                        // 32 float4 = the pair's 128 features
+          const long long slab = static_cast<long long>(ep.M) * ep.N;
+          bf16* act = reinterpret_cast<bf16*>(ep.gu_act);
+          for (int m0 = e >> 5; m0 < rowsB; m0 += 32) { // rows m0, m0 + 8, m0 + 16, m0 + 24: their loads fly together
+            float a[4][4], c[4][4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) a[r][j] = c[r][j] = 0.f;
+            for (int s0 = 0; s0 < splits; s0 += 3) {
+              float4 x[4][3], y[4][3];
+#pragma unroll
+              for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int t = 0; t < 3; ++t) {
+                  const int m = m0 + 8 * r;
+                  if (m < rowsB && s0 + t < splits) {
+                    const float* pp = ep.partial + (s0 + t) * slab + static_cast<long long>(m) * ep.N + pair * 128 + 4 * f4;
+                    x[r][t] = __ldcg(reinterpret_cast<const float4*>(pp));
+                    y[r][t] = __ldcg(reinterpret_cast<const float4*>(pp + I));
+                  }
+                }
+#pragma unroll
+              for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int t = 0; t < 3; ++t)
+                  if (m0 + 8 * r < rowsB && s0 + t < splits) {
+                    a[r][0] += x[r][t].x; a[r][1] += x[r][t].y; a[r][2] += x[r][t].z; a[r][3] += x[r][t].w;
+                    c[r][0] += y[r][t].x; c[r][1] += y[r][t].y; c[r][2] += y[r][t].z; c[r][3] += y[r][t].w;
+                  }
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+              const int m = m0 + 8 * r;
+              if (m >= rowsB) continue;
+              float o[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float gg = rbf(a[r][j]), uu = rbf(c[r][j]);
+                o[j] = rbf(gg / (1.f + expf(-gg))) * uu;
+              }
+              uint2 pk; pk.x = pack_bf16(o[0], o[1]); pk.y = pack_bf16(o[2], o[3]);
+              *reinterpret_cast<uint2*>(act + static_cast<long long>(m) * I + pair * 128 + 4 * f4) = pk;
+            }
+          }
+        }
+      }
     }
     if (warp == 2 && lane == 0) stamp(7);
   }
@@ -271,6 +336,8 @@ int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, in
 }
 
 }  // namespace
+
+static inline bool bf_in(int dtype) { return dtype == MT_DTYPE_BF16; }
 
 // Split count for the persistent kernel: minimise the longest CTA's work, counted in k-blocks, with every
 // unit charged ~2 k-blocks for its epilogue (a [128 x BN] fp32 partial tile costs about as much traffic).
@@ -315,6 +382,11 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
     ep.partial = p.workspace;
   } else if (splits > 1) {
     ep.partial = p.workspace;
+  }
+  if (p.gu_counters) {
+    MT_CHECK(p.out_splits && p.gu_act && p.N % 256 == 0 && !p.tile_filter_flag && bf_in(p.dtype_in),
+             "linear_dec: the fused SwiGLU consumer needs out_splits, bf16 inputs and N = 2I with I %% 128 == 0 (N=%d)", p.N);
+    ep.gu_counters = p.gu_counters; ep.gu_act = p.gu_act;
   }
   const int w_tiled = p.w_tiled ? 1 : 0;
   // a filtered launch decides its unit list after the dependency wait: no early weight fetch

@@ -405,6 +405,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   ep.out = p.out; ep.ldo = p.ldo; ep.out_f32 = out_kind(p.dtype_out);
   ep.bias = p.bias; ep.act = p.act; ep.residual = p.residual; ep.ldr = p.ldr; ep.scale = p.scale;
   ep.round_bf16 = p.round_bf16; ep.M = p.M; ep.N = p.N; ep.partial = nullptr;
+  ep.gu_counters = nullptr; ep.gu_act = nullptr;
 
   if (p.impl == MT_GEMM_SIMT || g_force_simt) {
     if (p.out_splits) { *p.out_splits = 1; ep.partial = p.workspace; }
