@@ -3,8 +3,8 @@
 Workload (BASELINE.json configs[1]): MossTTSDelay, assumed released 8B shape (Qwen3-8B backbone,
 n_vq=32, random-init bf16 weights, never-stop head tie), batch 64 utterances per GPU, 96-token
 prompt, 156 greedy steps = 125 codec frames = 10 s of audio per utterance, then
-MOSS-Audio-Tokenizer (released config.json shape, fp32 storage / TF32 tensor-core math) RVQ
-dequantise + decoder to a 24 kHz waveform.  One "step" = that whole pass over one batch.
+MOSS-Audio-Tokenizer (released config.json shape; fp32 residual stream and accumulation, fp16-operand
+tensor-core GEMMs / attention in the transformer blocks) RVQ dequantise + decoder to a 24 kHz waveform.  One "step" = that whole pass over one batch.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 For N > 1 launch with torchrun (one rank per GPU); ranks shard the utterances (weak scaling).
@@ -315,7 +315,9 @@ def run_ours(args):
                                "+ MOSS-Audio-Tokenizer decode to 24 kHz" + (" [SMALL DEBUG SHAPES]" if args.small else ""),
                    "lm_shape": "assumed released 8B = Qwen3-8B backbone H4096 L36 32q/8kv x128 I12288 n_vq32 (hub-only config)"
                    if not args.small else "mid debug shape",
-                   "codec": "config.json decoder (32+12+12+12 layers), fp32 storage, TF32 tensor-core GEMMs",
+                   "codec": "config.json decoder (32+12+12+12 layers): fp32 residual stream / accumulation / softmax / LayerNorm, "
+                            "fp16-operand tensor-core GEMMs and attention in the transformer blocks (TF32's mantissa), TF32 stage "
+                            "projections; waveform SNR vs the fp32 reference 48.9-50.9 dB (gate: >= 40 dB)",
                    "batch_per_gpu": B, "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "frames": FRAMES,
                    "sharding": f"request-sharded x{world}, no in-step collective",
                    "l2_policy": "inputs larger than L2: 15.4 GB of weights streamed every decode step"},
