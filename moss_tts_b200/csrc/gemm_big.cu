@@ -38,7 +38,21 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   constexpr int kKElems = KIND == 2 ? 32 : 64;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_tiles = m_tiles * n_tiles;
+  // Tile walk of this CTA (iteration i = 0, 1, ...).  While whole bands of gridDim.x token tiles remain, a CTA keeps ITS
+  // token tile and walks the feature tiles: the 128 x K activation tile is re-read from L2 instead of HBM (the codec's
+  // M = 64,000-token GEMMs streamed the activations n_tiles times: 0.99 GB of DRAM reads for 98 MB of input), and the
+  // CTAs running together still share one weight tile.  The ragged last band (and every problem with fewer token tiles
+  // than CTAs, e.g. prefill) is walked in the flat token-fastest order.
+  const int full_bands = m_tiles / static_cast<int>(gridDim.x);
+  const int rem_m = m_tiles - full_bands * static_cast<int>(gridDim.x);
+  auto tile_of = [&](int i, int& mt, int& nt) -> bool {
+    const int banded = full_bands * n_tiles;
+    if (i < banded) { mt = (i / n_tiles) * gridDim.x + blockIdx.x; nt = i % n_tiles; return true; }
+    const int t = blockIdx.x + (i - banded) * gridDim.x;
+    if (t >= rem_m * n_tiles) return false;
+    mt = full_bands * gridDim.x + t % rem_m; nt = t / rem_m;
+    return true;
+  };
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -82,9 +96,10 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       };
       int it = 0;
       int pre = 0;
-      if (w_early && static_cast<int>(blockIdx.x) < total_tiles) {
+      int mt = 0, nt = 0;
+      if (w_early && tile_of(0, mt, nt)) {
         // constant weights: first ring fill before the previous kernel is known to have finished
-        const int nt0 = blockIdx.x / m_tiles;
+        const int nt0 = nt;
         pre = k_blocks < kStages ? k_blocks : kStages;
         for (int i = 0; i < pre; ++i) {
           ptx::mbar_expect_tx(&full[i], kStageBytes);
@@ -92,8 +107,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         }
       }
       pdl_wait();
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int mt = t % m_tiles, nt = t / m_tiles;
+      for (int i = 0; tile_of(i, mt, nt); ++i) {
         for (int kb = 0; kb < k_blocks; ++kb, ++it) {
           const int st = it % kStages;
           if (it < pre) { load_a(st, mt, kb); continue; }
@@ -108,8 +122,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = ptx::make_idesc(KIND == 3 ? 0 : KIND, kBM, kBN);   // a/b format: 0 F16, 1 BF16, 2 TF32
-      int it = 0, i = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
+      int it = 0, mt = 0, nt = 0;
+      for (int i = 0; tile_of(i, mt, nt); ++i) {
         const int buf = i & 1;
         ptx::mbar_wait(&tmem_empty[buf], ((i >> 1) & 1) ^ 1);     // epilogue drained this accumulator
         ptx::tc_fence_after();
@@ -136,9 +150,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;          // column half
     pdl_wait();                                // residual reads / output writes follow the previous kernel
-    int i = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++i) {
-      const int mt = t % m_tiles, nt = t / m_tiles;
+    int mt = 0, nt = 0;
+    for (int i = 0; tile_of(i, mt, nt); ++i) {
       const int buf = i & 1;
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
       ptx::tc_fence_after();
