@@ -124,11 +124,21 @@ class OracleCodec:
             return out
         return rot(q), rot(k)
 
-    def _visible(self, T: int, context: int, chunk: Optional[int]) -> torch.Tensor:
-        """Boolean [T,T] (query, key) visibility; see module docstring for the chunked form."""
+    def _visible(self, T: int, context: int, chunk, up: int = 1) -> torch.Tensor:
+        """Boolean [T,T] (query, key) visibility; see module docstring for the chunked form.
+        chunk: None, a uniform chunk length in tokens, or a list of per-push lengths in FRAMES (streaming pushes of
+        uneven size, `with model.streaming(B): _decode_frame(...)` repeatedly; scaled by `up` tokens per frame)."""
         qp = torch.arange(T)[:, None]
         kp = torch.arange(T)[None, :]
         vis = (kp <= qp) & (qp - kp < context)
+        if isinstance(chunk, (list, tuple)):
+            end = torch.zeros(T, dtype=torch.long)
+            pos = 0
+            for n in chunk:
+                end[pos: pos + n * up] = pos + n * up
+                pos += n * up
+            assert pos == T, (pos, T)
+            return vis & (kp >= end[:, None] - context)
         if chunk is not None and T > chunk:
             start = (qp // chunk) * chunk
             ln = torch.clamp(T - start, max=chunk)
@@ -144,7 +154,10 @@ class OracleCodec:
             x = x @ self.w[base + "input_proj.weight"].T
         B, T, d = x.shape
         hd = d // st.num_heads
-        vis = self._visible(T, st.context, None if chunk_frames is None else chunk_frames * up)
+        if isinstance(chunk_frames, (list, tuple)):
+            vis = self._visible(T, st.context, chunk_frames, up)
+        else:
+            vis = self._visible(T, st.context, None if chunk_frames is None else chunk_frames * up)
         for l in range(st.num_layers):
             p = base + f"transformer.layers.{l}."
             h = F.layer_norm(x, (d,), self.w[p + "norm1.weight"], self.w[p + "norm1.bias"], 1e-5)
