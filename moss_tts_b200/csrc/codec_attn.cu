@@ -240,9 +240,14 @@ __device__ __forceinline__ uint4 rope8(uint4 raw, const float4* __restrict__ rop
   return o;
 }
 
+// RING = true: streaming push.  Queries are the T new tokens (absolute positions pos0 + row); keys live in the layer's ring
+// cache (already rotated) at slot = position % cap; `context` carries cap and the visible range of every row starts at
+// max(pos0 + T - cap, 0).  Key positions, not rows, drive the tile loop.
+template <bool RING>
 __global__ void __launch_bounds__(kHWarps * 32, 2)
 codec_attention_f16_kernel(const __half* __restrict__ qkv, __half* __restrict__ out, int T, int heads, int context,
-                           int chunk, float scale, const float4* __restrict__ rope) {
+                           int chunk, float scale, const float4* __restrict__ rope, const __half* __restrict__ ring,
+                           int pos0) {
   __shared__ __align__(16) __half sm[2 * kK * kHPitch];        // K tile | V tile (both: the 128-row Q tile first)
   __half* sk = sm;
   __half* sv = sm + kK * kHPitch;
@@ -273,23 +278,34 @@ codec_attention_f16_kernel(const __half* __restrict__ qkv, __half* __restrict__ 
     for (int s = 0; s < kD / 16; ++s) ldsm_x4(qa[s], base + 16 * s);
   }
   const int row0 = q0 + warp * 16 + g, row1 = row0 + 8;
-  const int lo0 = vis_lo(min(row0, T - 1), T, context, chunk), lo1 = vis_lo(min(row1, T - 1), T, context, chunk);
-  const int wfirst = q0 + warp * 16, wlast = min(wfirst + 15, T - 1);      // this warp's query rows
-  const int wlo = vis_lo(min(wfirst, T - 1), T, context, chunk);           // lowest key any of them sees (lo is monotone)
+  const int ring_lo = max(pos0 + T - context, 0);
+  // from here on rows and keys are compared as POSITIONS (pos0 = 0 outside streaming)
+  const int p0 = pos0 + row0, p1 = pos0 + row1;
+  const int lo0 = RING ? ring_lo : vis_lo(min(row0, T - 1), T, context, chunk);
+  const int lo1 = RING ? ring_lo : vis_lo(min(row1, T - 1), T, context, chunk);
+  const int wfirst = q0 + warp * 16, wlast = pos0 + min(wfirst + 15, T - 1);   // this warp's query rows / last position
+  const int wlo = RING ? ring_lo : vis_lo(min(wfirst, T - 1), T, context, chunk);   // lowest key any of them sees
   float o[kD / 8][4];
 #pragma unroll
   for (int n = 0; n < kD / 8; ++n) { o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f; }
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
-  const int last_q = min(q0 + kHQ, T) - 1;
-  const int k_begin = (vis_lo(q0, T, context, chunk) / kK) * kK;
-  const int lo_last = vis_lo(last_q, T, context, chunk);
+  const int last_q = pos0 + min(q0 + kHQ, T) - 1;                 // position of the CTA's last query
+  const int k_begin = ((RING ? ring_lo : vis_lo(q0, T, context, chunk)) / kK) * kK;
+  const int lo_last = RING ? ring_lo : vis_lo(last_q, T, context, chunk);
   for (int k0 = k_begin; k0 <= last_q; k0 += kK) {
     __syncthreads();                                            // previous tile (or the Q staging) is consumed
     for (int i = threadIdx.x; i < kK * (kD / 8); i += kHWarps * 32) {
       const int r = i / (kD / 8), c = i % (kD / 8);
       uint4 kv = make_uint4(0u, 0u, 0u, 0u), vv = kv;
-      if (k0 + r < T) {
+      if constexpr (RING) {
+        const int kp = k0 + r;
+        if (kp >= ring_lo && kp < pos0 + T) {
+          const __half* base = ring + ((static_cast<long long>(b) * context + kp % context) * 2) * d + h * kD + 8 * c;
+          kv = *reinterpret_cast<const uint4*>(base);
+          vv = *reinterpret_cast<const uint4*>(base + d);
+        }
+      } else if (k0 + r < T) {
         const __half* base = qkv + (tok0 + k0 + r) * 3 * d + h * kD + 8 * c;
         kv = rope8(*reinterpret_cast<const uint4*>(base + d), rope, k0 + r, c, 1.f);
         vv = *reinterpret_cast<const uint4*>(base + 2 * d);
@@ -316,16 +332,16 @@ codec_attention_f16_kernel(const __half* __restrict__ qkv, __half* __restrict__ 
       mma_f16_16816(sc[n], qa[3], kb[2], kb[3]);
     }
     // ---- mask (edge tiles only), row max
-    const bool interior = k0 + kK - 1 <= q0 && k0 >= lo_last;
+    const bool interior = k0 + kK - 1 <= pos0 + q0 && k0 >= lo_last;
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
     for (int n = 0; n < kK / 8; ++n) {
       if (!interior) {
         const int ka = k0 + 8 * n + 2 * t4, kb2 = ka + 1;
-        if (ka < lo0 || ka > row0) sc[n][0] = -INFINITY;
-        if (kb2 < lo0 || kb2 > row0) sc[n][1] = -INFINITY;
-        if (ka < lo1 || ka > row1) sc[n][2] = -INFINITY;
-        if (kb2 < lo1 || kb2 > row1) sc[n][3] = -INFINITY;
+        if (ka < lo0 || ka > p0) sc[n][0] = -INFINITY;
+        if (kb2 < lo0 || kb2 > p0) sc[n][1] = -INFINITY;
+        if (ka < lo1 || ka > p1) sc[n][2] = -INFINITY;
+        if (kb2 < lo1 || kb2 > p1) sc[n][3] = -INFINITY;
       }
       mx0 = fmaxf(mx0, fmaxf(sc[n][0], sc[n][1]));
       mx1 = fmaxf(mx1, fmaxf(sc[n][2], sc[n][3]));
@@ -383,9 +399,56 @@ int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int
   if (hd != kD) return fail(MT_ERR_UNSUPPORTED, "codec attention supports head_dim 64 only (got %d)", hd);
   MT_CHECK(rope_table, "codec_attention_f16: the RoPE table is required");
   dim3 grid(cdiv(T, kHQ), heads, B);
-  MT_CUDA(launch(codec_attention_f16_kernel, grid, dim3(kHWarps * 32), 0, s, reinterpret_cast<const __half*>(qkv),
+  MT_CUDA(launch(codec_attention_f16_kernel<false>, grid, dim3(kHWarps * 32), 0, s, reinterpret_cast<const __half*>(qkv),
                  reinterpret_cast<__half*>(out), T, heads, context, chunk, 1.0f / sqrtf(static_cast<float>(hd)),
-                 reinterpret_cast<const float4*>(rope_table)));
+                 reinterpret_cast<const float4*>(rope_table), static_cast<const __half*>(nullptr), 0));
+  count_launch();
+  return MT_OK;
+}
+
+namespace {
+// new tokens' k (rotated: table row t = position pos0 + t) and v -> ring slots (pos0 + t) % cap; 8 halves per thread
+__global__ void codec_kv_append_kernel(const __half* __restrict__ qkv, __half* __restrict__ ring, int T, int d, int cap,
+                                       int pos0, const float4* __restrict__ rope, long long total) {
+  pdl_trigger();
+  pdl_wait();
+  const int d8 = d / 8;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long tok = idx / d8;                 // b * T + t
+    const int c8 = static_cast<int>(idx % d8);      // 8-half column group inside the d-wide k (or v) vector
+    const int b = static_cast<int>(tok / T), t = static_cast<int>(tok % T);
+    const __half* src = qkv + tok * 3 * d + 8 * c8;
+    const uint4 k = rope8(*reinterpret_cast<const uint4*>(src + d), rope, t, c8 % (kD / 8), 1.f);
+    const uint4 v = *reinterpret_cast<const uint4*>(src + 2 * d);
+    __half* dst = ring + ((static_cast<long long>(b) * cap + (pos0 + t) % cap) * 2) * d + 8 * c8;
+    *reinterpret_cast<uint4*>(dst) = k;
+    *reinterpret_cast<uint4*>(dst + d) = v;
+  }
+}
+}  // namespace
+
+int codec_kv_append_f16(const void* qkv, void* ring, int B, int T, int heads, int cap, long long pos0, const float* rope_table,
+                        cudaStream_t s) {
+  MT_CHECK(rope_table && T <= cap, "codec_kv_append_f16: a push of %d tokens exceeds the ring capacity %d", T, cap);
+  MT_CHECK(pos0 + T < (1ll << 31), "codec stream position overflow");
+  const int d = heads * kD;
+  const long long total = static_cast<long long>(B) * T * (d / 8);
+  int blocks = static_cast<int>(cdivll(total, 256));
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  MT_CUDA(launch(codec_kv_append_kernel, dim3(blocks), dim3(256), 0, s, reinterpret_cast<const __half*>(qkv),
+                 reinterpret_cast<__half*>(ring), T, d, cap, static_cast<int>(pos0), reinterpret_cast<const float4*>(rope_table), total));
+  count_launch();
+  return MT_OK;
+}
+
+int codec_attention_ring_f16(const void* qkv, const void* ring, void* out, int B, int T, int heads, int cap, long long pos0,
+                             cudaStream_t s, const float* rope_table) {
+  MT_CHECK(rope_table && ring, "codec_attention_ring_f16: null argument");
+  dim3 grid(cdiv(T, kHQ), heads, B);
+  MT_CUDA(launch(codec_attention_f16_kernel<true>, grid, dim3(kHWarps * 32), 0, s, reinterpret_cast<const __half*>(qkv),
+                 reinterpret_cast<__half*>(out), T, heads, cap, 0, 1.0f / sqrtf(static_cast<float>(kD)),
+                 reinterpret_cast<const float4*>(rope_table), reinterpret_cast<const __half*>(ring), static_cast<int>(pos0)));
   count_launch();
   return MT_OK;
 }

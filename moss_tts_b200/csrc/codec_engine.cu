@@ -4,6 +4,7 @@
 // linear2*scale+res) -> output_proj -> patch upsample].  Linear layers run on the tcgen05 GEMM with
 // fp32 storage / TF32 math; LayerScale + residual and GELU are GEMM epilogues.
 #include "codec_ops.cuh"
+#include <cuda_fp16.h>
 
 #include <stdlib.h>
 #include <vector>
@@ -123,7 +124,8 @@ extern "C" int mt_rvq_dequant(const mt_codec* h, const int64_t* codes, int nq, i
 // input_proj + the transformer layers of stage `st` for nb samples x Ts tokens (M = nb*Ts rows of `in`); the stage's
 // activations are left in x [M, d_model].  `y` (y_floats floats) parks the stage's RoPE table while the layers run.
 static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, int nb, long long Ts, int chunk,
-                          float* x, float* hbuf, float* qkv, float* ff, float* y, long long y_floats, cudaStream_t s) {
+                          float* x, float* hbuf, float* qkv, float* ff, float* y, long long y_floats, cudaStream_t s,
+                          __half* ring = nullptr, long long ring_layer_halves = 0, long long pos0 = 0) {
   const mt_codec_config& c = h->cfg;
   const int d = c.d_model[st], heads = c.num_heads[st], ffd = c.dim_ff[st];
   MT_CHECK(M < (1ll << 31), "codec: too many tokens in one group");
@@ -133,7 +135,7 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
   // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
   const bool table_fits = static_cast<long long>(Ts) * 64 <= y_floats;
-  if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s));
+  if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s, pos0));
   // layer_gemm_f16: hbuf, qkv and ff hold IEEE half values (GEMM / attention operands); the residual stream x stays fp32
   const int h16 = c.layer_gemm_f16 ? 1 : 0;
   const int din = h16 ? MT_DTYPE_F16 : MT_DTYPE_F32;
@@ -146,7 +148,13 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
     const mt_codec_layer& L = h->layers[st][l];
     MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
     MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32));
-    if (a16) {
+    if (ring) {
+      // streaming push: the layer's ring cache takes the new keys / values, the new queries attend to the ring
+      MT_CHECK(a16, "codec streaming needs layer_gemm_f16 = 1 (half ring caches)");
+      __half* lr = ring + l * ring_layer_halves;
+      MT_TRY(codec_kv_append_f16(qkv, lr, nb, static_cast<int>(Ts), heads, c.context[st], pos0, y, s));
+      MT_TRY(codec_attention_ring_f16(qkv, lr, hbuf, nb, static_cast<int>(Ts), heads, c.context[st], pos0, s, y));
+    } else if (a16) {
       MT_TRY(codec_attention_f16(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
     } else if (simt_attn || !table_fits) {
       MT_TRY(codec_rope(qkv, M, static_cast<int>(Ts), d, 64, c.max_period, s));
@@ -164,8 +172,10 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
 }
 
 // decode `nb` samples starting at batch offset b0 (codes are [nq, B, T]: sample stride T, quantizer stride B*T)
+struct StreamRef { __half* cache; const long long* stage_off; const long long* layer_halves; long long frames_done; };
+
 static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T, int b0, int nb, int chunk_frames,
-                        float* wav, float* ws, cudaStream_t s) {
+                        float* wav, float* ws, cudaStream_t s, const StreamRef* sr = nullptr) {
   const mt_codec_config& c = h->cfg;
   long long xs, qs, fs, ys, es;
   per_sample_floats(c, T, &xs, &qs, &fs, &ys, &es);
@@ -188,8 +198,12 @@ static int decode_group(mt_codec* h, const int64_t* codes, int nq, int B, int T,
   for (int st = 0; st < c.num_stages; ++st) {
     const int d = c.d_model[st];
     const long long M = Ts * nb;
-    MT_TRY(run_stage_layers(h, st, in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
-                            x, hbuf, qkv, ff, y, ys * nb, s));
+    if (sr)
+      MT_TRY(run_stage_layers(h, st, in, M, nb, Ts, 0, x, hbuf, qkv, ff, y, ys * nb, s, sr->cache + sr->stage_off[st],
+                              sr->layer_halves[st], sr->frames_done * (Ts / T)));
+    else
+      MT_TRY(run_stage_layers(h, st, in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
+                              x, hbuf, qkv, ff, y, ys * nb, s));
     const bool last = st + 1 == c.num_stages;
     const int od = c.output_dim[st], p = c.patch[st];
     const bool identity_patch = od == p;           // one output channel: the reshape is the identity
@@ -326,3 +340,64 @@ extern "C" int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, cons
   }
   return MT_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// incremental streaming decode (model.streaming(batch_size) + _decode_frame per push)
+// ---------------------------------------------------------------------------------------------
+struct mt_codec_stream {
+  mt_codec* h;
+  int B;
+  __half* cache;
+  long long stage_off[MT_CODEC_MAX_STAGES], layer_halves[MT_CODEC_MAX_STAGES];
+  long long frames_done;
+};
+
+static long long stream_layout(const mt_codec* h, int B, long long* stage_off, long long* layer_halves) {
+  const mt_codec_config& c = h->cfg;
+  long long off = 0;
+  for (int s = 0; s < c.num_stages; ++s) {
+    const long long lh = static_cast<long long>(B) * c.context[s] * 2 * c.d_model[s];
+    if (stage_off) { stage_off[s] = off; layer_halves[s] = lh; }
+    off += lh * c.num_layers[s];
+  }
+  return off;
+}
+
+extern "C" int mt_codec_stream_bytes(const mt_codec* h, int B, long long* bytes) {
+  MT_CHECK(h && bytes && B > 0, "mt_codec_stream_bytes: bad argument");
+  *bytes = stream_layout(h, B, nullptr, nullptr) * 2 + 256;
+  return MT_OK;
+}
+
+extern "C" int mt_codec_stream_begin(mt_codec* h, int B, void* cache, long long cache_bytes, mt_codec_stream** out) {
+  MT_CHECK(h && cache && out && B > 0, "mt_codec_stream_begin: bad argument");
+  MT_CHECK(!h->cfg.encoder, "mt_codec_stream_begin: streaming is implemented for the decoder");
+  if (!h->cfg.layer_gemm_f16) return fail(MT_ERR_UNSUPPORTED, "codec streaming needs a codec built with layer_gemm_f16 = 1");
+  long long need = 0;
+  MT_TRY(mt_codec_stream_bytes(h, B, &need));
+  MT_CHECK(cache_bytes >= need, "mt_codec_stream_begin: cache of %lld bytes, %lld needed", cache_bytes, need);
+  mt_codec_stream* st = new mt_codec_stream();
+  st->h = h; st->B = B; st->cache = reinterpret_cast<__half*>(cache); st->frames_done = 0;
+  stream_layout(h, B, st->stage_off, st->layer_halves);
+  *out = st;
+  return MT_OK;
+}
+
+extern "C" int mt_codec_stream_push(mt_codec_stream* st, const int64_t* codes, int nq, int T, float* wav, void* workspace,
+                                    long long workspace_bytes, mt_stream stream) {
+  MT_CHECK(st && codes && wav && workspace, "mt_codec_stream_push: null argument");
+  mt_codec* h = st->h;
+  MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
+  MT_CHECK(T > 0, "mt_codec_stream_push: empty push");
+  MT_CHECK(T <= h->cfg.context[0], "mt_codec_stream_push: %d frames exceed the ring capacity (%d frames of context)", T, h->cfg.context[0]);
+  long long need = 0;
+  MT_TRY(mt_codec_workspace_bytes(h, st->B, T, &need));
+  MT_CHECK(workspace_bytes >= need, "mt_codec_stream_push: workspace of %lld bytes, %lld needed", workspace_bytes, need);
+  StreamRef sr{st->cache, st->stage_off, st->layer_halves, st->frames_done};
+  MT_TRY(decode_group(h, codes, nq, st->B, T, 0, st->B, 0, wav, reinterpret_cast<float*>(workspace),
+                      reinterpret_cast<cudaStream_t>(stream), &sr));
+  st->frames_done += T;
+  return MT_OK;
+}
+
+extern "C" int mt_codec_stream_end(mt_codec_stream* st) { delete st; return MT_OK; }

@@ -244,19 +244,19 @@ __global__ void codec_rope_kernel(float* __restrict__ qkv, long long M, int T, i
     *p = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
   }
 }
-__global__ void codec_rope_table_kernel(float2* __restrict__ table, int T, int hd, float log_period) {
+__global__ void codec_rope_table_kernel(float2* __restrict__ table, int T, int hd, float log_period, long long pos0) {
   const int total = T * (hd / 2);
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
     const int t = idx / (hd / 2), j = idx % (hd / 2);
     const float freq = expf(static_cast<float>(j) * (-log_period * 2.f / hd));     // same expressions as codec_rope_kernel
     float sn, cs;
-    sincosf(freq * static_cast<float>(t), &sn, &cs);
+    sincosf(freq * static_cast<float>(pos0 + t), &sn, &cs);     // fp32 angle of the absolute position, as the reference
     table[idx] = make_float2(cs, sn);
   }
 }
-int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s) {
+int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s, long long pos0) {
   const int total = T * (hd / 2);
-  codec_rope_table_kernel<<<(total + 255) / 256, 256, 0, s>>>(reinterpret_cast<float2*>(table), T, hd, logf(max_period));
+  codec_rope_table_kernel<<<(total + 255) / 256, 256, 0, s>>>(reinterpret_cast<float2*>(table), T, hd, logf(max_period), pos0);
   count_launch();
   MT_LAUNCH_CHECK();
   return MT_OK;

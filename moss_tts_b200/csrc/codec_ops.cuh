@@ -17,13 +17,22 @@ int codec_attention(const float* qkv, float* out, int B, int T, int heads, int h
                     cudaStream_t s);
 // tensor-core (TF32 mma) version of codec_attention: the product path (codec_attn.cu)
 // (cos, sin) of every (position, pair) as codec_rope computes them: table[t * hd/2 + j] = (cos, sin)(t * freq_j)
-int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s);
+// pos0: absolute position of table row 0 (streaming pushes)
+int codec_rope_table(float* table, int T, int hd, float max_period, cudaStream_t s, long long pos0 = 0);
 // rope_table != nullptr: q and k are rotated while they are staged (no separate codec_rope pass over qkv)
 int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, int hd, int context, int chunk,
                        cudaStream_t s, const float* rope_table = nullptr, int out_f16 = 0);
 // fp16 flavour (codec_attn.cu): qkv [B*T, 3*heads*64] and out [B*T, heads*64] are IEEE half; RoPE table required
 int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk,
                         cudaStream_t s, const float* rope_table);
+// Streaming decode (RingKVCache :413-480, MHAState :488-499).  ring: one layer's cache [B][cap][2][heads*64] half, slot =
+// position % cap, K stored AFTER RoPE (as the reference caches it).  kv_append rotates the new tokens' keys (table row t =
+// position pos0 + t) and writes k, v into their slots; the attention then reads q from qkv (rotated on the way in) and
+// K / V from the ring: visible keys of every query of the push are [max(pos0 + T - cap, 0), its own position].
+int codec_kv_append_f16(const void* qkv, void* ring, int B, int T, int heads, int cap, long long pos0, const float* rope_table,
+                        cudaStream_t s);
+int codec_attention_ring_f16(const void* qkv, const void* ring, void* out, int B, int T, int heads, int cap, long long pos0,
+                             cudaStream_t s, const float* rope_table);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
 // encode side (codec_enc.cu)
 using QuantWeights = mt_codec_quant_weights;

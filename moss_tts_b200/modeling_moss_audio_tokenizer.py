@@ -17,6 +17,7 @@ Differences from the reference, all output-preserving:
 from __future__ import annotations
 
 import ctypes as C
+from contextlib import contextmanager
 from dataclasses import dataclass
 from typing import Dict, List, Optional
 
@@ -299,6 +300,43 @@ class MossAudioTokenizerModel:
             self._ws = torch.empty(want, dtype=torch.uint8, device=self.device)
         return self._ws
 
+    # ---- streaming (reference :1393-1400, StreamingModule :121-177, RingKVCache :413-480) ------------------
+    @contextmanager
+    def streaming(self, batch_size: int = 1):
+        """`with model.streaming(batch_size): model._decode_frame(chunk)` per push: every decoder layer keeps a ring
+        cache of `context` tokens on the device between pushes (mt_codec_stream_*).  Decode side only."""
+        if getattr(self, "_stream", None) is not None:
+            raise RuntimeError("MossAudioTokenizerModel is already streaming!")
+        need = C.c_longlong(0)
+        L.check(L.lib().mt_codec_stream_bytes(self._engine, int(batch_size), C.byref(need)), "mt_codec_stream_bytes")
+        cache = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+        h = C.c_void_p()
+        L.check(L.lib().mt_codec_stream_begin(self._engine, int(batch_size), L.ptr(cache), C.c_longlong(cache.numel()),
+                                              C.byref(h)), "mt_codec_stream_begin")
+        self._stream, self._stream_batch, self._stream_cache = h, int(batch_size), cache
+        try:
+            yield
+        finally:
+            torch.cuda.current_stream(self.device).synchronize()
+            L.lib().mt_codec_stream_end(self._stream)
+            self._stream = self._stream_cache = None
+
+    def _stream_push(self, codes: torch.Tensor, codes_lengths: torch.Tensor) -> MossAudioTokenizerDecoderOutput:
+        nq, B, T = codes.shape
+        if B != self._stream_batch:
+            raise ValueError(f"streaming batch size is {self._stream_batch}, got {B}")
+        wav = torch.empty(B, 1, T * self.downsample_rate, dtype=torch.float32, device=self.device)
+        if T > 0:
+            ws = self._workspace(B, T)
+            need = C.c_longlong(0)
+            L.check(L.lib().mt_codec_workspace_bytes(self._engine, B, T, C.byref(need)), "mt_codec_workspace_bytes")
+            if ws.numel() < need.value:
+                raise L.MossTTSNativeError("codec workspace too small for a streaming push of the whole batch")
+            with torch.cuda.device(self.device):
+                L.check(L.lib().mt_codec_stream_push(self._stream, L.ptr(codes), nq, T, L.ptr(wav), L.ptr(ws),
+                                                     C.c_longlong(ws.numel()), L.stream_ptr(self.device)), "mt_codec_stream_push")
+        return MossAudioTokenizerDecoderOutput(audio=wav, audio_lengths=codes_lengths.to(self.device) * self.downsample_rate)
+
     # ---- reference surface ----------------------------------------------------------------------
     @torch.inference_mode()
     def _decode_frame(self, codes: torch.Tensor, codes_lengths: Optional[torch.Tensor] = None,
@@ -307,6 +345,11 @@ class MossAudioTokenizerModel:
         codes = codes.to(device=self.device, dtype=torch.int64).contiguous()
         if codes_lengths is None:
             codes_lengths = torch.full((B,), T, device=self.device, dtype=torch.long)
+        if getattr(self, "_stream", None) is not None:
+            if chunk_frames:
+                # the reference would enter decoder_module.streaming() a second time here (:1732)
+                raise RuntimeError("decoder is already streaming!")
+            return self._stream_push(codes, codes_lengths)
         wav = torch.empty(B, 1, T * self.downsample_rate, dtype=torch.float32, device=self.device)
         if B * T > 0:
             ws = self._workspace(B, T)
