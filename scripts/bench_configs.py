@@ -2,6 +2,7 @@
   C3  codec decode sweep                     B in {1,4,16,64,256} x T in {13,63,125,375,750} frames
   C4  MossTTSLocal (assumed 1.7B shape)      B = 128, 96-token prompt, 125 frames, n_vq_for_inference = 32
   C5  MossTTSDelay n_vq = 16 long context    B = 4, ~512-token prompt, 3765 steps (>= 5 min of audio)
+  stream  incremental streaming decode: per-push latency (SURVEY §8f rank 3 building block)
   enc codec ENCODE sweep B in {1,16,64} x {1,10,30} s of 24 kHz audio -> 32 codebooks
 One JSON line per measurement; device-timed with CUDA events after a warm-up call.
 
@@ -66,6 +67,27 @@ def enc(args, dev):
                               "ms_quantiser_alone": ms_q}), flush=True)
 
 
+def stream(args, dev):
+    """Incremental streaming decode at the released shape: per-push latency for 0.32 s pushes (4 frames, what
+    moss_tts_realtime's AudioStreamDecoder uses), steady state = ring caches full (10 s of context)."""
+    from moss_tts_b200.config import CodecConfig
+    from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+    ccfg = CodecConfig.released()
+    codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=8 << 30)
+    for B, n in ((1, 4), (1, 1), (16, 4), (64, 4)):
+        pushes = 60 if n == 4 else 160
+        codes = torch.randint(0, 1024, (ccfg.num_quantizers, B, n * pushes), device=dev)
+        ms = []
+        with codec.streaming(batch_size=B):
+            for i in range(pushes):
+                t, _ = timed(lambda: codec._decode_frame(codes[:, :, i * n: (i + 1) * n]))
+                ms.append(t)
+        tail = sorted(ms[len(ms) // 2:])
+        print(json.dumps({"config": "codec streaming decode (released shape, ring KV caches)", "B": B, "frames_per_push": n,
+                          "audio_ms_per_push": n * 80, "first_push_ms": ms[0], "steady_push_ms_median": tail[len(tail) // 2],
+                          "realtime_factor": B * n * 80 / tail[len(tail) // 2]}), flush=True)
+
+
 def c4(args, dev):
     from moss_tts_b200.config import LocalConfig
     from moss_tts_b200.modeling_moss_tts_local import MossTTSLocalModel
@@ -124,7 +146,7 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     for w in args.what.split(","):
-        {"c3": c3, "c4": c4, "c5": c5, "enc": enc}[w](args, dev)
+        {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream}[w](args, dev)
         torch.cuda.empty_cache()
 
 
