@@ -294,6 +294,9 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   sc.text_top_p = p->text_top_p; sc.text_top_k = p->text_top_k;
   sc.audio_top_p = p->audio_top_p; sc.audio_top_k = p->audio_top_k;
   sc.penalty = p->audio_repetition_penalty; sc.seed = p->seed;
+  // audio_top_k = None / <= 0 (no top-k filter, inference_utils.py:135): the pad code of every audio head is -inf
+  // (modeling_moss_tts.py:295-300, 486-487), so keeping the audio_head_size - 1 real codes IS "no filter"
+  if (sc.audio_do_sample && sc.audio_top_k <= 0 && c.audio_head_size - 1 <= kMaxTopK) sc.audio_top_k = c.audio_head_size - 1;
   if ((sc.text_do_sample && (sc.text_top_k <= 0 || sc.text_top_k > kMaxTopK)) ||
       (sc.audio_do_sample && (sc.audio_top_k <= 0 || sc.audio_top_k > kMaxTopK)))
     return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d", kMaxTopK);

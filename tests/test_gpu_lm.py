@@ -138,6 +138,27 @@ def test_generate_sampling_mode_follows_oracle():
     assert rows >= 4
 
 
+def test_generate_sampling_without_audio_top_k_follows_oracle():
+    """audio_top_k=None (the reference skips apply_top_k): every real code stays a candidate, top-p still applies."""
+    cfg = LMConfig.tiny(n_vq=4)
+    w = make_lm_weights(cfg, seed=5, never_stop=True)
+    model = MossTTSDelayModel(cfg, w, device=DEV)
+    oracle = OracleLM(cfg, w, torch.bfloat16)
+    ids, mask = make_prompt(cfg, 2, 12, seed=5)
+    kw = dict(max_new_tokens=10, text_temperature=0, audio_temperature=1.2, audio_top_k=None, audio_top_p=0.9, seed=7)
+    out = model.generate(ids, mask, **kw)
+    o_out = oracle.generate(ids, mask, **kw)
+    rows = sum(int((a[1].cpu()[: b[1].shape[0]] == b[1][: a[1].shape[0]]).all(dim=1).sum()) for a, b in zip(out, o_out))
+    total = sum(b[1].shape[0] for b in o_out)
+    print(f"[sampling, no audio top-k] identical rows {rows}/{total}")
+    assert rows >= total // 2
+    for (sl, g_), (osl, og) in zip(out, o_out):
+        assert sl == osl and torch.equal(g_.cpu()[0], og[0])
+        assert int(g_[:, 1:].max()) <= 1024 and int(g_[:, 1:].min()) >= 0
+    with pytest.raises(NotImplementedError):
+        model.generate(ids, mask, max_new_tokens=4, text_temperature=1.0, text_top_k=None)     # full-vocabulary sort: not built
+
+
 def test_forward_rejects_bad_shape():
     cfg = LMConfig.tiny(n_vq=4)
     model = MossTTSDelayModel(cfg, make_lm_weights(cfg, seed=1), device=DEV)
