@@ -472,7 +472,7 @@ int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, cons
 // standalone sample_token (inference_utils.py:111-145) on [N,V] bf16 logits
 // ---------------------------------------------------------------------------------------------
 template <bool W>
-__global__ void __launch_bounds__(kSampThreads, 3)
+__global__ void __launch_bounds__(kSampThreads, W ? 4 : 3)
 sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int N, int V, float temperature,
                      const uint32_t* __restrict__ bitmap, float penalty, float top_p, int top_k, int do_sample,
                      const float* __restrict__ uniforms, int64_t* __restrict__ out) {
