@@ -173,6 +173,24 @@ int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_
                    float* step_ms /* optional [max_new_tokens] host array of per-step device ms, or NULL */,
                    mt_stream s);
 
+/* Sliced form of generate() for streaming synthesis (LM decode overlapped with chunked codec
+ * decode, the structure of moss_tts_realtime's streaming session, streaming_mossttsrealtime.py:301-357 + :682-799,
+ * applied to MossTTSDelay).  mt_lm_stream_begin = everything mt_lm_generate does up to and including time_step 0
+ * (prefill + first sample); mt_lm_stream_steps enqueues up to n further decode steps (CUDA-graph replays when
+ * use_cuda_graph) and returns WITHOUT synchronising; rows [0, S0 + steps) of gen_ids are final once the work enqueued
+ * so far has run.  status_dev (optional, device int32[2]) receives {time steps executed, all rows stopped} as of the
+ * end of this slice; *launched (optional, host) = steps enqueued so far including time_step 0.  Steps enqueued after
+ * every row has stopped change nothing.  The token sequence is the one mt_lm_generate produces for the same params. */
+int mt_lm_stream_begin(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
+                       const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, mt_stream s);
+int mt_lm_stream_steps(mt_lm* h, int n, int* status_dev, int* launched, mt_stream s);
+int mt_lm_stream_end(mt_lm* h);
+/* De-delay (processing_moss_tts.py:528-537) of selected frames straight out of gen_ids [B, max_len, C]:
+ * rows [B, T] int32 (device) = generated-row index of the gen-slot row opening each frame (-1 = none -> code 0);
+ * out [C-1, B, T] int64 = gen_ids[b, S0 + rows[b,f] + q, 1 + q], the layout mt_codec_stream_push takes. */
+int mt_stream_gather_frames(const int64_t* gen_ids, int B, int max_len, int C, int S0, const int* rows, int T,
+                            int64_t* out, mt_stream s);
+
 /* inference_utils.sample_token (:111-145) on bf16 logits [N,V] (row stride ld elements).
  * prev_bitmap: optional device bitmap (ceil(V/32) uint32) of ids the repetition penalty applies to
  * (the union the reference builds with torch.unique, :78-86).  uniforms [N] float in [0,1) drive the
@@ -358,6 +376,11 @@ int mt_codec_stream_begin(mt_codec* h, int B, void* cache, long long cache_bytes
 int mt_codec_stream_push(mt_codec_stream* st, const int64_t* codes /* [nq, B, T] */, int nq, int T, float* wav,
                          void* workspace, long long workspace_bytes, mt_stream s);
 int mt_codec_stream_end(mt_codec_stream* st);
+
+/* AudioStreamDecoder._apply_crossfade (moss_tts_realtime/mossttsrealtime/streaming_mossttsrealtime.py:776-799):
+ * out[i] = prev_tail[i] * fade_out[i] + wav[i] * (1 - fade_out[i]), fade_out = linspace(1, 0, overlap) in fp32
+ * (torch's two-sided formula).  All pointers device fp32 [overlap]; out may alias wav. */
+int mt_crossfade(const float* prev_tail, const float* wav, int overlap, float* out, mt_stream s);
 
 /* ------------------------------------------------------------------------------------------
  * Prompt side of MossTTSDelayProcessor (moss_tts_delay/processing_moss_tts.py)

@@ -254,6 +254,7 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
 extern "C" int mt_lm_destroy(mt_lm* h) {
   if (!h) return MT_OK;
   if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
+  if (h->sess.exec) cudaGraphExecDestroy(h->sess.exec);
   if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
   delete h;
   return MT_OK;
@@ -277,17 +278,8 @@ static TokenIds token_ids(const mt_lm_config& c) {
   return t;
 }
 
-extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
-                              const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, int* n_steps,
-                              float* step_ms, mt_stream stream) {
-  MT_CHECK(h && input_ids && p && gen_ids && start_indices && n_steps, "mt_lm_generate: null argument");
-  const mt_lm_config& c = h->cfg;
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  const int max_len = S0 + p->max_new_tokens;
-  MT_CHECK(B > 0 && B <= c.max_batch, "generate: batch %d exceeds max_batch %d", B, c.max_batch);
-  MT_CHECK(S0 > 0 && p->max_new_tokens >= 0 && max_len <= c.max_seq, "generate: %d positions exceed max_seq %d", max_len, c.max_seq);
-  MT_CHECK(B * S0 <= c.max_tokens, "generate: prompt of %d tokens exceeds max_tokens %d", B * S0, c.max_tokens);
-  SampleCfg sc;
+// mt_gen_params -> SampleCfg (shared by mt_lm_generate and the sliced mt_lm_stream_* form)
+static int make_sample_cfg(const mt_lm_config& c, const mt_gen_params* p, SampleCfg& sc) {
   sc.text_do_sample = p->text_temperature > 0.f; sc.audio_do_sample = p->audio_temperature > 0.f;
   sc.text_temperature = sc.text_do_sample ? p->text_temperature : 1.f;
   sc.audio_temperature = sc.audio_do_sample ? p->audio_temperature : 1.f;
@@ -300,6 +292,21 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   if ((sc.text_do_sample && (sc.text_top_k <= 0 || sc.text_top_k > kMaxTopK)) ||
       (sc.audio_do_sample && (sc.audio_top_k <= 0 || sc.audio_top_k > kMaxTopK)))
     return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d", kMaxTopK);
+  return MT_OK;
+}
+
+extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
+                              const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, int* n_steps,
+                              float* step_ms, mt_stream stream) {
+  MT_CHECK(h && input_ids && p && gen_ids && start_indices && n_steps, "mt_lm_generate: null argument");
+  const mt_lm_config& c = h->cfg;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int max_len = S0 + p->max_new_tokens;
+  MT_CHECK(B > 0 && B <= c.max_batch, "generate: batch %d exceeds max_batch %d", B, c.max_batch);
+  MT_CHECK(S0 > 0 && p->max_new_tokens >= 0 && max_len <= c.max_seq, "generate: %d positions exceed max_seq %d", max_len, c.max_seq);
+  MT_CHECK(B * S0 <= c.max_tokens, "generate: prompt of %d tokens exceeds max_tokens %d", B * S0, c.max_tokens);
+  SampleCfg sc;
+  MT_TRY(make_sample_cfg(c, p, sc));
   *n_steps = 0;
   if (p->max_new_tokens == 0) {
     MT_CUDA(cudaMemcpyAsync(gen_ids, input_ids, sizeof(int64_t) * B * S0 * (1 + c.n_vq), cudaMemcpyDeviceToDevice, s));
@@ -394,4 +401,80 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   for (auto& e : poll_ev) if (e) cudaEventDestroy(e);
   cudaFreeHost(done_host);
   return status;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Sliced form of generate(): the same prefill / decode-step / sampler sequence as mt_lm_generate, enqueued by the
+// caller a few steps at a time and never synchronised here, so that a second stream can de-delay and decode the
+// frames that are already final (codec streaming, mt_codec_stream_push) while later steps run.
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int mt_lm_stream_begin(mt_lm* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
+                                  const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, mt_stream stream) {
+  MT_CHECK(h && input_ids && p && gen_ids && start_indices, "mt_lm_stream_begin: null argument");
+  MT_CHECK(!h->sess.active, "mt_lm_stream_begin: a sliced generation is already open on this handle");
+  const mt_lm_config& c = h->cfg;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  const int max_len = S0 + p->max_new_tokens;
+  MT_CHECK(B > 0 && B <= c.max_batch, "generate: batch %d exceeds max_batch %d", B, c.max_batch);
+  MT_CHECK(S0 > 0 && p->max_new_tokens >= 1 && max_len <= c.max_seq, "generate: %d positions exceed max_seq %d", max_len, c.max_seq);
+  MT_CHECK(B * S0 <= c.max_tokens, "generate: prompt of %d tokens exceeds max_tokens %d", B * S0, c.max_tokens);
+  mt_lm::Session& ss = h->sess;
+  MT_TRY(make_sample_cfg(c, p, ss.sc));
+  ss.tk = token_ids(c);
+  ss.st = gen_state_carve(h->gen_state_buf, B, 1 + c.n_vq, max_len, c.audio_head_size, gen_ids);
+  ss.B = B; ss.S0 = S0; ss.max_len = max_len; ss.max_new = p->max_new_tokens; ss.use_graph = p->use_cuda_graph;
+  MT_TRY(gen_init(ss.st, input_ids, attention_mask, S0, ss.tk, start_indices, s));
+  MT_TRY(lm_forward_impl(h, input_ids, ss.st.mask, max_len, B, S0, 0, nullptr, S0, 1, h->text_logits, h->audio_logits, s));
+  MT_TRY(gen_sample_step(ss.st, h->text_logits, c.vocab_size, h->audio_logits, c.audio_head_size, ss.sc, ss.tk, s));
+  ss.launched = 1;
+  ss.active = true;
+  return MT_OK;
+}
+
+extern "C" int mt_lm_stream_steps(mt_lm* h, int n, int* status_dev, int* launched, mt_stream stream) {
+  MT_CHECK(h && h->sess.active, "mt_lm_stream_steps: no open sliced generation");
+  mt_lm::Session& ss = h->sess;
+  const mt_lm_config& c = h->cfg;
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  auto decode_step = [&](cudaStream_t cs) -> int {
+    MT_TRY(lm_forward_impl(h, ss.st.next_ids, ss.st.mask, ss.max_len, ss.B, 1, 0, ss.st.pos, ss.max_len, 1, h->text_logits,
+                           h->audio_logits, cs, ss.st.text_full));
+    return gen_sample_step(ss.st, h->text_logits, c.vocab_size, h->audio_logits, c.audio_head_size, ss.sc, ss.tk, cs);
+  };
+  for (int i = 0; i < n && ss.launched < ss.max_new; ++i) {
+    if (ss.use_graph && ss.launched >= 2) {
+      if (!ss.exec) {
+        cudaGraph_t graph = nullptr;
+        if (!h->cap_stream) MT_CUDA(cudaStreamCreateWithFlags(&h->cap_stream, cudaStreamNonBlocking));
+        MT_CUDA(cudaStreamBeginCapture(h->cap_stream, cudaStreamCaptureModeThreadLocal));
+        const long long before = g_launches;
+        int status = decode_step(h->cap_stream);
+        cudaError_t ce = cudaStreamEndCapture(h->cap_stream, &graph);
+        if (status == MT_OK && ce != cudaSuccess) status = fail(MT_ERR_CUDA, "end capture: %s", cudaGetErrorString(ce));
+        if (status == MT_OK && cudaGraphInstantiate(&ss.exec, graph, 0) != cudaSuccess) status = fail(MT_ERR_CUDA, "graph instantiate failed");
+        if (graph) cudaGraphDestroy(graph);
+        ss.graph_launches = g_launches - before;
+        g_launches = before;
+        MT_TRY(status);
+      }
+      MT_CUDA(cudaGraphLaunch(ss.exec, s));
+      g_launches += ss.graph_launches;
+    } else {
+      MT_TRY(decode_step(s));
+    }
+    ++ss.launched;
+  }
+  if (status_dev) {
+    MT_CUDA(cudaMemcpyAsync(status_dev, ss.st.step, sizeof(int), cudaMemcpyDeviceToDevice, s));
+    MT_CUDA(cudaMemcpyAsync(status_dev + 1, ss.st.done, sizeof(int), cudaMemcpyDeviceToDevice, s));
+  }
+  if (launched) *launched = ss.launched;
+  return MT_OK;
+}
+
+extern "C" int mt_lm_stream_end(mt_lm* h) {
+  MT_CHECK(h, "mt_lm_stream_end: null handle");
+  if (h->sess.exec) { cudaGraphExecDestroy(h->sess.exec); h->sess.exec = nullptr; }
+  h->sess.active = false;
+  return MT_OK;
 }

@@ -22,6 +22,14 @@ struct mt_lm {
   cudaGraphExec_t graph_exec = nullptr;
   cudaStream_t cap_stream = nullptr;   // capture-only stream (the caller's stream may be the legacy default stream)
   int graph_B = 0; long long graph_key = 0;
+  // sliced generation (mt_lm_stream_*): the loop state of one generate() call kept between calls
+  struct Session {
+    bool active = false;
+    mt::SampleCfg sc; mt::TokenIds tk; mt::GenState st;
+    int B = 0, S0 = 0, max_len = 0, max_new = 0, launched = 0, use_graph = 0;
+    cudaGraphExec_t exec = nullptr;
+    long long graph_launches = 0;
+  } sess;
 };
 
 namespace mt {

@@ -112,9 +112,63 @@ int pad_left(const int64_t* const* rows, const int* lens, int B, int Lmax, int C
   return MT_OK;
 }
 
+// AudioStreamDecoder._apply_crossfade (streaming_mossttsrealtime.py:776-799): linear fade between the previous chunk's
+// tail and the head of the new chunk; fade_out = torch.linspace(1, 0, n) (start + i*step below the middle, end - (n-1-i)*step
+// above it, fp32).
+__global__ void crossfade_kernel(const float* __restrict__ prev_tail, const float* __restrict__ wav, int n,
+                                 float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
+  const float step = n > 1 ? (0.f - 1.f) / static_cast<float>(n - 1) : 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const float fo = n == 1 ? 1.f : (i < n / 2 ? 1.f + step * static_cast<float>(i) : 0.f - step * static_cast<float>(n - 1 - i));
+    out[i] = prev_tail[i] * fo + wav[i] * (1.f - fo);
+  }
+}
+
+// Streaming synthesis: collect the frames whose n_vq codes are final out of the delayed rows of gen_ids.
+// rows[b, f] = generated-row index (0 = first generated row) of the gen-slot row that opens frame f of row b, or -1;
+// out[q, b, f] = gen_ids[b, S0 + rows[b, f] + q, 1 + q]  (the de-delay rule, processing_moss_tts.py:528-537), 0 for -1.
+__global__ void gather_frames_kernel(const int64_t* __restrict__ gen, int B, int max_len, int C, int S0,
+                                     const int* __restrict__ rows, int T, int64_t* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
+  const int nq = C - 1;
+  const long long total = static_cast<long long>(nq) * B * T;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int f = static_cast<int>(i % T), b = static_cast<int>((i / T) % B), q = static_cast<int>(i / (static_cast<long long>(T) * B));
+    const int r = rows[b * T + f];
+    int64_t v = 0;
+    if (r >= 0 && S0 + r + q < max_len) v = gen[(static_cast<long long>(b) * max_len + S0 + r + q) * C + 1 + q];
+    out[i] = v;
+  }
+}
+
 }  // namespace mt
 
 using namespace mt;
+
+extern "C" int mt_crossfade(const float* prev_tail, const float* wav, int overlap, float* out, mt_stream s) {
+  MT_CHECK(overlap >= 0 && (overlap == 0 || (prev_tail && wav && out)), "mt_crossfade: null argument");
+  if (overlap == 0) return MT_OK;
+  const int blocks = overlap / 256 + 1 < 4 * kNumSMs ? overlap / 256 + 1 : 4 * kNumSMs;
+  MT_CUDA(launch(crossfade_kernel, dim3(blocks), dim3(256), 0, reinterpret_cast<cudaStream_t>(s), prev_tail, wav, overlap, out));
+  count_launch();
+  return MT_OK;
+}
+extern "C" int mt_stream_gather_frames(const int64_t* gen_ids, int B, int max_len, int C, int S0, const int* rows, int T,
+                                       int64_t* out, mt_stream s) {
+  MT_CHECK(B >= 0 && T >= 0 && C >= 2 && S0 >= 0 && max_len >= S0, "mt_stream_gather_frames: bad sizes");
+  if (B * T == 0) return MT_OK;
+  MT_CHECK(gen_ids && rows && out, "mt_stream_gather_frames: null argument");
+  const long long total = static_cast<long long>(C - 1) * B * T;
+  const int blocks = static_cast<int>(total / 256 + 1 < 4 * kNumSMs ? total / 256 + 1 : 4 * kNumSMs);
+  MT_CUDA(launch(gather_frames_kernel, dim3(blocks), dim3(256), 0, reinterpret_cast<cudaStream_t>(s), gen_ids, B, max_len, C,
+                 S0, rows, T, out));
+  count_launch();
+  return MT_OK;
+}
 
 extern "C" int mt_loudness_normalize(float* wav, long long ld, const int64_t* lengths, int B, float target_dbfs,
                                      float gain_lo, float gain_hi, mt_stream s) {

@@ -1,0 +1,144 @@
+"""Streaming synthesis: mt_lm_stream_* + mt_stream_gather_frames + mt_codec_stream_push behind
+moss_tts_b200.streaming.generate_stream, and the reference-shaped AudioStreamDecoder (mt_crossfade).  Parity:
+* the reference AudioStreamDecoder's own chunks (tests/golden/stream_decoder_mini.npz, reference-executed),
+* generate_stream ids == generate ids (bit-exact, same seed), streamed audio == the codec's streaming decode of the
+  finished, de-delayed codes with the same pushes (bit-exact) and the oracle's closed form (SNR)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from moss_tts_b200 import _lib as L
+from moss_tts_b200.config import CodecConfig, LMConfig
+from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+from moss_tts_b200.modeling_moss_tts import MossTTSDelayModel
+from moss_tts_b200.streaming import AudioStreamDecoder, generate_stream
+from oracle.codec import OracleCodec, apply_de_delay_pattern
+from oracle.weights import make_codec_weights, make_lm_weights, make_prompt
+from gpu_util import DEV, snr_db
+
+pytestmark = pytest.mark.gpu
+SNR_DB = 40.0
+
+
+@pytest.fixture(scope="module")
+def codec():
+    cfg = CodecConfig.mini()
+    w = make_codec_weights(cfg, seed=11)
+    return cfg, MossAudioTokenizerModel(cfg, w, device=DEV), OracleCodec(cfg, w)
+
+
+def test_crossfade_kernel_known_answer():
+    g = np.load(os.path.join(GOLDEN, "stream_decoder_mini.npz"), allow_pickle=False)
+    pt, hd = torch.from_numpy(g["xf_prev"]).to(DEV), torch.from_numpy(g["xf_head"]).to(DEV)
+    out = torch.empty_like(pt)
+    L.check(L.lib().mt_crossfade(L.ptr(pt), L.ptr(hd), pt.numel(), L.ptr(out), L.stream_ptr(DEV)), "mt_crossfade")
+    np.testing.assert_allclose(out.cpu().numpy(), g["xf_out"], rtol=0, atol=1e-6)
+    one = torch.empty(1, device=DEV)
+    L.check(L.lib().mt_crossfade(L.ptr(pt), L.ptr(hd), 1, L.ptr(one), L.stream_ptr(DEV)), "mt_crossfade")
+    assert one.item() == pt[0].item()                      # linspace(1, 0, 1) == [1]
+
+
+def test_audio_stream_decoder_matches_reference_chunks(codec):
+    g = np.load(os.path.join(GOLDEN, "stream_decoder_mini.npz"), allow_pickle=False)
+    cfg, model, _ = codec
+    dec = AudioStreamDecoder(model, chunk_frames=int(g["chunk_frames"]), overlap_frames=int(g["overlap_frames"]))
+    chunks, after, pos = [], [], 0
+    for n in g["pushes"]:
+        dec.push_tokens(g["tokens"][pos: pos + int(n)])
+        pos += int(n)
+        chunks += list(dec.audio_chunks())
+        after.append(len(chunks))
+    last = dec.flush()
+    if last is not None:
+        chunks.append(last)
+    assert after == g["chunks_after_push"].tolist() and len(chunks) == int(g["n_chunks"])
+    for i, ch in enumerate(chunks):
+        ref = torch.from_numpy(g[f"chunk{i}"])
+        assert tuple(ch.shape) == tuple(ref.shape)
+        s = snr_db(ref, ch.cpu())
+        print(f"[AudioStreamDecoder chunk {i}] SNR vs the reference's chunk {s:.1f} dB")
+        assert s >= SNR_DB
+    assert dec.flush() is None
+    with pytest.raises(ValueError):
+        dec.push_tokens(torch.zeros(3, dtype=torch.long))
+
+
+def _stream_case(codec, never_stop, B, steps, chunk_frames, sample, left_pad=None, lm_slice=None, text_greedy=False):
+    ccfg, cmodel, oracle = codec
+    cfg = LMConfig.tiny(n_vq=ccfg.num_quantizers)
+    w = make_lm_weights(cfg, seed=5, never_stop=never_stop)
+    lm = MossTTSDelayModel(cfg, w, device=DEV)
+    ids, mask = make_prompt(cfg, B, 12, seed=3, left_pad=left_pad)
+    kw = dict(max_new_tokens=steps, audio_repetition_penalty=1.1 if sample else 1.0, seed=7)
+    if not sample:
+        kw.update(text_temperature=0, audio_temperature=0)
+    elif text_greedy:
+        kw.update(text_temperature=0)                       # sampled audio codes under a never-stopping text channel
+    ref = lm.generate(ids, mask, **kw)
+    chunks = list(generate_stream(lm, cmodel, ids, mask, chunk_frames=chunk_frames, lm_slice=lm_slice, **kw))
+    out = lm.last_stream_output
+    for (a, x), (b_, y) in zip(ref, out):                   # the sliced loop is the same loop
+        assert a == b_ and torch.equal(x, y)
+    # frames of every row from the finished ids: gen-slot rows open a frame, its n_vq codes sit on the delay diagonal
+    nq, ds = cfg.n_vq, cmodel.downsample_rate
+    frames = []
+    for sl, x in out:
+        x = x.cpu().numpy()
+        gen = x[sl:]
+        rows = np.nonzero(gen[:, 0] == cfg.audio_assistant_gen_slot_token_id)[0]
+        rows = rows[rows + nq - 1 < gen.shape[0]]
+        frames.append(np.stack([gen[rows + q, 1 + q] for q in range(nq)], 1) if len(rows) else np.zeros((0, nq), np.int64))
+        if len(rows) and (np.diff(rows) == 1).all():        # one contiguous span: the processor's de-delay agrees
+            dd = apply_de_delay_pattern(gen[rows[0]: rows[-1] + nq, 1:])
+            np.testing.assert_array_equal(dd, frames[-1])
+    pushes = [w_.shape[1] // ds for w_, _ in chunks]
+    total = [sum(v[b] for _, v in chunks) // ds for b in range(B)]
+    assert total == [len(f) for f in frames]
+    if not pushes:
+        return chunks, frames
+    Tmax = sum(pushes)
+    codes = torch.zeros(nq, B, Tmax, dtype=torch.int64)
+    for b in range(B):
+        codes[:, b, :len(frames[b])] = torch.from_numpy(frames[b].T)
+    outs, pos = [], 0
+    with cmodel.streaming(batch_size=B):
+        for n in pushes:
+            outs.append(cmodel._decode_frame(codes[:, :, pos: pos + n].to(DEV)).audio[:, 0])
+            pos += n
+    direct = torch.cat(outs, -1)
+    streamed = torch.cat([w_ for w_, _ in chunks], -1)
+    orc = oracle.decode_frames(codes, chunk_frames=pushes)[:, 0]
+    for b in range(B):
+        n = len(frames[b]) * ds
+        assert torch.equal(streamed[b, :n], direct[b, :n])
+        if n:
+            assert snr_db(orc[b, :n], streamed[b, :n].cpu()) >= SNR_DB
+    # valid_samples are prefixes that only shrink once a row has finished
+    for b in range(B):
+        v = [val[b] for _, val in chunks]
+        full = [w_.shape[1] for w_, _ in chunks]
+        short = [i for i in range(len(v)) if v[i] < full[i]]
+        assert all(v[i] == 0 for i in range(short[0] + 1, len(v))) if short else True
+    return chunks, frames
+
+
+@pytest.mark.parametrize("sample", [False, True])
+def test_generate_stream_never_stop(codec, sample):
+    chunks, frames = _stream_case(codec, True, 3, 45, 4, sample, left_pad=[0, 2, 5], text_greedy=True)
+    assert len(chunks) >= 5 and all(len(f) in (37, 38) for f in frames)
+    assert all(w.shape[1] // 1920 >= 4 for w, _ in chunks[:-1])
+
+
+def test_generate_stream_slices_and_single_row(codec):
+    _stream_case(codec, True, 1, 30, 3, False, lm_slice=5)
+    _stream_case(codec, True, 2, 9, 4, False)               # too short for one complete frame... or exactly one
+    _stream_case(codec, True, 2, 1, 4, False)               # max_new_tokens = 1: time_step 0 only
+
+
+def test_generate_stream_rows_that_stop(codec):
+    chunks, frames = _stream_case(codec, False, 4, 60, 2, True, left_pad=[0, 1, 0, 3])
+    print("[generate_stream, stopping rows] frames per row", [len(f) for f in frames], "chunks", len(chunks))
