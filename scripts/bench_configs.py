@@ -3,6 +3,8 @@
   C4  MossTTSLocal (assumed 1.7B shape)      B = 128, 96-token prompt, 125 frames, n_vq_for_inference = 32
   C5  MossTTSDelay n_vq = 16 long context    B = 4, ~512-token prompt, 3765 steps (>= 5 min of audio)
   stream  incremental streaming decode: per-push latency (SURVEY §8f rank 3 building block)
+  synth  streaming synthesis: generate_stream at the 8B / released-codec shapes, time to first audio
+         and total time vs generate + one-shot decode
   enc codec ENCODE sweep B in {1,16,64} x {1,10,30} s of 24 kHz audio -> 32 codebooks
 One JSON line per measurement; device-timed with CUDA events after a warm-up call.
 
@@ -88,6 +90,46 @@ def stream(args, dev):
                           "realtime_factor": B * n * 80 / tail[len(tail) // 2]}), flush=True)
 
 
+def synth(args, dev):
+    """Streaming synthesis at the headline shapes: B rows x 10 s, chunks of `cf` frames.  Wall-clock (host) timing:
+    time to first audio is a host-visible latency, the chunk is on the device and synchronised when it is yielded."""
+    import time
+    import bench
+    from moss_tts_b200.config import CodecConfig, LMConfig
+    from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
+    from moss_tts_b200.modeling_moss_tts import MossTTSDelayModel
+    from moss_tts_b200.streaming import generate_stream
+    cfg = LMConfig.delay_8b()
+    lm = MossTTSDelayModel.random_init(cfg, device=dev, seed=1234, never_stop=True)
+    ccfg = CodecConfig.released()
+    codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=8 << 30)
+    steps = 60 if args.quick else 156
+    for B, cf in ((1, 4), (1, 8), (8, 8), (64, 8), (64, 25)):
+        ids, mask = bench.make_prompts(cfg, B, seed=0)
+        kw = dict(max_new_tokens=steps, text_temperature=0, audio_temperature=0)
+        for rep in range(2):                                   # rep 0 warms graphs / lazy attributes
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            first, n_chunks, frames = None, 0, 0
+            for wav, valid in generate_stream(lm, codec, ids, mask, chunk_frames=cf, **kw):
+                if first is None:
+                    first = time.perf_counter() - t0
+                n_chunks += 1
+                frames += wav.shape[1] // codec.downsample_rate
+            torch.cuda.synchronize()
+            total = time.perf_counter() - t0
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = lm.generate(ids, mask, **kw)
+        torch.cuda.synchronize()
+        t_gen = time.perf_counter() - t0
+        print(json.dumps({"config": "streaming synthesis (8B shape + released codec, greedy)", "B": B, "chunk_frames": cf,
+                          "steps": steps, "chunks": n_chunks, "frames_per_row": frames,
+                          "first_audio_ms": None if first is None else first * 1e3, "total_ms": total * 1e3,
+                          "generate_only_ms": t_gen * 1e3,
+                          "audio_s_per_s": B * frames / 12.5 / total}), flush=True)
+
+
 def c4(args, dev):
     from moss_tts_b200.config import LocalConfig
     from moss_tts_b200.modeling_moss_tts_local import MossTTSLocalModel
@@ -146,7 +188,7 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     for w in args.what.split(","):
-        {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream}[w](args, dev)
+        {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream, "synth": synth}[w](args, dev)
         torch.cuda.empty_cache()
 
 
