@@ -44,3 +44,43 @@ def test_stream_decoder_matches_reference_chunks():
         assert ch.shape == ref.shape
         np.testing.assert_allclose(ch, ref, rtol=0, atol=2e-5 * max(1.0, float(np.abs(ref).max())))
     assert dec.flush() is None
+
+
+class _FakeCodec:
+    """codec.decode stand-in for the host-logic test: one sample per frame = the frame's first code."""
+    device = None
+
+    def __init__(self):
+        self.calls = []
+
+    def decode(self, tokens_t, chunk_duration=None, **kw):
+        self.calls.append((tuple(tokens_t.shape), chunk_duration, kw))
+        return {"audio": [tokens_t[0].float()[None, :]]}
+
+
+def test_product_stream_decoder_host_logic_on_cpu():
+    """Buffering / chunking / decode_kwargs handling of the product AudioStreamDecoder (no crossfade -> no kernel):
+    same consumption order and chunk boundaries as the oracle's restatement; the crossfade path refuses CPU tensors."""
+    import pytest
+    from moss_tts_b200 import _lib as L
+    from moss_tts_b200.streaming import AudioStreamDecoder
+    rng = np.random.default_rng(0)
+    tokens = rng.integers(0, 1024, size=(23, 4))
+    fake = _FakeCodec()
+    dec = AudioStreamDecoder(fake, chunk_frames=5, overlap_frames=0, decode_kwargs={"chunk_duration": -1, "num_quantizers": 4})
+    got, pos = [], 0
+    for n in (2, 9, 1, 11):
+        dec.push_tokens(tokens[pos: pos + n])
+        pos += n
+        got += [w.numpy() for w in dec.audio_chunks()]
+    got.append(dec.flush().numpy())
+    assert [g.shape[0] for g in got] == [5, 5, 5, 5, 3]
+    np.testing.assert_array_equal(np.concatenate(got), tokens[:, 0].astype(np.float32))
+    assert all(c[1] is None and c[2] == {"num_quantizers": 4} for c in fake.calls)      # chunk_duration <= 0 -> chunking off
+    assert dec.flush() is None
+    dec2 = AudioStreamDecoder(_FakeCodec(), chunk_frames=4, overlap_frames=2)
+    dec2.push_tokens(tokens[:8])
+    it = dec2.audio_chunks()
+    assert next(it).shape[0] == 4                      # first chunk: nothing to fade against
+    with pytest.raises(L.MossTTSNativeError):
+        next(it)                                       # CPU waveforms: there is no CPU crossfade
