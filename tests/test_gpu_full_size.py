@@ -108,3 +108,33 @@ def test_released_codec_encode_shapes_and_determinism(codec_full):
     dec = codec.decode(enc.audio_codes, padding_mask=torch.arange(Tf, device=DEV)[None, :] < enc.audio_codes_lengths[:, None])
     assert tuple(dec.audio.shape) == (3, 1, Tf * 1920)
     assert dec.audio_lengths.tolist() == [n * 1920 for n in enc.audio_codes_lengths.tolist()]
+
+
+def test_8b_streaming_synthesis_equals_generate_plus_streaming_decode(lm8b, codec_full):
+    """BASELINE shapes (8B LM, released codec): the sliced loop reproduces generate()'s ids bit-for-bit and the chunks it
+    yields are the codec's streaming decode of the frames those ids carry (same pushes -> bit-exact)."""
+    from moss_tts_b200.streaming import generate_stream
+    cfg, model, ids, mask = lm8b
+    ccfg, codec = codec_full
+    B, steps, cf = 8, 72, 8
+    kw = dict(max_new_tokens=steps, text_temperature=0, audio_temperature=0)
+    ref = model.generate(ids[:B], mask[:B], **kw)
+    chunks = list(generate_stream(model, codec, ids[:B], mask[:B], chunk_frames=cf, **kw))
+    for (a, x), (b, y) in zip(ref, model.last_stream_output):
+        assert a == b and torch.equal(x, y)
+    nq, ds = cfg.n_vq, codec.downsample_rate
+    pushes = [w.shape[1] // ds for w, _ in chunks]
+    frames = steps - (nq - 1)                               # never-stop weights: every generated row opens a frame
+    assert sum(pushes) == frames and all(p >= cf for p in pushes[:-1]) and len(pushes) >= 4
+    assert all(v == [p * ds] * B for (_, v), p in zip(chunks, pushes))
+    codes = torch.stack([MossTTSDelayProcessor.apply_de_delay_pattern(g[sl:, 1:]).T for sl, g in ref], 1)   # [nq, B, T]
+    assert codes.shape[-1] == frames
+    outs, pos = [], 0
+    with codec.streaming(batch_size=B):
+        for n in pushes:
+            outs.append(codec._decode_frame(codes[:, :, pos: pos + n].contiguous()).audio[:, 0])
+            pos += n
+    assert torch.equal(torch.cat(outs, -1), torch.cat([w for w, _ in chunks], -1))
+    # and one un-chunked decode of the same codes agrees while everything is inside the 10 s context
+    full = codec.decode(codes).audio[:, 0]
+    assert snr_db(full.cpu(), torch.cat(outs, -1).cpu()) >= 45.0
