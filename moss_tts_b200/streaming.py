@@ -117,6 +117,32 @@ class AudioStreamDecoder:
         return merged
 
 
+def scan_text_tokens(new_tokens: np.ndarray, first_row: int, frame_rows: List[List[int]], finished: List[bool],
+                     gen_slot_id: int, im_end_id: int) -> None:
+    """Book-keeping of one consumed slice: `new_tokens` [B, n] are the text-channel tokens of generated rows
+    [first_row, first_row + n).  Every gen-slot row opens a frame (its n_vq codes sit on the delay diagonal below it,
+    processing_moss_tts.py:528-537); a row that has emitted <|im_end|> will produce no more frames."""
+    for b in range(new_tokens.shape[0]):
+        for j in np.nonzero(new_tokens[b] == gen_slot_id)[0]:
+            frame_rows[b].append(first_row + int(j))
+        if (new_tokens[b] == im_end_id).any():
+            finished[b] = True
+
+
+def plan_push(frame_rows: List[List[int]], finished: List[bool], scanned: int, pushed: int, n_vq: int, chunk_frames: int,
+              max_push: int) -> Optional[Tuple[int, List[int]]]:
+    """Next lockstep push, or None.  A frame opened at generated row r is complete once row r + n_vq - 1 exists
+    (`scanned` rows exist).  Unfinished rows must all have `chunk_frames` complete frames beyond the `pushed` already
+    sent; once every row has finished, whatever is left goes out.  Returns (T, frames of each row inside the push)."""
+    avail = [sum(1 for r in fr if r + n_vq - 1 < scanned) - pushed for fr in frame_rows]
+    live = [a for a, f in zip(avail, finished) if not f]
+    T = min(live) if live else max(avail + [0])
+    if T <= 0 or (live and T < chunk_frames):
+        return None
+    T = min(T, max_push)
+    return T, [max(0, min(a, T)) for a in avail]
+
+
 @torch.inference_mode()
 def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, *,
                     chunk_frames: int = 8, lm_slice: Optional[int] = None, max_new_tokens: int = 1000,
@@ -203,12 +229,8 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                     if steps_exec > scanned:
                         text_host[:, scanned:steps_exec].copy_(gen[:, S0 + scanned:S0 + steps_exec, 0], non_blocking=True)
                         side.synchronize()
-                        new = text_host[:, scanned:steps_exec].numpy()
-                        for b in range(B):
-                            for j in np.nonzero(new[b] == c.audio_assistant_gen_slot_token_id)[0]:
-                                frame_rows[b].append(scanned + int(j))
-                            if (new[b] == c.im_end_token_id).any():
-                                finished[b] = True
+                        scan_text_tokens(text_host[:, scanned:steps_exec].numpy(), scanned, frame_rows, finished,
+                                         c.audio_assistant_gen_slot_token_id, c.im_end_token_id)
                         scanned = steps_exec
                     if done:
                         all_done = True
@@ -217,17 +239,13 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                     if last:
                         finished = [True] * B
                     while True:
-                        avail = [sum(1 for r in frame_rows[b] if r + nvq - 1 < scanned) - pushed for b in range(B)]
-                        live = [avail[b] for b in range(B) if not finished[b]]
-                        T = min(live) if live else max(avail + [0])
-                        if T <= 0 or (live and T < chunk_frames):
+                        plan = plan_push(frame_rows, finished, scanned, pushed, nvq, chunk_frames, max_push)
+                        if plan is None:
                             break
-                        T = min(T, max_push)
+                        T, counts = plan
                         rows = torch.full((B, T), -1, dtype=torch.int32)
-                        valid = []
-                        for b in range(B):
-                            n = max(0, min(avail[b], T))
-                            valid.append(n * codec.downsample_rate)
+                        valid = [n * codec.downsample_rate for n in counts]
+                        for b, n in enumerate(counts):
                             if n:
                                 rows[b, :n] = torch.tensor(frame_rows[b][pushed:pushed + n], dtype=torch.int32)
                         rows_dev = rows.to(dev)

@@ -84,3 +84,53 @@ def test_product_stream_decoder_host_logic_on_cpu():
     assert next(it).shape[0] == 4                      # first chunk: nothing to fade against
     with pytest.raises(L.MossTTSNativeError):
         next(it)                                       # CPU waveforms: there is no CPU crossfade
+
+
+def test_stream_planner_against_the_oracle_dedelay():
+    """Host logic of generate_stream on CPU: feed the planner the text channel of a synthetic generation slice by slice;
+    the frames it schedules, read off the delay diagonal, must be the oracle's de-delay of every row's audio span, each
+    frame exactly once and only after its last code exists."""
+    from moss_tts_b200.streaming import plan_push, scan_text_tokens
+    from oracle.codec import apply_de_delay_pattern
+    rng = np.random.default_rng(3)
+    GEN, DELAY, END, IM_END, PAD, nq = 7, 8, 9, 10, 0, 4
+    B, steps = 3, 40
+    n_frames = [17, 5, 30]                       # row 2 is cut by max_new_tokens before its span ends
+    lead = [1, 3, 0]                             # text tokens before the first gen slot
+    gen = np.full((B, steps, 1 + nq), 1024, dtype=np.int64)
+    for b in range(B):
+        seq = [PAD + 1] * lead[b] + [GEN] * n_frames[b] + [DELAY] * (nq - 1) + [END, IM_END]
+        seq = (seq + [PAD] * steps)[:steps]
+        gen[b, :, 0] = seq
+        for f in range(n_frames[b]):
+            for q in range(nq):
+                if lead[b] + f + q < steps:
+                    gen[b, lead[b] + f + q, 1 + q] = rng.integers(0, 1024)
+    frame_rows, finished = [[] for _ in range(B)], [False] * B
+    scanned = pushed = 0
+    got = [[] for _ in range(B)]
+    pushes = []
+    for upto in [1, 6, 11, 19, 23, 31, 40]:      # uneven slices
+        scan_text_tokens(gen[:, scanned:upto, 0], scanned, frame_rows, finished, GEN, IM_END)
+        scanned = upto
+        if upto == steps:
+            finished = [True] * B
+        while True:
+            plan = plan_push(frame_rows, finished, scanned, pushed, nq, chunk_frames=3, max_push=6)
+            if plan is None:
+                break
+            T, counts = plan
+            assert 0 < T <= 6 and (all(finished) or T >= 3)
+            for b, n in enumerate(counts):
+                for r in frame_rows[b][pushed:pushed + n]:
+                    assert r + nq - 1 < scanned                      # every code of the frame exists
+                    got[b].append([gen[b, r + q, 1 + q] for q in range(nq)])
+            pushes.append(T)
+            pushed += T
+    for b in range(B):
+        span = gen[b, lead[b]:, 1:]
+        n_real = min(n_frames[b], steps - lead[b] - (nq - 1))        # frames whose last code was generated
+        ref = apply_de_delay_pattern(span[: n_real + nq - 1])
+        np.testing.assert_array_equal(np.asarray(got[b], dtype=np.int64).reshape(-1, nq), ref)
+    assert finished == [True, True, True] and sum(pushes) == max(len(g) for g in got)
+    assert plan_push(frame_rows, finished, scanned, pushed, nq, 3, 6) is None
