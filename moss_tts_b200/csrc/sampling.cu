@@ -7,6 +7,8 @@
 //   a8  find_last_equal_C                      inference_utils.py:148-165
 //   a9  (de-)delay pattern                     processing_moss_tts.py:516-537
 // Logits are bf16; every transform returns the value a bf16 PyTorch tensor would hold.
+#include <cstddef>
+
 #include "sampling.cuh"
 #include "sampling_select.cuh"
 
@@ -80,7 +82,8 @@ __device__ void find_bin(const int* hist, int need, int* out_bin, int* out_above
   *out_bin = 0; *out_above = acc - hist[0];
 }
 
-__device__ int row_sample(const RowXform& x, int top_k, float top_p, float u, SampSmem& sm) {
+// ebuf / result: scratch outside `sm` (SelSmem<BlockG>::ebuf lies behind the end of SampSmem in the union below)
+__device__ int row_sample(const RowXform& x, int top_k, float top_p, float u, SampSmem& sm, float* ebuf, int* result) {
   const int tid = threadIdx.x;
   const int k = top_k < x.V ? top_k : x.V;
   // pass 1: high byte
@@ -156,46 +159,16 @@ __device__ int row_sample(const RowXform& x, int top_k, float top_p, float u, Sa
       __syncthreads();
     }
   }
-  // sequential tail on one thread: softmax -> top-p cut -> softmax -> inverse-CDF draw
-  if (tid == 0) {
-    int n = 0;
-    while (n < k && sm.cand[n] != ~0ull) ++n;
-    int result = 0;
-    if (n > 0) {
-      const float mx = unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[0] >> 32));
-      int keep = n;
-      if (top_p < 1.0f) {
-        float sum = 0.f;
-        for (int j = 0; j < n; ++j) sum += expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx);
-        const float thr_p = rbf(top_p);
-        float run = 0.f;
-        keep = 0;
-        for (int j = 0; j < n; ++j) {
-          // entry j is removed when the rounded cumulative sum of entries < j exceeds top_p
-          if (j > 0 && rbf(run) > thr_p) break;
-          ++keep;
-          run += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum);
-        }
-      }
-      float sum2 = 0.f;
-      for (int j = 0; j < keep; ++j) sum2 += expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx);
-      float total = 0.f;
-      for (int j = 0; j < keep; ++j)
-        total += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum2);
-      const float target = u * total;
-      float run2 = 0.f;
-      result = static_cast<int>(sm.cand[keep - 1] & 0xFFFFFFFFu);
-      for (int j = 0; j < keep; ++j) {
-        run2 += rbf(expf(unkey16(0xFFFFu - static_cast<uint32_t>(sm.cand[j] >> 32)) - mx) / sum2);
-        if (run2 > target) { result = static_cast<int>(sm.cand[j] & 0xFFFFFFFFu); break; }
-      }
-    }
-    sm.misc[5] = result;
-  }
+  // softmax -> top-p cut -> softmax -> inverse-CDF draw on the sorted list: the same routine as the one-pass path
+  // (exponentials and divisions by all threads, the order-sensitive fp32 sums by one)
+  if (tid == 0) sm.misc[6] = 0;
   __syncthreads();
-  const int r = sm.misc[5];
+  for (int j = tid; j < k; j += blockDim.x)
+    if (sm.cand[j] != ~0ull && (j + 1 == k || sm.cand[j + 1] == ~0ull)) sm.misc[6] = j + 1;   // valid entries sort first
   __syncthreads();
-  return r;
+  const int n = sm.misc[6];
+  __syncthreads();
+  return draw_sorted<BlockG>(sm.cand, n, top_p, u, ebuf, result);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -207,6 +180,8 @@ struct BlockSmem {
     SampSmem old;
   };
 };
+static_assert(offsetof(SelSmem<BlockG>, ebuf) >= sizeof(SampSmem),
+              "row_sample's draw scratch (sel.ebuf, sel.result) must lie behind the multi-pass selection state");
 union SampleShared {
   BlockSmem blk;
   SelSmem<WarpG> warp[kSampThreads / 32];
@@ -242,7 +217,7 @@ __device__ int block_pick(const RowXform& x, bool do_sample, int top_k, float to
                             : (x.bitmap == nullptr ? select_topk<BlockG, true>(x, k, sm.sel) : select_topk<BlockG, false>(x, k, sm.sel));
   if (n < 0) {
     __syncthreads();
-    return do_sample ? row_sample(x, top_k, top_p, u, sm.old) : row_argmax(x, reinterpret_cast<uint32_t*>(sm.old.red));
+    return do_sample ? row_sample(x, top_k, top_p, u, sm.old, sm.sel.ebuf, &sm.sel.result) : row_argmax(x, reinterpret_cast<uint32_t*>(sm.old.red));
   }
   if (!do_sample) return n ? static_cast<int>(sm.sel.list[0] & 0xFFFFFFFFu) : 0;
   return draw_sorted<BlockG>(sm.sel.list, n, top_p, u, sm.sel.ebuf, &sm.sel.result);
