@@ -358,7 +358,11 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "audio-s/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": FRAMES / FRAME_RATE / v * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[1] sample on host cores: B=1 at the full 8B / codec shapes"},
+            "config": {"workload": "configs[1]: MossTTSDelay batch-64 x 10 s utterances bf16 (greedy, 96-token prompt, 156 steps) "
+                                   "+ MOSS-Audio-Tokenizer decode to 24 kHz",
+                       "sample": "bounded sample of that workload on the host cores: B=1 at the full 8B / codec shapes, fp32 "
+                                 "(the reference's CPU dtype), prefill + timed decode steps extrapolated to 156 + codec decode of 10 s",
+                       "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "frames": FRAMES},
             "cpu_baseline": best,
             "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
