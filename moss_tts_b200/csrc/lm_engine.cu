@@ -263,6 +263,7 @@ extern "C" int mt_lm_destroy(mt_lm* h) {
 extern "C" int mt_lm_forward(mt_lm* h, const int64_t* ids, const uint8_t* attn_mask, long long mask_ld, int B, int T,
                              int past_len, int last_only, void* text_logits, void* audio_logits, mt_stream s) {
   MT_CHECK(h && ids && attn_mask, "mt_lm_forward: null argument");
+  MT_CHECK(!h->sess.active, "mt_lm_forward: a sliced generation (mt_lm_stream_begin) owns this handle's KV cache and workspace");
   MT_CHECK(B > 0 && T > 0 && past_len >= 0, "mt_lm_forward: bad shape B=%d T=%d past=%d", B, T, past_len);
   return lm_forward_impl(h, ids, attn_mask, mask_ld, B, T, past_len, nullptr, past_len + T, last_only,
                          reinterpret_cast<bf16*>(text_logits), reinterpret_cast<bf16*>(audio_logits),
@@ -299,6 +300,7 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
                               const mt_gen_params* p, int64_t* gen_ids, int64_t* start_indices, int* n_steps,
                               float* step_ms, mt_stream stream) {
   MT_CHECK(h && input_ids && p && gen_ids && start_indices && n_steps, "mt_lm_generate: null argument");
+  MT_CHECK(!h->sess.active, "mt_lm_generate: a sliced generation (mt_lm_stream_begin) owns this handle's KV cache and workspace");
   const mt_lm_config& c = h->cfg;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   const int max_len = S0 + p->max_new_tokens;

@@ -142,3 +142,31 @@ def test_generate_stream_slices_and_single_row(codec):
 def test_generate_stream_rows_that_stop(codec):
     chunks, frames = _stream_case(codec, False, 4, 60, 2, True, left_pad=[0, 1, 0, 3])
     print("[generate_stream, stopping rows] frames per row", [len(f) for f in frames], "chunks", len(chunks))
+
+
+def test_open_session_owns_the_engine(codec):
+    ccfg, cmodel, _ = codec
+    cfg = LMConfig.tiny(n_vq=ccfg.num_quantizers)
+    lm = MossTTSDelayModel(cfg, make_lm_weights(cfg, seed=5, never_stop=True), device=DEV)
+    ids, mask = make_prompt(cfg, 2, 12, seed=3)
+    kw = dict(max_new_tokens=30, text_temperature=0, audio_temperature=0)
+    it = generate_stream(lm, cmodel, ids, mask, chunk_frames=2, **kw)
+    first = next(it)                                         # the session is open and has steps queued
+    with pytest.raises(ValueError):
+        lm.generate(ids, mask, **kw)
+    with pytest.raises(ValueError):
+        lm.forward(ids, mask)
+    with pytest.raises(RuntimeError):
+        with cmodel.streaming(2):                            # the codec is streaming for the session, too
+            pass
+    rest = list(it)
+    assert first[0].shape[0] == 2 and len(rest) >= 1
+    ref = lm.generate(ids, mask, **kw)                       # closed: the handle is free again and unchanged
+    for (a, x), (b_, y) in zip(ref, lm.last_stream_output):
+        assert a == b_ and torch.equal(x, y)
+    it2 = generate_stream(lm, cmodel, ids, mask, chunk_frames=2, **kw)
+    next(it2)
+    it2.close()                                              # abandoning a session releases engine and codec stream
+    assert torch.equal(lm.generate(ids, mask, **kw)[0][1], ref[0][1])
+    with cmodel.streaming(2):
+        pass
