@@ -15,6 +15,7 @@ Two pieces, both on the native path (libmosstts_sm100.so; no CPU fallback):
 from __future__ import annotations
 
 import ctypes as C
+from bisect import bisect_left
 from typing import Iterable, Iterator, List, Optional, Tuple
 
 import numpy as np
@@ -134,7 +135,8 @@ def plan_push(frame_rows: List[List[int]], finished: List[bool], scanned: int, p
     """Next lockstep push, or None.  A frame opened at generated row r is complete once row r + n_vq - 1 exists
     (`scanned` rows exist).  Unfinished rows must all have `chunk_frames` complete frames beyond the `pushed` already
     sent; once every row has finished, whatever is left goes out.  Returns (T, frames of each row inside the push)."""
-    avail = [sum(1 for r in fr if r + n_vq - 1 < scanned) - pushed for fr in frame_rows]
+    # frame_rows[b] is ascending: frames with r + n_vq - 1 < scanned are a prefix (O(log n) per row, long generations)
+    avail = [bisect_left(fr, scanned - n_vq + 1) - pushed for fr in frame_rows]
     live = [a for a, f in zip(avail, finished) if not f]
     T = min(live) if live else max(avail + [0])
     if T <= 0 or (live and T < chunk_frames):
