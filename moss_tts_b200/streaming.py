@@ -147,7 +147,8 @@ def plan_push(frame_rows: List[List[int]], finished: List[bool], scanned: int, p
 
 @torch.inference_mode()
 def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, *,
-                    chunk_frames: int = 8, lm_slice: Optional[int] = None, max_new_tokens: int = 1000,
+                    chunk_frames: int = 8, first_chunk_frames: Optional[int] = None, lm_slice: Optional[int] = None,
+                    max_new_tokens: int = 1000,
                     text_temperature: float = 1.5, text_top_p: float = 1.0, text_top_k: int = 50,
                     audio_temperature: float = 1.7, audio_top_p: float = 0.8, audio_top_k: int = 25,
                     audio_repetition_penalty: float = 1.0, seed: int = 0,
@@ -157,16 +158,19 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
     Yields ``(wav [B, T * downsample_rate] float32 on the device, valid_samples [B])`` per chunk: the next T frames of
     every row (rows that have already finished are padded, ``valid_samples[b]`` says how much of the chunk is row b's).
     A frame is pushed once all of its n_vq delayed codes exist, rows advance in lockstep, and a chunk leaves as soon
-    as ``chunk_frames`` frames are final for every unfinished row (everything left at the end).  The LM keeps one
-    slice of ``lm_slice`` (default ``chunk_frames``) steps queued on the caller's stream while the previous slice is
-    scanned / gathered / decoded on a side stream.  Afterwards ``model.last_stream_output`` holds what ``generate``
+    as ``chunk_frames`` frames are final for every unfinished row (everything left at the end);
+    ``first_chunk_frames`` (< ``chunk_frames``) lets the very first chunk leave earlier - short time to first audio with
+    the throughput of large chunks afterwards.  The LM keeps one slice of ``lm_slice`` (default: the smaller of the
+    two chunk sizes) steps queued on the caller's stream while the previous slice is scanned / gathered / decoded on a
+    side stream.  Afterwards ``model.last_stream_output`` holds what ``generate``
     would have returned, ``[(start_length, ids)]``.  All audio spans of a row feed one codec context.
     """
     c = model.config
     if input_ids.dim() != 3 or input_ids.shape[-1] != c.n_vq + 1:
         raise ValueError("`Input_ids`'s shape should be exactly (batch_size, sequence_length, 1 + n_vq).")
-    if chunk_frames < 1:
-        raise ValueError("chunk_frames must be >= 1")
+    if chunk_frames < 1 or (first_chunk_frames is not None and first_chunk_frames < 1):
+        raise ValueError("chunk_frames / first_chunk_frames must be >= 1")
+    first_chunk = min(int(first_chunk_frames), chunk_frames) if first_chunk_frames else chunk_frames
     dev = model.device
     B, S0, Cc = input_ids.shape
     nvq = c.n_vq
@@ -188,7 +192,7 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
     lm_stream = torch.cuda.current_stream(dev)
     lm_ptr = C.c_void_p(lm_stream.cuda_stream)
     side = torch.cuda.Stream(dev)
-    slice_steps = int(lm_slice or chunk_frames)
+    slice_steps = int(lm_slice or first_chunk)
     max_push = max(chunk_frames, int(round(codec.causal_transformer_context_duration * codec.sampling_rate))
                    // codec.downsample_rate)
     frame_rows: List[List[int]] = [[] for _ in range(B)]
@@ -241,7 +245,9 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                     if last:
                         finished = [True] * B
                     while True:
-                        plan = plan_push(frame_rows, finished, scanned, pushed, nvq, chunk_frames, max_push)
+                        first = pushed == 0 and first_chunk < chunk_frames
+                        plan = plan_push(frame_rows, finished, scanned, pushed, nvq, first_chunk if first else chunk_frames,
+                                         first_chunk if first else max_push)
                         if plan is None:
                             break
                         T, counts = plan

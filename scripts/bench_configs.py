@@ -104,14 +104,14 @@ def synth(args, dev):
     ccfg = CodecConfig.released()
     codec = MossAudioTokenizerModel.random_init(ccfg, device=dev, seed=99, workspace_bytes=8 << 30)
     steps = 60 if args.quick else 156
-    for B, cf in ((1, 4), (1, 8), (8, 8), (64, 8), (64, 25)):
+    for B, cf, fc in ((1, 4, None), (1, 8, None), (8, 8, None), (64, 8, None), (64, 25, None), (64, 25, 8), (64, 25, 4)):
         ids, mask = bench.make_prompts(cfg, B, seed=0)
         kw = dict(max_new_tokens=steps, text_temperature=0, audio_temperature=0)
         for rep in range(2):                                   # rep 0 warms graphs / lazy attributes
             torch.cuda.synchronize()
             t0 = time.perf_counter()
             first, n_chunks, frames = None, 0, 0
-            for wav, valid in generate_stream(lm, codec, ids, mask, chunk_frames=cf, **kw):
+            for wav, valid in generate_stream(lm, codec, ids, mask, chunk_frames=cf, first_chunk_frames=fc, **kw):
                 if first is None:
                     first = time.perf_counter() - t0
                 n_chunks += 1
@@ -123,7 +123,7 @@ def synth(args, dev):
         out = lm.generate(ids, mask, **kw)
         torch.cuda.synchronize()
         t_gen = time.perf_counter() - t0
-        print(json.dumps({"config": "streaming synthesis (8B shape + released codec, greedy)", "B": B, "chunk_frames": cf,
+        print(json.dumps({"config": "streaming synthesis (8B shape + released codec, greedy)", "B": B, "chunk_frames": cf, "first_chunk_frames": fc,
                           "steps": steps, "chunks": n_chunks, "frames_per_row": frames,
                           "first_audio_ms": None if first is None else first * 1e3, "total_ms": total * 1e3,
                           "generate_only_ms": t_gen * 1e3,

@@ -67,7 +67,8 @@ def test_audio_stream_decoder_matches_reference_chunks(codec):
         dec.push_tokens(torch.zeros(3, dtype=torch.long))
 
 
-def _stream_case(codec, never_stop, B, steps, chunk_frames, sample, left_pad=None, lm_slice=None, text_greedy=False):
+def _stream_case(codec, never_stop, B, steps, chunk_frames, sample, left_pad=None, lm_slice=None, text_greedy=False,
+                 first_chunk_frames=None):
     ccfg, cmodel, oracle = codec
     cfg = LMConfig.tiny(n_vq=ccfg.num_quantizers)
     w = make_lm_weights(cfg, seed=5, never_stop=never_stop)
@@ -79,7 +80,8 @@ def _stream_case(codec, never_stop, B, steps, chunk_frames, sample, left_pad=Non
     elif text_greedy:
         kw.update(text_temperature=0)                       # sampled audio codes under a never-stopping text channel
     ref = lm.generate(ids, mask, **kw)
-    chunks = list(generate_stream(lm, cmodel, ids, mask, chunk_frames=chunk_frames, lm_slice=lm_slice, **kw))
+    chunks = list(generate_stream(lm, cmodel, ids, mask, chunk_frames=chunk_frames, lm_slice=lm_slice,
+                                  first_chunk_frames=first_chunk_frames, **kw))
     out = lm.last_stream_output
     for (a, x), (b_, y) in zip(ref, out):                   # the sliced loop is the same loop
         assert a == b_ and torch.equal(x, y)
@@ -137,6 +139,12 @@ def test_generate_stream_slices_and_single_row(codec):
     _stream_case(codec, True, 1, 30, 3, False, lm_slice=5)
     _stream_case(codec, True, 2, 9, 4, False)               # too short for one complete frame... or exactly one
     _stream_case(codec, True, 2, 1, 4, False)               # max_new_tokens = 1: time_step 0 only
+
+
+def test_generate_stream_small_first_chunk(codec):
+    chunks, frames = _stream_case(codec, True, 2, 45, 6, False, first_chunk_frames=2)
+    sizes = [w.shape[1] // 1920 for w, _ in chunks]
+    assert sizes[0] == 2 and all(s >= 6 for s in sizes[1:-1]) and sum(sizes) == len(frames[0])
 
 
 def test_generate_stream_rows_that_stop(codec):
