@@ -13,12 +13,18 @@ const char* last_error() { return g_err.c_str(); }
 
 #include <stdlib.h>
 namespace mt {
-static int g_pdl_state = -1;   // -1 = read MT_NO_PDL from the environment on first use
+int exp_env(const char* name, int dflt) {
+#ifdef MT_EXPERIMENTS
+  const char* e = getenv(name);
+  return e && e[0] ? atoi(e) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
+}
+static int g_pdl_state = -1;   // -1 = first use (an MT_EXPERIMENTS build reads MT_NO_PDL); mt_debug_set_pdl overrides
 bool pdl_enabled() {
-  if (g_pdl_state < 0) {
-    const char* e = getenv("MT_NO_PDL");
-    g_pdl_state = (e && e[0] && e[0] != '0') ? 0 : 1;
-  }
+  if (g_pdl_state < 0) g_pdl_state = exp_env("MT_NO_PDL", 0) ? 0 : 1;
   return g_pdl_state == 1;
 }
 void set_pdl(int on) { g_pdl_state = on ? 1 : 0; }

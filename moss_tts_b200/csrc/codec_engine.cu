@@ -132,7 +132,7 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   if (h->w.input_proj[st]) MT_TRY(codec_linear(in, M, c.input_dim[st], h->w.input_proj[st], d, x, d, 0, nullptr, nullptr, s));
   else MT_CUDA(cudaMemcpyAsync(x, in, M * d * sizeof(float), cudaMemcpyDeviceToDevice, s));
   // MT_CODEC_ATTN_SIMT=1 keeps the fp32 CUDA-core kernel (+ the separate RoPE pass) as a cross-check of the TF32 one
-  static const bool simt_attn = [] { const char* e = getenv("MT_CODEC_ATTN_SIMT"); return e && e[0] == '1'; }();
+  static const bool simt_attn = exp_env("MT_CODEC_ATTN_SIMT", 0) != 0;
   // (cos, sin) table of this stage's positions, parked in `y` (only written again after the last layer)
   const bool table_fits = static_cast<long long>(Ts) * 64 <= y_floats;
   if (!simt_attn && table_fits) MT_TRY(codec_rope_table(y, static_cast<int>(Ts), 64, c.max_period, s, pos0));
@@ -142,7 +142,7 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   MT_CHECK(!(h16 && simt_attn), "MT_CODEC_ATTN_SIMT=1 needs a codec built with layer_gemm_f16 = 0");
   MT_CHECK(!h16 || table_fits, "codec: no room for the RoPE table of stage %d", st);
   // MT_CODEC_ATTN_TF32=1: keep q/k/v in fp32 and run the TF32 attention kernel inside an fp16-GEMM codec (A/B switch)
-  static const bool attn_tf32 = [] { const char* e = getenv("MT_CODEC_ATTN_TF32"); return e && e[0] == '1'; }();
+  static const bool attn_tf32 = exp_env("MT_CODEC_ATTN_TF32", 0) != 0;
   const bool a16 = h16 && !attn_tf32;
   for (int l = 0; l < c.num_layers[st]; ++l) {
     const mt_codec_layer& L = h->layers[st][l];

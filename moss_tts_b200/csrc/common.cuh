@@ -50,6 +50,9 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 bool pdl_enabled();
+// A/B switches between alternative (all correct) kernels are read from the environment only in a library built with
+// -DMT_EXPERIMENTS (make EXPERIMENTS=1); the product build ignores the environment and has no work-skipping switch.
+int exp_env(const char* name, int dflt);
 // Debug timeline buffer (mt_debug_set_trace): returns the next `words` uint64 slots, or nullptr when tracing is off.
 unsigned long long* trace_slot(int words);
 

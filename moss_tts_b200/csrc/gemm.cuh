@@ -42,9 +42,6 @@ struct LinearPlan {
   // untouched.  nullptr = always compute everything.
   const int* tile_filter_flag = nullptr;
   int tile_lo = 0, tile_hi = 0;
-  // Decode orientation with out_splits: fused SwiGLU consumer (see Epi::gu_counters).  Needs N = 2I with I % 128 == 0.
-  int* gu_counters = nullptr;
-  void* gu_act = nullptr;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -57,12 +54,6 @@ struct Epi {
   const float* scale; int round_bf16;
   int M, N;                       // logical output extent
   float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
-  // Decode-orientation kernel only (gemm_dec.cu), with `partial`: fused SwiGLU consumer.  N = 2I holds gate | up features;
-  // the CTA that delivers the LAST of the 2 * splits partial tiles of a (gate tile t, up tile t + tiles/2) pair sums the
-  // slabs in split order and writes gu_act[m, 128 t ..] = bf16(bf16(silu(gate)) * up) -- what silu_mul_kernel computes,
-  // without a kernel boundary.  gu_counters: tiles/2 ints, zero before the first launch (the last arriver resets its own).
-  int* gu_counters;
-  void* gu_act;
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }

@@ -38,8 +38,8 @@ struct DecCfg {
 template <int BN, int KIND /*1 bf16, 2 tf32, 3 fp16*/>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int rowsA,
-                int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled, int exp_nox,
-                const int* __restrict__ full_flag, int keep_lo, int keep_hi, int pf_stages, int pf_hint,
+                int rowsB, int k_blocks, int tiles, int splits, int w_early, int w_tiled,
+                const int* __restrict__ full_flag, int keep_lo, int keep_hi,
                 unsigned long long* __restrict__ trace) {
   using C = DecCfg<BN>;
   constexpr int S = C::kStages;
@@ -50,7 +50,6 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   uint64_t* tmem_full = empty + S;           // [2]
   uint64_t* tmem_empty = tmem_full + 2;      // [2]
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  volatile int* gu_last = reinterpret_cast<volatile int*>(tmem_holder + 2);     // fused-SwiGLU "last arriver" flag
   constexpr int kKElems = KIND == 2 ? 32 : 64;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -103,7 +102,6 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         else ptx::tma_load_2d(sa, &tmA, &full[st], kb * kKElems, tile * kTileA, ptx::kEvictFirst);
       };
       auto load_x = [&](int st, int kb) {
-        if (exp_nox) return;
         ptx::tma_load_2d(smem + st * C::kStageBytes + C::kABytes, &tmB, &full[st], kb * kKElems, 0, ptx::kEvictLast);
       };
       // pass 1 (only with constant weights): fill the ring with weight tiles before the dependency wait
@@ -113,22 +111,8 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int u = blockIdx.x; u < units && pre < depth; u += gridDim.x) {
           const int tile = u % tiles, split = u / tiles;
           for (int kb = kb_begin(split); kb < kb_begin(split + 1) && pre < depth; ++kb, ++pre) {
-            ptx::mbar_expect_tx(&full[pre], exp_nox ? C::kABytes : C::kStageBytes);
+            ptx::mbar_expect_tx(&full[pre], C::kStageBytes);
             load_w(pre, tile, kb);
-          }
-        }
-        // the ring is full and x is not there yet: use the idle HBM time to pull the NEXT weight tiles of this
-        // CTA's unit list into L2, where the ring will find them once the main loop drains it
-        if (pf_stages > 0) {
-          int idx = 0;
-          for (int u = blockIdx.x; u < units && idx < pre + pf_stages; u += gridDim.x) {
-            const int tile = u % tiles, split = u / tiles;
-            for (int kb = kb_begin(split); kb < kb_begin(split + 1) && idx < pre + pf_stages; ++kb, ++idx) {
-              if (idx < pre) continue;
-              const uint64_t hint = pf_hint == 0 ? ptx::kEvictFirst : (pf_hint == 1 ? ptx::kEvictNormal : ptx::kEvictLast);
-              if (w_tiled) ptx::tma_prefetch_2d(&tmA, 0, (tile * k_blocks + kb) * kTileA, hint);
-              else ptx::tma_prefetch_2d(&tmA, kb * kKElems, tile * kTileA, hint);
-            }
           }
         }
       }
@@ -143,7 +127,7 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
           const int st = it % S;
           if (it < pre) { load_x(st, kb); continue; }
           ptx::mbar_wait(&empty[st], ((it / S) & 1) ^ 1);
-          ptx::mbar_expect_tx(&full[st], exp_nox ? C::kABytes : C::kStageBytes);
+          ptx::mbar_expect_tx(&full[st], C::kStageBytes);
           load_w(st, tile, kb);
           load_x(st, kb);
         }
@@ -237,70 +221,6 @@ gemm_dec_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[buf]);
       ++i;
-      if (ep.gu_counters) {
-        // ---- fused SwiGLU consumer: the last of the 2 * splits contributors of a (gate, up) tile pair finishes it.
-        // bar.sync orders the eight epilogue warps' partial stores before the elected thread's gpu-scope acq_rel
-        // atomic (the CUTLASS semaphore pattern); the slabs are then read through L2 (ld.cg), never through L1.
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        const int pair = tile % (tiles >> 1);
-        if (warp == 2 && lane == 0) {
-          int old;
-          asm volatile("atom.add.acq_rel.gpu.global.s32 %0, [%1], 1;" : "=r"(old) : "l"(ep.gu_counters + pair) : "memory");
-          const int last = old == 2 * splits - 1;
-          if (last) ep.gu_counters[pair] = 0;          // nobody touches it again before the next launch
-          *gu_last = last;
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (*gu_last) {
-          const int I = ep.N >> 1;
-          const int e = threadIdx.x - 64;               // 0..255 over the epilogue warps
-          const int f4 = e & 31;                        // 32 float4 = the pair's 128 features
-          const long long slab = static_cast<long long>(ep.M) * ep.N;
-          bf16* act = reinterpret_cast<bf16*>(ep.gu_act);
-          for (int m0 = e >> 5; m0 < rowsB; m0 += 32) { // rows m0, m0 + 8, m0 + 16, m0 + 24: their loads fly together
-            float a[4][4], c[4][4];
-#pragma unroll
-            for (int r = 0; r < 4; ++r)
-#pragma unroll
-              for (int j = 0; j < 4; ++j) a[r][j] = c[r][j] = 0.f;
-            for (int s0 = 0; s0 < splits; s0 += 3) {
-              float4 x[4][3], y[4][3];
-#pragma unroll
-              for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int t = 0; t < 3; ++t) {
-                  const int m = m0 + 8 * r;
-                  if (m < rowsB && s0 + t < splits) {
-                    const float* pp = ep.partial + (s0 + t) * slab + static_cast<long long>(m) * ep.N + pair * 128 + 4 * f4;
-                    x[r][t] = __ldcg(reinterpret_cast<const float4*>(pp));
-                    y[r][t] = __ldcg(reinterpret_cast<const float4*>(pp + I));
-                  }
-                }
-#pragma unroll
-              for (int r = 0; r < 4; ++r)
-#pragma unroll
-                for (int t = 0; t < 3; ++t)
-                  if (m0 + 8 * r < rowsB && s0 + t < splits) {
-                    a[r][0] += x[r][t].x; a[r][1] += x[r][t].y; a[r][2] += x[r][t].z; a[r][3] += x[r][t].w;
-                    c[r][0] += y[r][t].x; c[r][1] += y[r][t].y; c[r][2] += y[r][t].z; c[r][3] += y[r][t].w;
-                  }
-            }
-#pragma unroll
-            for (int r = 0; r < 4; ++r) {
-              const int m = m0 + 8 * r;
-              if (m >= rowsB) continue;
-              float o[4];
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float gg = rbf(a[r][j]), uu = rbf(c[r][j]);
-                o[j] = rbf(gg / (1.f + expf(-gg))) * uu;
-              }
-              uint2 pk; pk.x = pack_bf16(o[0], o[1]); pk.y = pack_bf16(o[2], o[3]);
-              *reinterpret_cast<uint2*>(act + static_cast<long long>(m) * I + pair * 128 + 4 * f4) = pk;
-            }
-          }
-        }
-      }
     }
     if (warp == 2 && lane == 0) stamp(7);
   }
@@ -324,20 +244,13 @@ int launch_dec(const CUtensorMap& tmA, const CUtensorMap& tmB, const Epi& ep, in
   }
   const int units = tiles * splits;
   const int grid = units < kNumSMs ? units : kNumSMs;
-  // timing experiment only (garbage results): do not load the activation operand
-  static const int exp_nox = [] { const char* e = getenv("MT_EXP_NOX"); return e && e[0] == '1' ? 1 : 0; }();
-  // L2 prefetch depth (ring stages' worth of weight tiles per CTA) issued while waiting for the producer kernel
-  static const int pf_stages = [] { const char* e = getenv("MT_DEC_PF"); return e ? atoi(e) : 0; }();
-  static const int pf_hint = [] { const char* e = getenv("MT_DEC_PF_HINT"); return e ? atoi(e) : 0; }();
   MT_CUDA(launch(kern, dim3(grid), dim3(kThreads), C::kTotal, s, tmA, tmB, ep, rowsA, rowsB, k_blocks, tiles, splits,
-                 w_early, w_tiled, exp_nox, full_flag, keep_lo, keep_hi, pf_stages, pf_hint, trace_slot(kNumSMs * 8)));
+                 w_early, w_tiled, full_flag, keep_lo, keep_hi, trace_slot(kNumSMs * 8)));
   count_launch();
   return MT_OK;
 }
 
 }  // namespace
-
-static inline bool bf_in(int dtype) { return dtype == MT_DTYPE_BF16; }
 
 // Split count for the persistent kernel: minimise the longest CTA's work, counted in k-blocks, with every
 // unit charged ~2 k-blocks for its epilogue (a [128 x BN] fp32 partial tile costs about as much traffic).
@@ -383,18 +296,11 @@ int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   } else if (splits > 1) {
     ep.partial = p.workspace;
   }
-  if (p.gu_counters) {
-    MT_CHECK(p.out_splits && p.gu_act && p.N % 256 == 0 && !p.tile_filter_flag && bf_in(p.dtype_in),
-             "linear_dec: the fused SwiGLU consumer needs out_splits, bf16 inputs and N = 2I with I %% 128 == 0 (N=%d)", p.N);
-    ep.gu_counters = p.gu_counters; ep.gu_act = p.gu_act;
-  }
   const int w_tiled = p.w_tiled ? 1 : 0;
   // a filtered launch decides its unit list after the dependency wait: no early weight fetch
-  // (w_early = number of ring stages requested before the dependency wait.  The full ring is NOT the best
-  // choice: 148 CTAs x 8 stages = 19 MB of HBM requests land exactly when the small kernel between two GEMMs
-  // issues its handful of latency-critical L2 reads, which then queue behind them for ~3 us.)
-  static const int early_depth = [] { const char* e = getenv("MT_DEC_EARLY"); return e ? atoi(e) : 64; }();
-  const int w_early = p.w_static && !p.tile_filter_flag ? early_depth : 0;
+  // w_early = number of ring stages requested before the dependency wait (capped at the ring depth).
+  // Measured: any early depth other than the full ring is within +-1 %.
+  const int w_early = p.w_static && !p.tile_filter_flag ? 64 : 0;
   const int keep_lo = p.tile_lo / kTileA, keep_hi = p.tile_hi / kTileA;
   if (p.tile_filter_flag) MT_CHECK(splits == 1 && !p.out_splits, "linear_dec: the row-tile filter needs an unsplit GEMM");
   const int kind = mma_kind(p.dtype_in);

@@ -192,7 +192,7 @@ int launch_prefill(const bf16* q, const bf16* k_cache, const bf16* v_cache, cons
 
 bool attention_tc_supported(int n_heads, int n_kv, int D) {
   const int G = n_kv > 0 ? n_heads / n_kv : 0;
-  static const bool off = [] { const char* e = getenv("MT_OLD_PREFILL_ATTN"); return e && e[0] == '1'; }();
+  static const bool off = exp_env("MT_OLD_PREFILL_ATTN", 0) != 0;   // A/B: the SIMT two-pass kernel
   return !off && (D == 64 || D == 128) && (G == 1 || G == 2 || G == 4 || G == 8);
 }
 

@@ -41,11 +41,10 @@ static size_t carve_workspace(mt_lm* h, const mt_lm_config& c, void* ws) {
   auto tl = cv.take<bf16>(static_cast<size_t>(c.max_batch) * c.vocab_size);
   auto al = cv.take<bf16>(static_cast<size_t>(c.max_batch) * c.n_vq * c.audio_head_size);
   auto sk = cv.take<float>(kSplitKBytes / 4);
-  auto gc = cv.take<int>(kGuCounters);
   auto gs = cv.take<uint8_t>(gen_state_bytes(c.max_batch, 1 + c.n_vq, c.max_seq, c.audio_head_size));
   if (h) {
     h->x = x; h->xn = xn; h->qkv = qkv; h->q = q; h->attn = attn; h->gu = gu; h->act = act; h->delta = delta;
-    h->last_h = last_h; h->text_logits = tl; h->audio_logits = al; h->splitk = sk; h->gu_counters = gc; h->gen_state_buf = gs;
+    h->last_h = last_h; h->text_logits = tl; h->audio_logits = al; h->splitk = sk; h->gen_state_buf = gs;
   }
   return cv.off + 256;
 }
@@ -66,17 +65,8 @@ static int check_cfg(const mt_lm_config* c) {
 
 // One Linear on the LM path.  Small M: split-K partials handed to the consumer kernel (returns the
 // split count through *splits, partials in h->splitk); large M: finished bf16 output in `out`.
-bool gu_fusable(int M, int I) {
-  // Experiment, off by default (MT_GU_FUSE=1): measured 3.86 vs 3.77 ms/step.  The silu_mul launch and its dependency hop
-  // disappear (the down GEMM starts 5.9 us earlier), but ~66 last-arriving CTAs each pull 196 KB of slabs through ONE SM's
-  // L2 port at the very end of the gate|up GEMM (+7.6 us tail), where the stand-alone kernel spreads 18.9 MB over 148 SMs.
-  static const bool on = [] { const char* e = getenv("MT_GU_FUSE"); return e && e[0] == '1'; }();
-  return on && !g_force_simt && M <= 256 && I % 128 == 0 && I / 128 <= kGuCounters &&
-         static_cast<long long>(M) * 2 * I * 4 <= kSplitKBytes;
-}
-
 int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtensorMap* tm, int N, bf16* out,
-              int* splits, cudaStream_t s, const int* tile_filter_flag, int tile_lo, int tile_hi, bf16* gu_act) {
+              int* splits, cudaStream_t s, const int* tile_filter_flag, int tile_lo, int tile_hi) {
   LinearPlan p;
   p.M = M; p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = N;
   p.round_bf16 = 0; p.w_tmap = tm;
@@ -91,7 +81,6 @@ int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtens
     if (M <= 256 && static_cast<long long>(M) * N * 4 <= kSplitKBytes) p.out_splits = splits;
     else { *splits = 0; p.workspace = nullptr; p.workspace_bytes = 0; }
   }
-  if (gu_act && p.out_splits && gu_fusable(M, N / 2)) { p.gu_counters = h->gu_counters; p.gu_act = gu_act; }
   return linear(p, s);
 }
 
@@ -108,67 +97,40 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
   const float eps = c.rms_norm_eps;
   const long long MH = static_cast<long long>(M) * H;
 
-  // MT_DEBUG_SKIP (timing experiments only; results are garbage): 1 = no GEMMs, 2 = no norm/rope/silu
-  // kernels, 4 = no heads, 8 = no attention.  Unset/0 in every product and test run.
-  static const int dbg = [] { const char* e = getenv("MT_DEBUG_SKIP"); return e ? atoi(e) : 0; }();
-  static const bool old_attn = [] { const char* e = getenv("MT_OLD_ATTN"); return e && e[0] == '1'; }();
-  static const bool text_head_filter = [] { const char* e = getenv("MT_NO_HEAD_FILTER"); return !(e && e[0] == '1'); }();
-  const bool fused_attn = T == 1 && !old_attn && attn_decode_fits(B, c.num_heads, c.num_kv_heads, D, max_keys);
-#define MT_GEMM_(x) do { if (!(dbg & 1)) MT_TRY(x); else sp = 1; } while (0)
-#define MT_SMALL_(x) do { if (!(dbg & 2)) MT_TRY(x); } while (0)
+  const bool fused_attn = T == 1 && attn_decode_fits(B, c.num_heads, c.num_kv_heads, D, max_keys);
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
                    h->x, M, H, n_vq_embed < 0 ? c.n_vq : n_vq_embed, c.audio_head_size, c.vocab_size, s, 1 + c.n_vq));
-  // decode experiment (MT_KV_PREFETCH=1, off by default): the norm in front of a layer's qkv GEMM also asks L2 for that
-  // layer's K/V rows.  Measured: the attention phase gets 1 us shorter, the norm and the qkv GEMM 3.5 us longer
-  // (the extra HBM requests queue in front of their latency-critical reads): 3.92 vs 3.80 ms/step.
-  static const bool kv_pf = [] { const char* e = getenv("MT_KV_PREFETCH"); return e && e[0] == '1'; }();
-  KvPrefetch kvp;
-  auto kv_job = [&](int l) -> const KvPrefetch* {
-    if (!fused_attn || !kv_pf || !past_len_dev || l >= c.num_layers) return nullptr;
-    kvp.k = h->k_cache + l * layer_stride; kvp.v = h->v_cache + l * layer_stride;
-    kvp.item_stride = static_cast<long long>(c.max_seq) * D; kvp.items = B * c.num_kv_heads; kvp.row_bytes = D * 2;
-    kvp.pos_dev = past_len_dev;
-    return &kvp;
-  };
-  MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s,
-                     kv_job(0)));
+  MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s));
   for (int l = 0; l < c.num_layers; ++l) {
     bf16* kc = h->k_cache + l * layer_stride;
     bf16* vc = h->v_cache + l * layer_stride;
     int sp = 0;
-    MT_GEMM_(lm_linear(h, h->xn, M, H, h->w_qkv[l], &h->tm_qkv[l], nqkv, h->qkv, &sp, s));
+    MT_TRY(lm_linear(h, h->xn, M, H, h->w_qkv[l], &h->tm_qkv[l], nqkv, h->qkv, &sp, s));
     if (fused_attn) {
       // decode: q/k norm + RoPE + KV append + attention in one warp-per-(row, kv head) kernel
-      if (!(dbg & 8))
-        MT_TRY(attn_decode(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
+      MT_TRY(attn_decode(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
                            reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
                            reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), kc, vc,
                            mask, mask_ld, h->attn, B, c.num_heads, c.num_kv_heads, D, past_len_dev, past_len, max_keys,
                            c.max_seq, eps, s));
     } else {
-      MT_SMALL_(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
+      MT_TRY(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
                       reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
                       reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), h->q, kc,
                       vc, B, T, c.num_heads, c.num_kv_heads, D, past_len, past_len_dev, c.max_seq, eps, s));
-      if (!(dbg & 8))
-        MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
+      MT_TRY(attention(h->q, kc, vc, mask, mask_ld, h->attn, B, T, c.num_heads, c.num_kv_heads, D, past_len,
                          past_len_dev, max_keys, c.max_seq, s));
     }
-    MT_GEMM_(lm_linear(h, h->attn, M, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
-    MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
+    MT_TRY(lm_linear(h, h->attn, M, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
+    MT_TRY(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
                        reinterpret_cast<const bf16*>(h->ln_post[l]), h->xn, M, H, eps, s));
-    // decode: the gate|up GEMM's last-arriving CTA of every (gate, up) tile pair writes silu(gate) * up itself
-    const bool gu_fused = gu_fusable(M, I) && !(dbg & 3);
-    MT_GEMM_(lm_linear(h, h->xn, M, H, h->w_gu[l], &h->tm_gu[l], 2 * I, h->gu, &sp, s, nullptr, 0, 0, gu_fused ? h->act : nullptr));
-    if (!gu_fused) MT_SMALL_(silu_mul(h->gu, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * 2 * I, h->act, M, I, s));
-    MT_GEMM_(lm_linear(h, h->act, M, I, h->w_down[l], &h->tm_down[l], H, h->delta, &sp, s));
+    MT_TRY(lm_linear(h, h->xn, M, H, h->w_gu[l], &h->tm_gu[l], 2 * I, h->gu, &sp, s));
+    MT_TRY(silu_mul(h->gu, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * 2 * I, h->act, M, I, s));
+    MT_TRY(lm_linear(h, h->act, M, I, h->w_down[l], &h->tm_down[l], H, h->delta, &sp, s));
     const void* next_gain = l + 1 < c.num_layers ? h->ln_in[l + 1] : h->w.final_norm;
-    MT_SMALL_(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
-                       reinterpret_cast<const bf16*>(next_gain), h->xn, M, H, eps, s, kv_job(l + 1)));
+    MT_TRY(add_rmsnorm(h->x, h->delta, sp ? h->splitk : nullptr, sp, MH, h->x,
+                       reinterpret_cast<const bf16*>(next_gain), h->xn, M, H, eps, s));
   }
-#undef MT_GEMM_
-#undef MT_SMALL_
-  if (dbg & 4) return MT_OK;
   // heads (modeling_moss_tts.py:292-300)
   const bf16* hs = h->xn;
   int Mh = M;
@@ -184,7 +146,7 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
     const int lo = std::min(c.audio_assistant_gen_slot_token_id, c.audio_assistant_delay_slot_token_id);
     const int hi = std::max(c.audio_assistant_gen_slot_token_id, c.audio_assistant_delay_slot_token_id);
     MT_TRY(lm_linear(h, hs, Mh, H, h->w.text_head, &h->tm_text, c.vocab_size, text_logits, nullptr, s,
-                     text_head_filter ? text_full_flag : nullptr, lo, hi));
+                     text_full_flag, lo, hi));
   }
   if (audio_logits) {
     const int NA = c.n_vq * c.audio_head_size;
@@ -224,7 +186,6 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
   cp(h->w_qkv, w->w_qkv); cp(h->w_o, w->w_o); cp(h->w_gu, w->w_gate_up); cp(h->w_down, w->w_down);
   cp(h->ln_in, w->ln_in); cp(h->ln_post, w->ln_post); cp(h->q_norm, w->q_norm); cp(h->k_norm, w->k_norm);
   h->ws_bytes = carve_workspace(h, *cfg, workspace);
-  if (cudaMemset(h->gu_counters, 0, kGuCounters * sizeof(int)) != cudaSuccess) { delete h; return fail(MT_ERR_CUDA, "mt_lm_create: cannot clear the workspace"); }
   const size_t half = kv_bytes_of(*cfg) / 2 / sizeof(bf16);
   h->k_cache = reinterpret_cast<bf16*>(kv_cache);
   h->v_cache = h->k_cache + half;
@@ -246,7 +207,10 @@ extern "C" int mt_lm_create(const mt_lm_config* cfg, const mt_lm_weights* w, voi
   // a backbone without heads (MossTTSLocal's global transformer) passes NULL head weights
   if (st == MT_OK && w->text_head) st = wmap(&h->tm_text, w->text_head, cfg->vocab_size, H);
   if (st == MT_OK && w->audio_heads) st = wmap(&h->tm_audio, w->audio_heads, NA, H);
-  if (st != MT_OK) { delete h; return st; }
+  if (st == MT_OK && cudaMallocHost(&h->done_host, 4 * sizeof(int)) != cudaSuccess) st = fail(MT_ERR_CUDA, "mt_lm_create: pinned poll slots");
+  for (auto& e : h->poll_ev)
+    if (st == MT_OK && cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) st = fail(MT_ERR_CUDA, "mt_lm_create: poll event");
+  if (st != MT_OK) { mt_lm_destroy(h); return st; }
   *out = h;
   return MT_OK;
 }
@@ -256,6 +220,8 @@ extern "C" int mt_lm_destroy(mt_lm* h) {
   if (h->graph_exec) cudaGraphExecDestroy(h->graph_exec);
   if (h->sess.exec) cudaGraphExecDestroy(h->sess.exec);
   if (h->cap_stream) cudaStreamDestroy(h->cap_stream);
+  for (auto& e : h->poll_ev) if (e) cudaEventDestroy(e);
+  if (h->done_host) cudaFreeHost(h->done_host);
   delete h;
   return MT_OK;
 }
@@ -318,9 +284,14 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   MT_TRY(gen_init(st, input_ids, attention_mask, S0, tk, start_indices, s));
   if (p->max_new_tokens == 0) return MT_OK;
 
-  std::vector<cudaEvent_t> ev;
+  // per-step timing events (record_step_times only); destroyed on every exit path
+  struct Events {
+    std::vector<cudaEvent_t> v;
+    ~Events() { for (auto e : v) if (e) cudaEventDestroy(e); }
+  } evs;
+  std::vector<cudaEvent_t>& ev = evs.v;
   if (step_ms) {
-    ev.resize(p->max_new_tokens + 1);
+    ev.assign(p->max_new_tokens + 1, nullptr);
     for (auto& e : ev) MT_CUDA(cudaEventCreate(&e));
     MT_CUDA(cudaEventRecord(ev[0], s));
   }
@@ -342,11 +313,9 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   // always has check_every .. 2*check_every steps queued.  (A blocking poll empties the queue and exposes the launch
   // latency of a ~300-node graph, ~0.4 ms, at every poll.)  Steps that run after every row has stopped are no-ops for
   // the state machine; the step count comes from the device at the end.
-  int* done_host = nullptr;
-  MT_CUDA(cudaMallocHost(&done_host, 4 * sizeof(int)));
+  int* done_host = h->done_host;
   done_host[0] = done_host[1] = 0;
-  cudaEvent_t poll_ev[2] = {nullptr, nullptr};
-  for (auto& e : poll_ev) MT_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  cudaEvent_t* poll_ev = h->poll_ev;
   int polls = 0;
   const int check_every = p->check_stop_every > 0 ? p->check_stop_every : 8;
   cudaGraphExec_t exec = nullptr;
@@ -398,10 +367,7 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
     for (int i = 0; i < p->max_new_tokens; ++i) step_ms[i] = -1.f;
     for (int i = 0; i < steps_launched; ++i) cudaEventElapsedTime(&step_ms[i], ev[i], ev[i + 1]);
   }
-  for (auto& e : ev) cudaEventDestroy(e);
   if (exec) cudaGraphExecDestroy(exec);
-  for (auto& e : poll_ev) if (e) cudaEventDestroy(e);
-  cudaFreeHost(done_host);
   return status;
 }
 

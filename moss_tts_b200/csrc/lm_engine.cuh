@@ -14,7 +14,6 @@ struct mt_lm {
   // workspace views
   mt::bf16 *x, *xn, *qkv, *q, *attn, *gu, *act, *delta, *last_h, *text_logits, *audio_logits;
   float* splitk;
-  int* gu_counters;              // fused SwiGLU consumer of the decode gate|up GEMM (Epi::gu_counters), zeroed at create
   void* gen_state_buf;
   mt::bf16 *k_cache, *v_cache;   // [L][B][kv][S][D] each
   size_t ws_bytes;
@@ -22,6 +21,9 @@ struct mt_lm {
   cudaGraphExec_t graph_exec = nullptr;
   cudaStream_t cap_stream = nullptr;   // capture-only stream (the caller's stream may be the legacy default stream)
   int graph_B = 0; long long graph_key = 0;
+  // stop polling (mt_lm_generate): pinned result slots and their events live as long as the handle
+  int* done_host = nullptr;            // 4 ints, cudaMallocHost at create
+  cudaEvent_t poll_ev[2] = {nullptr, nullptr};
   // sliced generation (mt_lm_stream_*): the loop state of one generate() call kept between calls
   struct Session {
     bool active = false;
@@ -39,11 +41,7 @@ constexpr long long kSplitKBytes = 96ll << 20;
 // One Linear on the LM path.  Small M: split-K partials handed to the consumer kernel (returns the split
 // count through *splits, partials in h->splitk); large M or splits == nullptr: finished bf16 output in `out`.
 int lm_linear(mt_lm* h, const bf16* x, int M, int K, const void* w, const CUtensorMap* tm, int N, bf16* out,
-              int* splits, cudaStream_t s, const int* tile_filter_flag = nullptr, int tile_lo = 0, int tile_hi = 0,
-              bf16* gu_act = nullptr);
-// true when lm_linear(..., N = 2I, ..., gu_act) will finish silu(gate) * up inside the GEMM (no silu_mul launch needed)
-bool gu_fusable(int M, int I);
-constexpr int kGuCounters = 1024;
+              int* splits, cudaStream_t s, const int* tile_filter_flag = nullptr, int tile_lo = 0, int tile_hi = 0);
 
 // Backbone forward over B*T tokens.  Leaves the final-norm hidden states in h->xn ([B*T, H]; with last_only
 // and T > 1 the last position of every row is also gathered into h->last_h).  Heads are skipped when both

@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(512)
 add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ delta,
                    const float* __restrict__ partials, int nsplit, long long split_stride,
                    bf16* __restrict__ x_out, const bf16* __restrict__ gain, bf16* __restrict__ normed, int H,
-                   float eps, unsigned long long* __restrict__ trace, KvPrefetch kv) {
+                   float eps, unsigned long long* __restrict__ trace) {
   __shared__ float scratch[40];
   const long long m = blockIdx.x;
   auto stamp = [&](int e) {                  // timeline instrumentation (mt_debug_set_trace; null in product runs)
@@ -188,18 +188,6 @@ add_rmsnorm_kernel(const bf16* __restrict__ residual, const bf16* __restrict__ d
       }
       if (residual) rr[it] = *reinterpret_cast<const uint2*>(residual + m * H + c);
       if (normed) gg[it] = *reinterpret_cast<const uint2*>(gain + c);
-    }
-  }
-  if (kv.items > 0) {        // after this kernel's own loads: the next attention's K/V rows -> L2
-    const int pos = *kv.pos_dev;
-    // one 128-byte line per instruction, spread over every thread of the grid (a bulk prefetch per (row, kv head)
-    // serialises in the few issuing SMs' TMA units: +70 us)
-    const int lines_per_item = pos * kv.row_bytes / 128;
-    const long long total = 2ll * kv.items * lines_per_item;
-    for (long long i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
-      const int item = static_cast<int>(i / lines_per_item), line = static_cast<int>(i % lines_per_item);
-      const bf16* p = (item < kv.items ? kv.k : kv.v) + static_cast<long long>(item % kv.items) * kv.item_stride + line * 64;
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     }
   }
   float v[kIt][4];
@@ -309,8 +297,7 @@ add_rmsnorm_rows_kernel(const bf16* __restrict__ residual, const bf16* __restric
 }
 
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
-                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s,
-                const KvPrefetch* kv) {
+                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s) {
   MT_CHECK(H % 4 == 0, "hidden size must be a multiple of 4");
   const size_t smem = (H + 40) * sizeof(float);
   int threads = ((H / 4 + 31) / 32) * 32;
@@ -319,7 +306,7 @@ int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, 
     MT_CUDA(launch(add_rmsnorm_rows_kernel, dim3(M), dim3(256), 0, s, residual, delta, x_out, gain, normed, H, eps));
   } else if (H <= 2 * 4 * threads) {
     MT_CUDA(launch(add_rmsnorm_kernel, dim3(M), dim3(threads), 0, s, residual, delta, partials, nsplit, split_stride,
-                   x_out, gain, normed, H, eps, M <= 1024 ? trace_slot(M * 8) : nullptr, kv ? *kv : KvPrefetch{}));
+                   x_out, gain, normed, H, eps, M <= 1024 ? trace_slot(M * 8) : nullptr));
   } else {
     MT_CUDA(launch(add_rmsnorm_generic_kernel, dim3(M), dim3(threads), smem, s, residual, delta, partials, nsplit,
                    split_stride, x_out, gain, normed, H, eps, static_cast<unsigned long long*>(nullptr)));

@@ -8,20 +8,8 @@ namespace mt {
 // ids rows are `row_stride` int64 wide (0 = 1 + n_vq); only channel 0 and the first n_vq audio channels are summed
 int embed_sum(const int64_t* ids, const bf16* emb_text, const bf16* emb_ext, bf16* out, int M, int H, int n_vq,
               int audio_rows, int vocab, cudaStream_t s, int row_stride = 0);
-// Optional job for the decode-step add_rmsnorm that precedes a layer's qkv GEMM: ask L2 for the K/V rows [0, pos) of
-// every (row, kv head) of that layer.  HBM is idle while the norm runs, and the attention kernel two launches later
-// then finds its keys and values on chip instead of paying HBM latency inside its dependent chain.
-struct KvPrefetch {
-  const bf16* k = nullptr;       // layer base of the K cache; V cache at `v`
-  const bf16* v = nullptr;
-  long long item_stride = 0;     // elements between consecutive (row, kv head) blocks = max_seq * D
-  int items = 0;                 // B * n_kv
-  int row_bytes = 0;             // D * 2
-  const int* pos_dev = nullptr;  // rows [0, *pos_dev) are fetched
-};
 int add_rmsnorm(const bf16* residual, const bf16* delta, const float* partials, int nsplit, long long split_stride,
-                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s,
-                const KvPrefetch* kv = nullptr);
+                bf16* x_out, const bf16* gain, bf16* normed, int M, int H, float eps, cudaStream_t s);
 int qkv_post(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
              const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* q_out, bf16* k_cache,
              bf16* v_cache, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
@@ -30,7 +18,7 @@ int attention(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uin
               bf16* out, int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev,
               int max_keys, int max_seq, cudaStream_t s);
 // tensor-core two-pass form of `attention` for any T and any number of keys (lm_attn_prefill.cu); `attention`
-// dispatches to it when the head layout is supported (MT_OLD_PREFILL_ATTN=1 keeps the SIMT kernel for A/B runs)
+// dispatches to it when the head layout is supported
 bool attention_tc_supported(int n_heads, int n_kv, int D);
 int attention_tc(const bf16* q, const bf16* k_cache, const bf16* v_cache, const uint8_t* mask, long long mask_ld, bf16* out,
                  int B, int T, int n_heads, int n_kv, int D, int past_len, const int* past_len_dev, int max_seq,
