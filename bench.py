@@ -86,13 +86,81 @@ def make_prompts(cfg, batch, seed):
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU baseline: the oracle (a port of the reference's PyTorch path) on the host cores
+# CPU baseline: the reference's own code (oracle/_ref, built by oracle/ref.py) on the host cores;
+# the oracle port only when the reference is not in the snapshot
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline(decode_steps: int = 3):
-    """B=1 sample of the same workload at the full shapes: prefill(96) + `decode_steps` decode steps of
-    the 8B-shape LM (fp32, eager attention: the reference's CPU choice, README.md:218-219) + a full
-    10 s codec decode, extrapolated to 156 steps.  All 36 layers alias ONE layer's weight tensors
-    (772 MB > LLC, so timing equals distinct layers) to avoid a 34 GB / 140 s init."""
+_REF_MODELS = None
+
+
+def host_threads() -> int:
+    """torchrun exports OMP_NUM_THREADS=1: the CPU arm must use the box's cores at every N."""
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
+def reference_models():
+    """(reference MossTTSDelayModel at the assumed 8B shape, reference processor over the reference codec), fp32,
+    the reference's own random init; built once per process."""
+    global _REF_MODELS
+    if _REF_MODELS is None:
+        from moss_tts_b200.config import LMConfig
+        from oracle import ref
+        t0 = time.perf_counter()
+        torch.manual_seed(0)
+        lm = ref.build_lm_bench(LMConfig.delay_8b(), alias_layers=True, never_stop=True)
+        codec = ref.build_codec_bench()
+        _REF_MODELS = (lm, ref.bare_processor(codec), time.perf_counter() - t0)
+    return _REF_MODELS
+
+
+def reference_utterance(new_tokens: int = NEW_TOKENS):
+    """ONE utterance of the bench workload through the reference's own public path, unmodified:
+    MossTTSDelayModel.generate (modeling_moss_tts.py:392-525, greedy) -> MossTTSDelayProcessor._parse_audio_codes
+    (processing_moss_tts.py:668-709: de-delay, split, codec.decode(chunk_duration=8), trim).  Returns
+    (seconds, codec-decoded frames, seconds inside generate)."""
+    import contextlib
+    import io
+    from moss_tts_b200.config import LMConfig
+    lm, proc, _ = reference_models()
+    ids, mask = make_prompts(LMConfig.delay_8b(), 1, 0)
+    t0 = time.perf_counter()
+    with contextlib.redirect_stderr(io.StringIO()):              # the reference prints a tqdm bar per step
+        out = lm.generate(ids, mask, max_new_tokens=new_tokens, text_temperature=0, audio_temperature=0)
+    t1 = time.perf_counter()
+    samples = 0
+    for start_length, g in out:
+        for w in proc._parse_audio_codes(int(start_length), g[:, 1:]):
+            samples += w.numel()
+    t2 = time.perf_counter()
+    # the reference trims start_length/first_codes_length of the first segment (1 frame here): count decoded frames
+    frames = new_tokens + 1 - 32 if new_tokens + 1 > 32 else 0
+    return t2 - t0, frames, t1 - t0, samples
+
+
+def cpu_baseline():
+    """The bench workload for ONE utterance (B = 1 of the 64) at the full shapes on the host cores."""
+    threads = host_threads()
+    from oracle import ref
+    if ref.available():
+        _, _, t_build = reference_models()
+        secs, frames, t_gen, samples = reference_utterance()
+        return {"value": frames / FRAME_RATE / secs, "unit": "audio-s/s", "cores": threads, "kind": "reference",
+                "sample": f"B=1 (one of the {BATCH_PER_GPU} utterances), the reference's own generate() + processor decode, fp32, "
+                          f"eager attention, assumed 8B shape with layers 1..35 aliasing layer 0's weights (772 MB/layer, DRAM-streamed), "
+                          f"released codec config.json: {NEW_TOKENS} steps in {t_gen:.1f}s + codec {secs - t_gen:.2f}s = {secs:.1f}s "
+                          f"for {frames} frames ({samples} samples); model build {t_build:.0f}s not timed",
+                "seconds": secs, "generate_s": t_gen, "frames": frames}
+    return cpu_baseline_port()
+
+
+def cpu_baseline_port(decode_steps: int = 3):
+    """Fallback when oracle/_ref is not in the snapshot: the oracle PORT (kind "port"), B=1 at the full shapes:
+    prefill(96) + `decode_steps` decode steps + a 10 s codec decode, extrapolated to 156 steps."""
     from moss_tts_b200.config import LMConfig, CodecConfig
     from oracle.lm import OracleLM
     from oracle.codec import OracleCodec
@@ -158,7 +226,8 @@ def time_dominant_kernel(model, batch, iters=3):
     """Times gemm_dec_kernel on the largest per-layer decode GEMM (gate|up: [2I, H] weights, M = batch) the way the
     engine launches it (mt_gemm with out_splits: fp32 split-K partials left for the consumer kernel, ONE kernel per
     call), cycling over all layers' weights so every launch streams from HBM (36 x 201 MB >> 126 MB L2).
-    Returns (avg ms per launch, algorithmic bytes per launch, splits, avg ms incl. the stand-alone reduce kernel)."""
+    Returns (avg ms per launch, algorithmic bytes per launch, splits, avg ms incl. the stand-alone reduce kernel,
+    bytes of fp32 split-K slabs the launch writes)."""
     import ctypes as C
     from moss_tts_b200 import _lib as L
     cfg = model.config
@@ -193,8 +262,9 @@ def time_dominant_kernel(model, batch, iters=3):
         return e0.elapsed_time(e1) / n
     ms_full = run(False)                               # finished bf16 tensor: GEMM + split-K reduce kernel
     ms = run(True)                                     # the kernel alone, as inside a decode step
-    alg = N * H * 2 + batch * H * 2 + splits.value * batch * N * 4
-    return ms, alg, splits.value, ms_full
+    alg = N * H * 2 + batch * H * 2 + batch * N * 2      # weights + x + the bf16 output, nothing else
+    slab = splits.value * batch * N * 4                   # implementation traffic (fp32 split-K slabs), reported apart
+    return ms, alg, splits.value, ms_full, slab
 
 
 def ncu_traffic():
@@ -207,6 +277,15 @@ def ncu_traffic():
         return None
 
 
+def refuse_mt_env():
+    """The product library ignores the environment (A/B switches exist only in an EXPERIMENTS=1 build); a bench run
+    with any MT_* variable set is refused anyway, so that no number can come from a non-default configuration."""
+    bad = sorted(k for k in os.environ if k.startswith("MT_"))
+    if bad:
+        print(json.dumps({"metric": METRIC, "value": None, "invalid": "MT_* environment variables are set: " + ", ".join(bad)}), flush=True)
+        sys.exit(2)
+
+
 def run_ours(args):
     from moss_tts_b200 import _lib as L
     from moss_tts_b200.config import LMConfig, CodecConfig
@@ -217,6 +296,7 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
+    refuse_mt_env()
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback for the product arm)"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -237,23 +317,34 @@ def run_ours(args):
     ids_d, mask_d = ids_h.to(dev), mask_h.to(dev)
     gen_kw = dict(max_new_tokens=NEW_TOKENS, text_temperature=0, audio_temperature=0)
     wav_h = torch.empty(B, FRAMES * ccfg.downsample_rate, dtype=torch.float32).pin_memory()
+    wav_all = torch.empty(B * world, FRAMES * ccfg.downsample_rate, dtype=torch.float32).pin_memory() if (world > 1 and rank == 0) else None
+    if world > 1:
+        from moss_tts_b200.sharding import gather_variable
 
     def step_device():
         out = model.generate(ids_d, mask_d, **gen_kw)
         return proc.decode_device(out)
 
+    gathered_bytes = [0]
+
     def step_e2e():
         out = model.generate(ids_h, mask_h, **gen_kw)          # H2D of the prompt inside
         wavs = proc.decode_device(out)
         n = 0
-        for b, ws in enumerate(wavs):
-            w = ws[0]
-            wav_h[b, : w.numel()].copy_(w, non_blocking=True)   # D2H of the result
-            n += w.numel()
-        if dist is not None:                                     # NCCL only gathers outputs (lengths here)
-            lens = torch.tensor([n], device=dev)
-            allv = [torch.zeros_like(lens) for _ in range(world)]
-            dist.all_gather(allv, lens)
+        if dist is not None:
+            # north_star: "NCCL used only to gather outputs": all_gather of the lengths, then ncclGather of the padded
+            # waveforms to rank 0 (moss_tts_b200/sharding.py), device tensors over NVLink, then ONE D2H on rank 0
+            rows = gather_variable([ws[0] for ws in wavs], device=dev)
+            n = sum(ws[0].numel() for ws in wavs)
+            if rank == 0:
+                for b, w in enumerate(rows):
+                    wav_all[b, : w.numel()].copy_(w, non_blocking=True)
+                gathered_bytes[0] = sum(w.numel() for w in rows) * 4
+        else:
+            for b, ws in enumerate(wavs):
+                w = ws[0]
+                wav_h[b, : w.numel()].copy_(w, non_blocking=True)   # D2H of the result
+                n += w.numel()
         torch.cuda.current_stream(dev).synchronize()
         return n
 
@@ -280,8 +371,14 @@ def run_ours(args):
     for _ in range(args.warmup):
         wavs = step_device()
     step_e2e()
-    frames = sum(w[0].numel() for w in wavs) / ccfg.downsample_rate
-    audio_s_per_step = B * FRAMES / FRAME_RATE              # codec-decoded frames / 12.5
+    # codec-decoded frames: the waveform of a row is its 125 frames minus the processor's start_length trim of 1/125
+    samples = sum(w[0].numel() for w in wavs)
+    frames = B * FRAMES
+    assert len(wavs) == B and all(len(w) == 1 for w in wavs), "every utterance must decode to exactly one audio segment"
+    assert abs(samples - B * (FRAMES - 1) * ccfg.downsample_rate) <= B, \
+        f"decoded {samples} samples, expected {B} x {FRAMES} frames (minus the 1-frame start_length trim)"
+    assert model.last_n_steps == NEW_TOKENS, f"generate ran {model.last_n_steps} steps, expected {NEW_TOKENS}"
+    audio_s_per_step = frames / FRAME_RATE                  # codec-decoded frames / 12.5
     sampler = ClockSampler(local)
     sampler.start()
     l0 = L.launch_count()
@@ -303,10 +400,18 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     hbm, tflops, src = measured_peaks()
-    k_ms, k_bytes, k_splits, k_ms_full = time_dominant_kernel(model, B)
+    k_ms, k_bytes, k_splits, k_ms_full, k_slab = time_dominant_kernel(model, B)
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
-    weight_bytes = sum(t.numel() for k in ("qkv", "o", "gu", "down") for t in model._w[k]) * 2 + \
-        (model._w["text_head"].numel() + model._w["audio_heads"].numel()) * 2
+    # bytes a decode step of THIS run streams from HBM: all layer weights + the audio heads + the text-head row tile(s)
+    # that hold the gen/delay-slot rows (every row of the bench batch is inside an audio span at every step, so the
+    # text-head filter is on throughout and the other 1.24 GB of the text head are never read)
+    H = cfg.hidden_size
+    lo, hi = sorted((cfg.audio_assistant_gen_slot_token_id, cfg.audio_assistant_delay_slot_token_id))
+    text_tiles = hi // 128 - lo // 128 + 1
+    layer_bytes = sum(t.numel() for k in ("qkv", "o", "gu", "down") for t in model._w[k]) * 2
+    streamed_bytes = layer_bytes + model._w["audio_heads"].numel() * 2 + text_tiles * 128 * H * 2
+    full_head_bytes = layer_bytes + (model._w["text_head"].numel() + model._w["audio_heads"].numel()) * 2
+    kv_bytes_mid = B * (PROMPT_LEN + NEW_TOKENS // 2) * cfg.num_layers * 2 * cfg.kv_size * 2
     line = {
         "metric": METRIC, "value": world * audio_s_per_step * args.steps / (ms_dev * 1e-3), "unit": "audio-s/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
@@ -320,49 +425,76 @@ def run_ours(args):
                             "projections; waveform SNR vs the fp32 reference 48.9-50.9 dB (gate: >= 40 dB)",
                    "batch_per_gpu": B, "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "frames": FRAMES,
                    "sharding": f"request-sharded x{world}, no in-step collective",
-                   "l2_policy": "inputs larger than L2: 15.4 GB of weights streamed every decode step"},
+                   "l2_policy": "inputs larger than L2: %.2f GB of weights streamed every decode step (text head filtered to %d "
+                                "row tile; %.2f GB with the full text head)" % (streamed_bytes / 1e9, text_tiles, full_head_bytes / 1e9),
+                   "nccl": ("all_gather of lengths + ncclGather of padded fp32 waveforms to rank 0 inside the e2e step: %d bytes per step"
+                            % gathered_bytes[0]) if world > 1 else "none (N=1)"},
         "e2e": {"value": world * audio_s_per_step * args.steps / (ms_e2e * 1e-3), "unit": "audio-s/s",
-                "h2d_bytes_per_step": ids_h.numel() * 8 + mask_h.numel(), "d2h_bytes_per_step": int(n_samples) * 4,
+                "h2d_bytes_per_step": ids_h.numel() * 8 + mask_h.numel(), "d2h_bytes_per_step": int(gathered_bytes[0]) if world > 1 else int(n_samples) * 4,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": int(launches),
         "decode_ms_per_step": dec_med, "prefill_ms": prefill_ms, "codec_ms": codec_ms,
-        "decode_weight_stream_gbs": weight_bytes / (dec_med * 1e-3) / 1e9 if dec_med == dec_med else None,
+        "decode_weight_stream_gbs": streamed_bytes / (dec_med * 1e-3) / 1e9 if dec_med == dec_med else None,
+        "roofline_step": {"bound": "hbm", "streamed_bytes": streamed_bytes, "kv_bytes_mid_generation": kv_bytes_mid,
+                          "achieved": (streamed_bytes + kv_bytes_mid) / (dec_med * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
+                          "frac": (streamed_bytes + kv_bytes_mid) / (dec_med * 1e-3) / 1e9 / hbm,
+                          "what": "whole decode step in situ: weight + KV bytes actually streamed / median decode-step time"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                      "traffic": ncu_traffic(), "kernel": "gemm_dec_kernel<BN=64,bf16> gate|up decode GEMM (M=%d,N=%d,K=%d) through mt_gemm as the engine "
                                "launches it: %d split-K fp32 partial slabs left for the fused consumer" % (B, 2 * cfg.intermediate_size, cfg.hidden_size, k_splits),
-                     "ms_per_launch": k_ms, "algorithmic_bytes": k_bytes, "peak_source": src,
+                     "ms_per_launch": k_ms, "algorithmic_bytes": k_bytes, "algorithmic_bytes_def": "weights N*K*2 + x M*K*2 + bf16 output M*N*2",
+                     "splitk_slab_bytes_written": k_slab, "peak_source": src,
                      "ms_per_call_with_own_reduce_kernel": k_ms_full},
         "clocks": clocks,
     }
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:          # cpu_baseline: rank 0 at N = 1 only
         try:
             line["cpu_baseline"] = cpu_baseline() if not args.small else {"value": None, "kind": "port", "sample": "skipped (--small)"}
         except Exception as e:           # the baseline must not take the product number down with it
-            line["cpu_baseline"] = {"value": None, "kind": "port", "error": repr(e)[:200]}
+            line["cpu_baseline"] = {"value": None, "kind": "reference", "error": repr(e)[:300]}
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
 
 def run_reference(args):
-    """Reference arm: the reference's CPU implementation of the path (the oracle port; the reference is
-    pure Python/PyTorch and cannot be shipped to the box), all host threads, bounded sample per step."""
+    """Reference arm: the UNMODIFIED reference (oracle/_ref) on the host cores, all host threads, through its own public
+    path.  A "step" is a bounded sample of the workload: ONE of the 64 utterances, start to finish (96-token prompt, 156
+    greedy steps, processor decode to 24 kHz) -- timed as it ran, no extrapolation.  The step count is clamped so the run
+    ends within a few minutes.  Falls back to the oracle port (kind "port") only when oracle/_ref is not in the snapshot."""
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    res = []
-    for _ in range(max(1, min(args.steps, 2))):
-        res.append(cpu_baseline(decode_steps=2))
-    best = max(res, key=lambda r: r["value"])
-    v = best["value"]
+    threads = host_threads()
+    from oracle import ref
+    if not ref.available():
+        best = cpu_baseline_port(decode_steps=2)
+        v, ms, steps = best["value"], FRAMES / FRAME_RATE / best["value"] * 1e3, 1
+        sample = best["sample"]
+    else:
+        _, _, t_build = reference_models()
+        reference_utterance(new_tokens=36)                             # warm-up: allocator, mkldnn primitives
+        steps = max(1, min(args.steps, 2))
+        runs = [reference_utterance()]
+        while len(runs) < steps and sum(r[0] for r in runs) < 60.0:      # keep the whole arm within a few minutes
+            runs.append(reference_utterance())
+        steps = len(runs)
+        secs = sum(r[0] for r in runs)
+        frames = sum(r[1] for r in runs)
+        v, ms = frames / FRAME_RATE / secs, secs / steps * 1e3
+        best = {"value": v, "unit": "audio-s/s", "cores": threads, "kind": "reference",
+                "sample": f"{steps} x one utterance (B=1) through the reference's generate() + processor decode at the full shapes",
+                "generate_s": [r[2] for r in runs], "seconds": [r[0] for r in runs], "model_build_s_not_timed": t_build}
+        sample = ("bounded sample: B=1 (one of the 64 utterances of a step), fp32 (the reference's CPU dtype), eager attention; "
+                  "assumed 8B shape with layers 1..35 aliasing layer 0's parameter storage (772 MB per layer, far beyond the LLC), "
+                  "released codec config.json with the reference's own random init")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "audio-s/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": FRAMES / FRAME_RATE / v * 1e3,
+            "steps": steps, "warmup": 1, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "configs[1]: MossTTSDelay batch-64 x 10 s utterances bf16 (greedy, 96-token prompt, 156 steps) "
                                    "+ MOSS-Audio-Tokenizer decode to 24 kHz",
-                       "sample": "bounded sample of that workload on the host cores: B=1 at the full 8B / codec shapes, fp32 "
-                                 "(the reference's CPU dtype), prefill + timed decode steps extrapolated to 156 + codec decode of 10 s",
-                       "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "frames": FRAMES},
+                       "sample": sample, "batch_per_step": 1,
+                       "prompt_len": PROMPT_LEN, "new_tokens": NEW_TOKENS, "frames": FRAMES, "host_threads": threads},
             "cpu_baseline": best,
             "e2e": {"value": v, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
