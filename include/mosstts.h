@@ -74,6 +74,11 @@ int mt_debug_set_attn_cluster(int cs);
  * 148*8 uint64 slots of the device buffer `buf` and records 8 %globaltimer stamps per CTA (scripts/trace_decode.py).
  * NULL switches it off.  Returns the number of slots handed out since the previous call. */
 long long mt_debug_set_trace(void* buf, long long words);
+/* Debug probe for the fp16-operand codec path (layer_gemm_f16): `slots` = MT_CODEC_MAX_STAGES x 4 device floats (zeroed by the
+ * caller).  Every codec pass launched afterwards folds max |value| of each stage's half operands into
+ * slots[stage][0..3] = {LayerNorm output, q|k|v, attention output, GELU output} (NaN if any NaN).  NULL switches it off.
+ * Used by the tests to prove the operands stay inside the fp16 range (65504) through all 68 released layers. */
+int mt_codec_debug_set_absmax(float* slots);
 
 /* ------------------------------------------------------------------------------------------
  * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:

@@ -20,6 +20,10 @@ struct mt_codec {
 
 namespace mt {
 
+// mt_codec_debug_set_absmax: device floats [MT_CODEC_MAX_STAGES][4] = max |value| of the fp16 operands
+// {LayerNorm output, q|k|v, attention output, GELU output} of every stage, over all layers and launches since it was set
+static float* g_absmax = nullptr;
+
 struct StageDims { long long x, qkv, ff, y; };
 
 // per-sample float counts of each activation buffer for T frames
@@ -96,6 +100,7 @@ extern "C" int mt_codec_create(const mt_codec_config* cfg, const mt_codec_weight
   return MT_OK;
 }
 extern "C" int mt_codec_destroy(mt_codec* h) { delete h; return MT_OK; }
+extern "C" int mt_codec_debug_set_absmax(float* slots) { mt::g_absmax = slots; return MT_OK; }
 
 extern "C" int mt_codec_workspace_bytes(const mt_codec* h, int B, int T, long long* bytes) {
   MT_CHECK(h && bytes, "null argument");
@@ -144,10 +149,13 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
   // MT_CODEC_ATTN_TF32=1: keep q/k/v in fp32 and run the TF32 attention kernel inside an fp16-GEMM codec (A/B switch)
   static const bool attn_tf32 = exp_env("MT_CODEC_ATTN_TF32", 0) != 0;
   const bool a16 = h16 && !attn_tf32;
+  float* probe = (g_absmax && h16 && a16) ? g_absmax + 4 * st : nullptr;
   for (int l = 0; l < c.num_layers[st]; ++l) {
     const mt_codec_layer& L = h->layers[st][l];
     MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
+    if (probe) MT_TRY(absmax_f16(hbuf, M * d, probe + 0, s));
     MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32));
+    if (probe) MT_TRY(absmax_f16(qkv, M * 3 * d, probe + 1, s));
     if (ring) {
       // streaming push: the layer's ring cache takes the new keys / values, the new queries attend to the ring
       MT_CHECK(a16, "codec streaming needs layer_gemm_f16 = 1 (half ring caches)");
@@ -163,9 +171,12 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
     } else {
       MT_TRY(codec_attention_tc(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y, h16));
     }
+    if (probe) MT_TRY(absmax_f16(hbuf, M * d, probe + 2, s));
     MT_TRY(codec_linear(hbuf, M, d, L.out_proj, d, x, d, 0, x, L.scale1, s, din));
     MT_TRY(layernorm(x, L.norm2_w, L.norm2_b, hbuf, M, d, s, h16));
+    if (probe) MT_TRY(absmax_f16(hbuf, M * d, probe + 0, s));
     MT_TRY(codec_linear(hbuf, M, d, L.linear1, ffd, ff, ffd, 1, nullptr, nullptr, s, din, din));
+    if (probe) MT_TRY(absmax_f16(ff, M * ffd, probe + 3, s));
     MT_TRY(codec_linear(ff, M, ffd, L.linear2, d, x, d, 0, x, L.scale2, s, din));
   }
   return MT_OK;

@@ -375,6 +375,32 @@ int codec_attention(const float* qkv, float* out, int B, int T, int heads, int h
 }
 
 // ---------------------------------------------------------------------------------------------
+// debug probe (mt_codec_debug_set_absmax): max |x| over an fp16 operand buffer, atomically folded into *slot
+// (non-negative floats order like their bit patterns; a NaN lands above +inf and stays visible)
+// ---------------------------------------------------------------------------------------------
+__global__ void absmax_f16_kernel(const __half2* __restrict__ x, long long n2, unsigned int* __restrict__ slot) {
+  float m = 0.f;
+  bool nan = false;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n2;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float2 v = __half22float2(x[i]);
+    nan |= (v.x != v.x) || (v.y != v.y);
+    m = fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y)));
+  }
+  m = warp_max(m);
+  nan = __any_sync(0xffffffffu, nan);
+  if ((threadIdx.x & 31) == 0) atomicMax(slot, nan ? 0x7fc00000u : __float_as_uint(m));
+}
+int absmax_f16(const void* x, long long n, float* slot, cudaStream_t s) {
+  int blocks = static_cast<int>(cdivll(n / 2, 256 * 8));
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks < 1) blocks = 1;
+  absmax_f16_kernel<<<blocks, 256, 0, s>>>(reinterpret_cast<const __half2*>(x), n / 2, reinterpret_cast<unsigned int*>(slot));
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // patch upsample in token-major form: x'[b, l*h + j, c] = y[b, l, c*h + j]
 // ---------------------------------------------------------------------------------------------
 __global__ void unpatch_kernel(const float* __restrict__ y, float* __restrict__ x, long long tokens, int dh, int h) {

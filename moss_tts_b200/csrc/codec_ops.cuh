@@ -34,6 +34,8 @@ int codec_kv_append_f16(const void* qkv, void* ring, int B, int T, int heads, in
 int codec_attention_ring_f16(const void* qkv, const void* ring, void* out, int B, int T, int heads, int cap, long long pos0,
                              cudaStream_t s, const float* rope_table);
 int unpatch(const float* y, float* x, long long tokens, int dh, int h, cudaStream_t s);
+// debug probe: *slot = max(*slot, max |x[i]|) over n IEEE-half values (n even); NaN if any element is NaN
+int absmax_f16(const void* x, long long n, float* slot, cudaStream_t s);
 // encode side (codec_enc.cu)
 using QuantWeights = mt_codec_quant_weights;
 int patchify(const float* x, float* y, long long tokens_out, int d, int h, cudaStream_t s);

@@ -155,3 +155,49 @@ def test_streaming_pushes_closed_form_matches_reference_streaming():
     wav = oc.decode_frames(codes, chunk_frames=[int(n) for n in g["pushes"]]).numpy()
     assert np.abs(wav - g["wav_stream"]).max() <= 2e-5 * max(1.0, np.abs(g["wav_stream"]).max())
     assert np.abs(g["wav_stream"] - g["wav_full"]).max() > 0.1          # and streaming genuinely differs from one shot
+
+
+# ---- BASELINE shapes (oracle/make_golden_big.py): 8B widths x 2 layers, released 68-layer codec --------------------------
+@pytest.fixture(scope="module")
+def wide_base_weights():
+    from oracle.make_golden_big import wide_cfg, wide_weights
+    return wide_weights(wide_cfg(32))
+
+
+@pytest.mark.parametrize("which,n_vq", [("lm32", 32), ("lm16", 16)])
+def test_oracle_matches_reference_at_8b_widths(wide_base_weights, which, n_vq):
+    """H 4096 / I 12288 / 32q-8kv x 128 / V 151936: greedy ids bit-exact (n_vq 32: ragged left pad; n_vq 16: codes in the
+    prompt, penalty 1.1) and the teacher-forced top-1 logit of every (row, position, head) bit-equal to the reference's."""
+    from oracle.make_golden_big import wide_prompt, wide_weights
+    g = np.load(os.path.join(GOLDEN, f"lm_wide_nvq{n_vq}_bf16.npz"), allow_pickle=False)
+    cfg = LMConfig(**json.loads(str(g["cfg"])))
+    oracle = OracleLM(cfg, wide_weights(cfg, wide_base_weights), torch.bfloat16)
+    ids, mask = wide_prompt(cfg, which)
+    out = oracle.generate(ids, mask, max_new_tokens=int(g["steps"]), text_temperature=0, audio_temperature=0,
+                          audio_repetition_penalty=float(g["penalty"]))
+    for b, (sl, gen) in enumerate(out):
+        assert sl == int(g[f"start_length{b}"])
+        np.testing.assert_array_equal(gen.numpy(), g[f"gen{b}"].astype(np.int64))
+    logits = oracle.forward(torch.from_numpy(g["tf_ids"].astype(np.int64)), torch.from_numpy(g["tf_mask"]))
+    valid = g["tf_mask"].astype(bool)
+    for h, lg in enumerate(logits):
+        lg = lg.float().numpy()
+        for k in range(2):
+            idx = g["tf_top2_i"][:, :, h, k].astype(np.int64)
+            got = np.take_along_axis(lg, idx[..., None], -1)[..., 0]
+            assert np.array_equal(got[valid], g["tf_top2_v"][:, :, h, k][valid]), (which, h, k)
+
+
+def test_oracle_matches_reference_released_codec_68_layers():
+    from oracle.make_golden_big import CODEC_SEED
+    g = np.load(os.path.join(GOLDEN, "codec_full.npz"), allow_pickle=False)
+    cfg = CodecConfig.from_dict(json.loads(str(g["cfg"])))
+    assert sum(st.num_layers for st in cfg.stages) == 68
+    oc = OracleCodec(cfg, make_codec_weights(cfg, seed=CODEC_SEED, layer_scale=float(g["layer_scale"])))
+    codes = torch.from_numpy(g["codes"].astype(np.int64))
+    for key, kw in (("wav", {}), ("wav_chunked", {"chunk_duration": 8})):
+        wav, _ = oc.decode(codes, **kw)
+        ref = g[key]
+        assert wav.shape == ref.shape
+        assert float(np.abs(wav.numpy() - ref).max()) <= 2e-4 * float(np.abs(ref).max())
+    assert float(np.abs(g["wav"] - g["wav_chunked"]).max()) > 1e-2          # the chunked path genuinely differs
