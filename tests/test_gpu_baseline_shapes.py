@@ -62,7 +62,7 @@ def test_wide_lm_matches_reference(base_weights, which, n_vq):
     logits = [lg.float().cpu() for lg in model.forward(tf_ids, tf_mask).logits]
     valid = tf_mask.numpy().astype(bool)
     top2_v, top2_i = g["tf_top2_v"], g["tf_top2_i"]
-    n_cells = n_flip = n_tie = 0
+    n_cells = n_flip = n_flip2 = n_tie = 0
     worst_top = 0.0
     for h, lg in enumerate(logits):
         mine_arg = lg.argmax(-1).numpy()
@@ -79,13 +79,15 @@ def test_wide_lm_matches_reference(base_weights, which, n_vq):
                 # torch.topk's order among equals is unspecified): either index is the reference's answer
                 n_tie += 1
                 continue
-            # otherwise allowed only where the REFERENCE's own top-2 margin is <= 1 bf16 ulp
+            # otherwise allowed only where the REFERENCE's own top-2 margin is <= 2 bf16 ulp: every logit is within one ulp of
+            # the reference (asserted below over all logits), so the winner can lose one ulp while the runner-up gains one
             ulps = (v1[b, t] - v2[b, t]) / bf16_ulp(v1[b, t])
-            assert ulps <= 1.0, f"{which}: head {h} row {b} pos {t}: argmax {mine_arg[b, t]} != reference {ref1[b, t]} at margin {ulps:.1f} ulp"
+            assert ulps <= 2.0, f"{which}: head {h} row {b} pos {t}: argmax {mine_arg[b, t]} != reference {ref1[b, t]} at margin {ulps:.1f} ulp"
             n_flip += 1
+            n_flip2 += ulps > 1.0
     print(f"[{which}] teacher-forced argmax over {n_cells} (row, position, head) cells: {n_flip} near-tie flips "
-          f"(reference margin <= 1 ulp), {n_tie} exact ties of the reference, 0 real mismatches; "
-          f"max |logit diff| at the reference's top-2: {worst_top:.4g}")
+          f"({n_flip - n_flip2} at a reference margin <= 1 ulp, {n_flip2} at 2 ulp), {n_tie} exact ties of the reference, "
+          f"0 real mismatches; max |logit diff| at the reference's top-2: {worst_top:.4g}")
     assert worst_top <= LOGIT_TOL
     # all audio logits at four positions (raw bf16 bits of the reference) + -inf pattern
     pos = g["tf_positions"].tolist()

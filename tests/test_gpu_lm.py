@@ -105,7 +105,7 @@ def test_teacher_forced_logits(name):
 def test_teacher_forced_argmax_along_reference_trajectory(name):
     """Every step of the reference's golden trajectory, every channel (no "first divergence, then stop"): the CUDA path,
     teacher-forced on the reference's ids, must pick the token the reference picked at every (row, step, channel); a
-    different argmax is accepted only where the reference arithmetic's own top-2 margin is <= 1 bf16 ulp (the oracle,
+    different argmax is accepted only where the reference arithmetic's own top-2 margin is <= 2 bf16 ulp (the oracle,
     bit-exact to the reference on these goldens, supplies the full logit rows).  Counts are printed."""
     g, cfg = _golden(name)
     w = make_lm_weights(cfg, seed=int(g["seed"]), never_stop=bool(g["never_stop"]))
@@ -117,7 +117,7 @@ def test_teacher_forced_argmax_along_reference_trajectory(name):
     mine = [x.float().cpu() for x in model.forward(ids, mask).logits]
     ref = [x.float() for x in OracleLM(cfg, w, torch.bfloat16).forward(ids, mask)]
     valid = mask.bool()
-    cells = flips = ties = 0
+    cells = flips = flips2 = ties = 0
     for h in range(C):
         am, ar = mine[h].argmax(-1), ref[h].argmax(-1)
         top2 = torch.topk(ref[h], 2, dim=-1).values
@@ -127,9 +127,12 @@ def test_teacher_forced_argmax_along_reference_trajectory(name):
             if margin == 0.0:
                 ties += 1
                 continue
+            # every logit is within one bf16 ulp of the oracle (test_teacher_forced_logits), so a winner can lose one ulp
+            # while the runner-up gains one: margins up to 2 ulp can flip, anything larger is a real mismatch
             ulps = margin / bf16_ulp(float(top2[b, t, 0]))
-            assert ulps <= 1.0, f"{name}: head {h} row {b} pos {t}: argmax differs at a {ulps:.1f}-ulp margin"
+            assert ulps <= 2.0, f"{name}: head {h} row {b} pos {t}: argmax differs at a {ulps:.1f}-ulp margin"
             flips += 1
+            flips2 += ulps > 1.0
     # the tokens the reference actually generated (audio channels, rows where the channel was live)
     gen_cells = gen_flips = 0
     for b in range(B):
@@ -146,7 +149,7 @@ def test_teacher_forced_argmax_along_reference_trajectory(name):
                     ulps = float(row.max() - row[tok]) / bf16_ulp(float(row.max()))
                     assert ulps <= 2.0, f"{name}: generated token of row {b} step {r} ch {c} is {ulps:.1f} ulp below our argmax"
                     gen_flips += 1
-    print(f"[{name}] teacher-forced argmax over {cells} cells (all {T - S0 + 1} steps): {flips} near-tie flips, {ties} exact ties, "
+    print(f"[{name}] teacher-forced argmax over {cells} cells (all {T - S0 + 1} steps): {flips} near-tie flips ({flips2} at a 2-ulp margin), {ties} exact ties, "
           f"0 real mismatches; {gen_cells} generated audio tokens re-scored: {gen_flips} near-tie flips")
     assert gen_cells > 0
 
