@@ -107,6 +107,20 @@ typedef struct {
 } mt_gemm_args;
 int mt_gemm(const mt_gemm_args* a, mt_stream s);
 
+/* mt_gemm for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arithmetic, kernels and result as mt_gemm called with a workspace of MT_GEMM_STATIC_SCRATCH_BYTES, but the split-K
+ * scratch (fp32 partial slabs) is a file-scope `static __device__` array inside the library (csrc/gemm_static.cu) that every
+ * GPU loading the library holds until the process exits; this entry point calls no cudaMalloc / cudaFree / allocating routine.
+ *   - a->workspace and a->out_splits must be NULL; `out` always receives the finished tensor.
+ *   - limits: M <= 256 (only the decode-orientation GEMM uses scratch) and 2 * M * N * 4 <= MT_GEMM_STATIC_SCRATCH_BYTES
+ *     (room for a two-way split); anything larger returns MT_ERR_ARG with a message naming the limit: use mt_gemm.
+ *   - every call on a device shares the one array, which keeps the previous call's contents; nothing needs clearing
+ *     (each partial is written before it is read within a call).  Calls that OVERLAP on the GPU (other streams,
+ *     concurrently replayed graphs) RACE on it: serialise them on one stream or with events. */
+#define MT_GEMM_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+int mt_gemm_static_scratch(const mt_gemm_args* a, mt_stream s);
+
 /* ------------------------------------------------------------------------------------------
  * MossTTSDelay language model
  * ------------------------------------------------------------------------------------------ */

@@ -17,9 +17,10 @@ MT_OK, MT_ERR_ARG, MT_ERR_CUDA, MT_ERR_UNSUPPORTED = 0, -1, -2, -3
 MT_DTYPE_BF16, MT_DTYPE_F32, MT_DTYPE_F16 = 0, 1, 2
 MT_GEMM_AUTO, MT_GEMM_SIMT, MT_GEMM_W_STATIC, MT_GEMM_W_TILED = 0, 1, 2, 4
 MT_CODEC_MAX_STAGES = 8
+MT_GEMM_STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 EXPORTS = [
-    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_debug_set_attn_cluster", "mt_debug_set_trace", "mt_codec_debug_set_absmax", "mt_gemm",
+    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_debug_set_attn_cluster", "mt_debug_set_trace", "mt_codec_debug_set_absmax", "mt_gemm", "mt_gemm_static_scratch",
     "mt_lm_query_sizes", "mt_lm_create", "mt_lm_destroy", "mt_lm_forward", "mt_lm_generate",
     "mt_lm_stream_begin", "mt_lm_stream_steps", "mt_lm_stream_end", "mt_stream_gather_frames", "mt_crossfade",
     "mt_sample_tokens", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
