@@ -171,6 +171,10 @@ int mt_lm_destroy(mt_lm* h);
 int mt_lm_forward(mt_lm* h, const int64_t* ids, const uint8_t* attn_mask, long long mask_ld,
                   int B, int T, int past_len, int last_only,
                   void* text_logits, void* audio_logits, mt_stream s);
+/* MossTTSDelayModel.get_input_embeddings (modeling_moss_tts.py:196-213): out [n_tokens, H] bf16 =
+ * E_text[ids[t,0]] + sum_i emb_ext[i][ids[t,1+i]], added left to right with a bf16 rounding after every add.
+ * ids [n_tokens, 1+n_vq] int64 (device).  Does not touch the KV cache or the workspace. */
+int mt_lm_embed(mt_lm* h, const int64_t* ids, long long n_tokens, void* out, mt_stream s);
 
 /* generate() (modeling_moss_tts.py:392-525). */
 typedef struct {

@@ -236,6 +236,15 @@ extern "C" int mt_lm_forward(mt_lm* h, const int64_t* ids, const uint8_t* attn_m
                          reinterpret_cast<cudaStream_t>(s));
 }
 
+extern "C" int mt_lm_embed(mt_lm* h, const int64_t* ids, long long n_tokens, void* out, mt_stream s) {
+  MT_CHECK(h && ids && out, "mt_lm_embed: null argument");
+  MT_CHECK(n_tokens > 0 && n_tokens < (1ll << 31), "mt_lm_embed: bad token count %lld", n_tokens);
+  const mt_lm_config& c = h->cfg;
+  return embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
+                   reinterpret_cast<bf16*>(out), static_cast<int>(n_tokens), c.hidden_size, c.n_vq, c.audio_head_size, c.vocab_size,
+                   reinterpret_cast<cudaStream_t>(s), 1 + c.n_vq);
+}
+
 static TokenIds token_ids(const mt_lm_config& c) {
   TokenIds t;
   t.pad = c.pad_token_id; t.im_start = c.im_start_token_id; t.im_end = c.im_end_token_id;

@@ -195,8 +195,22 @@ class MossTTSDelayModel:
             pass
 
     # ---- reference surface ----------------------------------------------------------------------
+    @torch.inference_mode()
     def get_input_embeddings(self, input_ids: torch.Tensor) -> torch.Tensor:
-        raise NotImplementedError("the summed codebook embedding is fused into forward(); not exposed separately")
+        """[B, T, 1+n_vq] ids -> [B, T, H] bf16 summed codebook embedding (reference :196-213; embed_sum_kernel)."""
+        c = self.config
+        if input_ids.dim() != 3 or input_ids.shape[-1] != c.n_vq + 1:
+            raise ValueError("`Input_ids`'s shape should be exactly (batch_size, sequence_length, 1 + n_vq).")
+        B, T, _ = input_ids.shape
+        ids = input_ids.to(device=self.device, dtype=torch.int64).contiguous()
+        out = torch.empty(B, T, c.hidden_size, dtype=torch.bfloat16, device=self.device)
+        if B * T == 0:
+            return out
+        self._ensure_engine(1, 1, 1)
+        with torch.cuda.device(self.device):
+            L.check(L.lib().mt_lm_embed(self._engine, L.ptr(ids), C.c_longlong(B * T), L.ptr(out), L.stream_ptr(self.device)),
+                    "mt_lm_embed")
+        return out
 
     @torch.inference_mode()
     def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, **unused):

@@ -15,7 +15,6 @@ Two pieces, both on the native path (libmosstts_sm100.so; no CPU fallback):
 from __future__ import annotations
 
 import ctypes as C
-from bisect import bisect_left
 from typing import Iterable, Iterator, List, Optional, Tuple
 
 import numpy as np
@@ -118,25 +117,40 @@ class AudioStreamDecoder:
         return merged
 
 
-def scan_text_tokens(new_tokens: np.ndarray, first_row: int, frame_rows: List[List[int]], finished: List[bool],
-                     gen_slot_id: int, im_end_id: int) -> None:
-    """Book-keeping of one consumed slice: `new_tokens` [B, n] are the text-channel tokens of generated rows
-    [first_row, first_row + n).  Every gen-slot row opens a frame (its n_vq codes sit on the delay diagonal below it,
-    processing_moss_tts.py:528-537); a row that has emitted <|im_end|> will produce no more frames."""
+def scan_frames(codes: np.ndarray, next_row: List[int], n_rows: int, frame_rows: List[List[int]], pad_code: int) -> None:
+    """Frames exactly as the processor defines them (processing_moss_tts.py:668-685): a frame is a de-delayed row
+    `[codes[r + q, q] for q < n_vq]` that is NOT all pad; all-pad rows separate audio spans.  `codes` [B, >= n_rows, n_vq]
+    holds the audio channels of every row known so far (prompt + generated, absolute row index), `next_row[b]` the first
+    opening row not yet judged.  A row r can be judged once row r + n_vq - 1 exists; the opening rows of the frames
+    found are appended to frame_rows[b] (ascending).  This covers what a gen-slot-only rule misses: the FIRST delay-slot
+    row of a generated span still has every channel sampled (modeling_moss_tts.py:475-481 builds the mask from the
+    pre-update delayed_lengths) and is a complete frame, and frames opened in the prompt whose diagonal reaches into the
+    generated rows."""
+    n_vq = codes.shape[2]
+    q = np.arange(n_vq)
+    for b in range(codes.shape[0]):
+        hi = n_rows - n_vq + 1
+        if hi <= next_row[b]:
+            continue
+        cand = np.arange(next_row[b], hi)
+        diag = codes[b, cand[:, None] + q[None, :], q[None, :]]
+        frame_rows[b].extend(int(r) for r in cand[(diag != pad_code).any(axis=1)])
+        next_row[b] = hi
+
+
+def scan_finished(new_tokens: np.ndarray, finished: List[bool], im_end_id: int) -> None:
+    """A row that has emitted <|im_end|> produces no more frames (it is fed pad codes from then on)."""
     for b in range(new_tokens.shape[0]):
-        for j in np.nonzero(new_tokens[b] == gen_slot_id)[0]:
-            frame_rows[b].append(first_row + int(j))
         if (new_tokens[b] == im_end_id).any():
             finished[b] = True
 
 
-def plan_push(frame_rows: List[List[int]], finished: List[bool], scanned: int, pushed: int, n_vq: int, chunk_frames: int,
+def plan_push(frame_rows: List[List[int]], finished: List[bool], pushed: int, chunk_frames: int,
               max_push: int) -> Optional[Tuple[int, List[int]]]:
-    """Next lockstep push, or None.  A frame opened at generated row r is complete once row r + n_vq - 1 exists
-    (`scanned` rows exist).  Unfinished rows must all have `chunk_frames` complete frames beyond the `pushed` already
-    sent; once every row has finished, whatever is left goes out.  Returns (T, frames of each row inside the push)."""
-    # frame_rows[b] is ascending: frames with r + n_vq - 1 < scanned are a prefix (O(log n) per row, long generations)
-    avail = [bisect_left(fr, scanned - n_vq + 1) - pushed for fr in frame_rows]
+    """Next lockstep push, or None.  frame_rows holds complete frames only (scan_frames).  Unfinished rows must all have
+    `chunk_frames` frames beyond the `pushed` already sent; once every row has finished, whatever is left goes out.
+    Returns (T, frames of each row inside the push)."""
+    avail = [len(fr) - pushed for fr in frame_rows]
     live = [a for a, f in zip(avail, finished) if not f]
     T = min(live) if live else max(avail + [0])
     if T <= 0 or (live and T < chunk_frames):
@@ -157,6 +171,11 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
 
     Yields ``(wav [B, T * downsample_rate] float32 on the device, valid_samples [B])`` per chunk: the next T frames of
     every row (rows that have already finished are padded, ``valid_samples[b]`` says how much of the chunk is row b's).
+    The frames of a row are exactly the ones ``processor.decode`` decodes for it: the de-delayed rows of the returned
+    ids that are not all pad (every audio span in order, including the frame on the first delay-slot row of a span and
+    frames of the returned prompt rows), so the streamed samples of a row total the samples of its decoded segments
+    BEFORE the processor's ``start_length`` waveform trim (processing_moss_tts.py:692-707 needs the finished first
+    segment's length, which a stream does not have; it is not applied here).
     A frame is pushed once all of its n_vq delayed codes exist, rows advance in lockstep, and a chunk leaves as soon
     as ``chunk_frames`` frames are final for every unfinished row (everything left at the end);
     ``first_chunk_frames`` (< ``chunk_frames``) lets the very first chunk leave earlier - short time to first audio with
@@ -184,6 +203,9 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
     starts = torch.empty(B, dtype=torch.int64, device=dev)
     status_dev = torch.zeros(2, 2, dtype=torch.int32, device=dev)
     text_host = torch.empty(B, max_new_tokens, dtype=torch.int64).pin_memory()
+    codes_host = torch.empty(B, max_len, nvq, dtype=torch.int16).pin_memory()      # audio channels of every row, for scan_frames
+    codes_host[:, :S0].copy_(ids[:, :, 1:].to(torch.int16))
+    starts_host = torch.zeros(B, dtype=torch.int64).pin_memory()
     status_host = torch.zeros(2, dtype=torch.int32).pin_memory()
     gp = L.GenParamsC(max_new_tokens, float(text_temperature), float(text_top_p), int(text_top_k or 0),
                       float(audio_temperature), float(audio_top_p), int(audio_top_k or 0),
@@ -195,7 +217,8 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
     slice_steps = int(lm_slice or first_chunk)
     max_push = max(chunk_frames, int(round(codec.causal_transformer_context_duration * codec.sampling_rate))
                    // codec.downsample_rate)
-    frame_rows: List[List[int]] = [[] for _ in range(B)]
+    frame_rows: List[List[int]] = [[] for _ in range(B)]      # absolute opening rows of the complete frames of each row
+    next_row: Optional[List[int]] = None                      # first row not yet judged (starts at the returned slice)
     finished = [False] * B
     scanned = pushed = n_slices = 0
     launched = C.c_int(1)
@@ -232,12 +255,18 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                     status_host.copy_(status_dev[slot], non_blocking=True)
                     side.synchronize()
                     steps_exec, done = int(status_host[0]), int(status_host[1])
+                    if next_row is None:          # time_step 0 has run: gen_init's start indices are final
+                        starts_host.copy_(starts, non_blocking=True)
+                        side.synchronize()
+                        next_row = [int(v) for v in starts_host]
                     if steps_exec > scanned:
                         text_host[:, scanned:steps_exec].copy_(gen[:, S0 + scanned:S0 + steps_exec, 0], non_blocking=True)
+                        codes_host[:, S0 + scanned:S0 + steps_exec].copy_(
+                            gen[:, S0 + scanned:S0 + steps_exec, 1:].to(torch.int16), non_blocking=True)
                         side.synchronize()
-                        scan_text_tokens(text_host[:, scanned:steps_exec].numpy(), scanned, frame_rows, finished,
-                                         c.audio_assistant_gen_slot_token_id, c.im_end_token_id)
+                        scan_finished(text_host[:, scanned:steps_exec].numpy(), finished, c.im_end_token_id)
                         scanned = steps_exec
+                        scan_frames(codes_host.numpy(), next_row, S0 + scanned, frame_rows, c.audio_pad_code)
                     if done:
                         all_done = True
                         pending.clear()           # slices queued behind an all-stopped state change nothing
@@ -246,7 +275,7 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                         finished = [True] * B
                     while True:
                         first = pushed == 0 and first_chunk < chunk_frames
-                        plan = plan_push(frame_rows, finished, scanned, pushed, nvq, first_chunk if first else chunk_frames,
+                        plan = plan_push(frame_rows, finished, pushed, first_chunk if first else chunk_frames,
                                          first_chunk if first else max_push)
                         if plan is None:
                             break
@@ -258,7 +287,7 @@ def generate_stream(model, codec, input_ids: torch.Tensor, attention_mask: Optio
                                 rows[b, :n] = torch.tensor(frame_rows[b][pushed:pushed + n], dtype=torch.int32)
                         rows_dev = rows.to(dev)
                         codes = torch.empty(nvq, B, T, dtype=torch.int64, device=dev)
-                        L.check(lib.mt_stream_gather_frames(L.ptr(gen), B, max_len, Cc, S0, L.ptr(rows_dev), T, L.ptr(codes),
+                        L.check(lib.mt_stream_gather_frames(L.ptr(gen), B, max_len, Cc, 0, L.ptr(rows_dev), T, L.ptr(codes),
                                                             C.c_void_p(side.cuda_stream)), "mt_stream_gather_frames")
                         chunks.append((codec._decode_frame(codes).audio[:, 0], valid))
                         pushed += T

@@ -166,6 +166,25 @@ def golden_sampling():
     print("sampling ok")
 
 
+def golden_sampling3d():
+    """sample_token on [B, H, V] logits with per-head repetition penalty (inference_utils.py:88-106, "case 2")."""
+    sys.path.insert(0, REF)
+    from moss_tts_delay import inference_utils as R
+    g = _gen(9, "sampling3d")
+    rec = {"versions": _versions()}
+    x = (torch.randn(3, 4, 1025, generator=g) * 2.0).to(torch.bfloat16)
+    prev = torch.randint(0, 1025, (3, 40, 4), generator=g)
+    prev[:, :, 2] = torch.randint(0, 64, (3, 40), generator=g)          # head 2 has a small id set: differs from the union
+    rec["logits"] = x.float().numpy()
+    rec["prev"] = prev.numpy()
+    rec["penalized"] = R.apply_repetition_penalty_delay_pattern(x.clone(), prev, 1.3).float().numpy()
+    rec["argmax"] = R.sample_token(x.clone(), prev_tokens=prev, repetition_penalty=1.3, do_sample=False).numpy()
+    rec["argmax_union"] = R.sample_token(x.clone().view(12, 1025), prev_tokens=prev, repetition_penalty=1.3, do_sample=False).numpy()
+    np.savez_compressed(os.path.join(OUT, "sampling3d.npz"), **rec)
+    print("sampling3d ok; rows where per-head and union penalties pick different tokens:",
+          int((rec["argmax"].reshape(-1) != rec["argmax_union"]).sum()))
+
+
 def golden_codec():
     cfg = CodecConfig.mini()
     w = make_codec_weights(cfg, seed=3)
@@ -228,6 +247,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     golden_sampling()
+    golden_sampling3d()
     golden_codec()
     tiny = LMConfig.tiny(n_vq=4)
     golden_lm("lm_tiny_f32", tiny, torch.float32, batch=2, prompt_len=12, left_pad=[0, 3], steps=16,

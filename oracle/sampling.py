@@ -44,6 +44,18 @@ def apply_penalty_row(row: torch.Tensor, ids: Iterable[int], penalty: float) -> 
     return row
 
 
+def apply_penalty_heads(logits: torch.Tensor, prev_tokens: torch.Tensor, penalty: float) -> torch.Tensor:
+    """"Case 2" of the reference (:88-106): logits [B, H, V], prev_tokens [B, T, H] or [B, H]; head h is penalised on the
+    unique ids of prev_tokens[..., h] only (union over the batch and time), on every batch row of that head."""
+    out = logits.clone()
+    B, H, _ = logits.shape
+    for h in range(H):
+        ids = penalty_set(prev_tokens[..., h])
+        for b in range(B):
+            out[b, h] = apply_penalty_row(out[b, h], ids, penalty)
+    return out
+
+
 def topk_survivors(row: torch.Tensor, k: int):
     """Indices of the k largest logits, ordered (value desc, index asc)."""
     V = row.numel()

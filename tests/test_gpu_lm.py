@@ -212,6 +212,22 @@ def test_generate_sampling_without_audio_top_k_follows_oracle():
         model.generate(ids, mask, max_new_tokens=4, text_temperature=1.0, text_top_k=None)     # full-vocabulary sort: not built
 
 
+def test_get_input_embeddings_bit_exact():
+    """a1: E_text[id0] + sum_i emb_ext[i][id_{i+1}], left to right, bf16 rounding after each add (reference :196-213)."""
+    cfg = LMConfig.mid(n_vq=32)
+    w = make_lm_weights(cfg, seed=3)
+    model = MossTTSDelayModel(cfg, w, device=DEV)
+    g = torch.Generator().manual_seed(2)
+    ids = torch.cat([torch.randint(0, cfg.vocab_size, (3, 17, 1), generator=g),
+                     torch.randint(0, cfg.audio_head_size, (3, 17, cfg.n_vq), generator=g)], dim=-1)
+    got = model.get_input_embeddings(ids).cpu()
+    ref = OracleLM(cfg, w, torch.bfloat16).embed(ids)
+    assert got.dtype == torch.bfloat16 and tuple(got.shape) == (3, 17, cfg.hidden_size)
+    assert torch.equal(got, ref)
+    with pytest.raises(ValueError):
+        model.get_input_embeddings(ids[..., :5])
+
+
 def test_forward_rejects_bad_shape():
     cfg = LMConfig.tiny(n_vq=4)
     model = MossTTSDelayModel(cfg, make_lm_weights(cfg, seed=1), device=DEV)

@@ -179,3 +179,27 @@ def test_rows_with_nan_and_inf_do_not_hang():
     assert int(g2[1]) == 0 and int(g2[2]) == 100
     for r in range(3, 8):
         assert int(g2[r]) == S.sample_row(x[r], do_sample=False)
+
+
+def test_penalty_per_head_on_3d_logits_matches_reference():
+    """sample_token on [B, H, V] logits: per-head id sets (reference inference_utils.py:88-106), checked against the
+    reference-executed golden; greedy and sampled (same uniforms -> the oracle's draw on the per-head penalised rows)."""
+    import os
+    from conftest import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "sampling3d.npz"), allow_pickle=False)
+    x = torch.from_numpy(g["logits"]).to(torch.bfloat16)
+    prev = torch.from_numpy(g["prev"])
+    got = sample_token(x.to(DEV), prev_tokens=prev.to(DEV), repetition_penalty=1.3, do_sample=False).cpu()
+    np.testing.assert_array_equal(got.numpy(), g["argmax"])
+    assert tuple(got.shape) == (3, 4) and (got.numpy().reshape(-1) != g["argmax_union"]).any()
+    u = torch.rand(3, 4, generator=torch.Generator().manual_seed(1))
+    got = sample_token(x.to(DEV), prev_tokens=prev.to(DEV), repetition_penalty=1.3, top_k=25, top_p=0.8, do_sample=True,
+                       uniforms=u.to(DEV)).cpu()
+    pen = S.apply_penalty_heads(x, prev, 1.3)
+    want = [[S.sample_row(pen[b, h], top_k=25, top_p=0.8, do_sample=True, u=float(u[b, h])) for h in range(4)] for b in range(3)]
+    assert (got.numpy() == np.asarray(want)).mean() >= 0.9
+    # top_k=None on a row of at most 1024 entries = no filter
+    y = x[:, :, :1024].contiguous()
+    got = sample_token(y.to(DEV), top_k=None, top_p=0.9, do_sample=True, uniforms=u.to(DEV)).cpu()
+    want = [[S.sample_row(y[b, h], top_k=None, top_p=0.9, do_sample=True, u=float(u[b, h])) for h in range(4)] for b in range(3)]
+    assert (got.numpy() == np.asarray(want)).mean() >= 0.9

@@ -16,7 +16,7 @@ from moss_tts_b200.config import CodecConfig, LMConfig
 from moss_tts_b200.modeling_moss_audio_tokenizer import MossAudioTokenizerModel
 from moss_tts_b200.modeling_moss_tts import MossTTSDelayModel
 from moss_tts_b200.streaming import AudioStreamDecoder, generate_stream
-from oracle.codec import OracleCodec, apply_de_delay_pattern
+from oracle.codec import OracleCodec, apply_de_delay_pattern, split_audio_segments
 from oracle.weights import make_codec_weights, make_lm_weights, make_prompt
 from gpu_util import DEV, snr_db
 
@@ -85,18 +85,13 @@ def _stream_case(codec, never_stop, B, steps, chunk_frames, sample, left_pad=Non
     out = lm.last_stream_output
     for (a, x), (b_, y) in zip(ref, out):                   # the sliced loop is the same loop
         assert a == b_ and torch.equal(x, y)
-    # frames of every row from the finished ids: gen-slot rows open a frame, its n_vq codes sit on the delay diagonal
+    # frames of every row from the finished ids, the way processor.decode finds them (processing_moss_tts.py:668-685):
+    # de-delay the returned ids, every row that is not all pad is a frame, runs of them are the audio segments
     nq, ds = cfg.n_vq, cmodel.downsample_rate
     frames = []
     for sl, x in out:
-        x = x.cpu().numpy()
-        gen = x[sl:]
-        rows = np.nonzero(gen[:, 0] == cfg.audio_assistant_gen_slot_token_id)[0]
-        rows = rows[rows + nq - 1 < gen.shape[0]]
-        frames.append(np.stack([gen[rows + q, 1 + q] for q in range(nq)], 1) if len(rows) else np.zeros((0, nq), np.int64))
-        if len(rows) and (np.diff(rows) == 1).all():        # one contiguous span: the processor's de-delay agrees
-            dd = apply_de_delay_pattern(gen[rows[0]: rows[-1] + nq, 1:])
-            np.testing.assert_array_equal(dd, frames[-1])
+        segs = split_audio_segments(apply_de_delay_pattern(x.cpu().numpy()[:, 1:]), cfg.audio_pad_code) if x.shape[0] >= nq else []
+        frames.append(np.concatenate(segs, 0) if segs else np.zeros((0, nq), np.int64))
     pushes = [w_.shape[1] // ds for w_, _ in chunks]
     total = [sum(v[b] for _, v in chunks) // ds for b in range(B)]
     assert total == [len(f) for f in frames]
@@ -150,6 +145,35 @@ def test_generate_stream_small_first_chunk(codec):
 def test_generate_stream_rows_that_stop(codec):
     chunks, frames = _stream_case(codec, False, 4, 60, 2, True, left_pad=[0, 1, 0, 3])
     print("[generate_stream, stopping rows] frames per row", [len(f) for f in frames], "chunks", len(chunks))
+
+
+def test_generate_stream_total_samples_equal_processor_decode(codec):
+    """Rows whose audio span ends naturally (ramp-down, audio_end): the frame on the first delay-slot row is streamed too, so
+    every row's streamed samples total the samples of the segments processor.decode(generate()) decodes (before its
+    start_length waveform trim).  The audio itself is checked inside _stream_case (bit-exact vs the codec's streaming decode
+    of those frames with the same pushes, SNR vs the oracle)."""
+    ccfg, cmodel, _ = codec
+    cfg = LMConfig.tiny(n_vq=ccfg.num_quantizers)
+    ds = cmodel.downsample_rate
+    natural_ends = 0
+    for seed in (5, 6, 9, 12):
+        lm = MossTTSDelayModel(cfg, make_lm_weights(cfg, seed=seed, never_stop=False), device=DEV)
+        ids, mask = make_prompt(cfg, 3, 12, seed=seed, left_pad=[0, 2, 1])
+        kw = dict(max_new_tokens=70, audio_repetition_penalty=1.0, seed=seed, text_temperature=1.0, text_top_k=50)
+        chunks = list(generate_stream(lm, cmodel, ids, mask, chunk_frames=3, **kw))
+        for b, (sl, x) in enumerate(lm.last_stream_output):
+            xs = x.cpu().numpy()
+            segs = split_audio_segments(apply_de_delay_pattern(xs[:, 1:]), cfg.audio_pad_code) if xs.shape[0] >= cfg.n_vq else []
+            want = sum(s_.shape[0] for s_ in segs) * ds
+            got = sum(v[b] for _, v in chunks)
+            assert got == want, (seed, b, got, want)
+            ends = np.nonzero(xs[:, 0] == cfg.audio_end_token_id)[0]
+            natural_ends += len(ends)
+            for e in ends:                   # the n_vq rows before audio_end are delay slots; the first of them is a frame
+                assert e >= cfg.n_vq and (xs[e - cfg.n_vq: e, 0] == cfg.audio_assistant_delay_slot_token_id).all()
+                assert (xs[e - cfg.n_vq, 1:] != cfg.audio_pad_code).any()
+    print(f"[generate_stream] audio spans that ended naturally: {natural_ends}")
+    assert natural_ends > 0, "no row ended its audio span naturally: the case under test did not occur"
 
 
 def test_open_session_owns_the_engine(codec):

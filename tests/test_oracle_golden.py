@@ -201,3 +201,14 @@ def test_oracle_matches_reference_released_codec_68_layers():
         assert wav.shape == ref.shape
         assert float(np.abs(wav.numpy() - ref).max()) <= 2e-4 * float(np.abs(ref).max())
     assert float(np.abs(g["wav"] - g["wav_chunked"]).max()) > 1e-2          # the chunked path genuinely differs
+
+
+def test_penalty_per_head_on_3d_logits_matches_reference():
+    """[B, H, V] logits: head h is penalised with the ids of prev_tokens[..., h] only (reference "case 2")."""
+    g = np.load(os.path.join(GOLDEN, "sampling3d.npz"), allow_pickle=False)
+    x = torch.from_numpy(g["logits"]).to(torch.bfloat16)
+    prev = torch.from_numpy(g["prev"])
+    pen = S.apply_penalty_heads(x, prev, 1.3)
+    np.testing.assert_array_equal(pen.float().numpy(), g["penalized"])
+    np.testing.assert_array_equal(pen.float().argmax(-1).numpy(), g["argmax"])
+    assert (g["argmax"].reshape(-1) != g["argmax_union"]).any()          # the fixture separates the two cases

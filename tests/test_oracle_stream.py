@@ -87,50 +87,69 @@ def test_product_stream_decoder_host_logic_on_cpu():
 
 
 def test_stream_planner_against_the_oracle_dedelay():
-    """Host logic of generate_stream on CPU: feed the planner the text channel of a synthetic generation slice by slice;
-    the frames it schedules, read off the delay diagonal, must be the oracle's de-delay of every row's audio span, each
-    frame exactly once and only after its last code exists."""
-    from moss_tts_b200.streaming import plan_push, scan_text_tokens
-    from oracle.codec import apply_de_delay_pattern
+    """Host logic of generate_stream on CPU: feed the planner a synthetic generation slice by slice, laid out the way the
+    reference's loop lays it out (SURVEY.md 8c KAT: k gen-slot rows, then n_vq delay-slot rows of which the FIRST still
+    carries every channel, then audio_end), with a prompt that already holds a few frames.  The frames it schedules must be
+    the ones processor.decode finds -- the non-pad rows of the oracle's de-delay of the returned rows -- each exactly once,
+    in order, and only after its last code exists."""
+    from moss_tts_b200.streaming import plan_push, scan_finished, scan_frames
+    from oracle.codec import apply_de_delay_pattern, split_audio_segments
     rng = np.random.default_rng(3)
-    GEN, DELAY, END, IM_END, PAD, nq = 7, 8, 9, 10, 0, 4
-    B, steps = 3, 40
-    n_frames = [17, 5, 30]                       # row 2 is cut by max_new_tokens before its span ends
-    lead = [1, 3, 0]                             # text tokens before the first gen slot
-    gen = np.full((B, steps, 1 + nq), 1024, dtype=np.int64)
-    for b in range(B):
-        seq = [PAD + 1] * lead[b] + [GEN] * n_frames[b] + [DELAY] * (nq - 1) + [END, IM_END]
-        seq = (seq + [PAD] * steps)[:steps]
-        gen[b, :, 0] = seq
-        for f in range(n_frames[b]):
+    GEN, DELAY, END, IM_END, TXT, P, nq = 7, 8, 9, 10, 1, 1024, 4
+    B, S0, steps = 3, 9, 40
+    start = [2, 0, 5]                            # first returned row (im_start + 3)
+    prompt_frames = [3, 0, 0]                    # row 0: the prompt ends inside an audio span (continuation)
+    n_gen = [16, 5, 40]                          # gen-slot rows generated; row 2 is cut by max_new_tokens before its span ends
+    lead = [0, 3, 0]                             # free text rows before the generated span
+    ids = np.full((B, S0 + steps, 1 + nq), P, dtype=np.int64)
+    ids[:, :, 0] = TXT
+
+    def put_span(b, row0, k, delay_rows):        # k gen-slot rows from row0, then delay-slot rows; codes on the diagonals
+        n_fr = k + (1 if delay_rows else 0)      # the first delay-slot row is a frame as well
+        for f in range(n_fr):
             for q in range(nq):
-                if lead[b] + f + q < steps:
-                    gen[b, lead[b] + f + q, 1 + q] = rng.integers(0, 1024)
-    frame_rows, finished = [[] for _ in range(B)], [False] * B
+                if row0 + f + q < ids.shape[1]:
+                    ids[b, row0 + f + q, 1 + q] = rng.integers(0, 1024)
+        for r in range(row0, min(row0 + k, ids.shape[1])):
+            ids[b, r, 0] = GEN
+        for r in range(row0 + k, min(row0 + k + delay_rows, ids.shape[1])):
+            ids[b, r, 0] = DELAY
+        return row0 + k + delay_rows
+
+    for b in range(B):
+        r = S0 - prompt_frames[b] if prompt_frames[b] else S0 + lead[b]
+        r = put_span(b, r, prompt_frames[b] + n_gen[b], nq)
+        for tok in (END, IM_END):
+            if r < ids.shape[1]:
+                ids[b, r, 0] = tok
+                r += 1
+    codes = ids[:, :, 1:].astype(np.int16)
+    frame_rows, finished, next_row = [[] for _ in range(B)], [False] * B, list(start)
     scanned = pushed = 0
     got = [[] for _ in range(B)]
     pushes = []
     for upto in [1, 6, 11, 19, 23, 31, 40]:      # uneven slices
-        scan_text_tokens(gen[:, scanned:upto, 0], scanned, frame_rows, finished, GEN, IM_END)
+        scan_finished(ids[:, S0 + scanned:S0 + upto, 0], finished, IM_END)
         scanned = upto
+        scan_frames(codes, next_row, S0 + scanned, frame_rows, P)
         if upto == steps:
             finished = [True] * B
         while True:
-            plan = plan_push(frame_rows, finished, scanned, pushed, nq, chunk_frames=3, max_push=6)
+            plan = plan_push(frame_rows, finished, pushed, chunk_frames=3, max_push=6)
             if plan is None:
                 break
             T, counts = plan
             assert 0 < T <= 6 and (all(finished) or T >= 3)
             for b, n in enumerate(counts):
                 for r in frame_rows[b][pushed:pushed + n]:
-                    assert r + nq - 1 < scanned                      # every code of the frame exists
-                    got[b].append([gen[b, r + q, 1 + q] for q in range(nq)])
+                    assert r + nq - 1 < S0 + scanned                 # every code of the frame exists
+                    got[b].append([ids[b, r + q, 1 + q] for q in range(nq)])
             pushes.append(T)
             pushed += T
     for b in range(B):
-        span = gen[b, lead[b]:, 1:]
-        n_real = min(n_frames[b], steps - lead[b] - (nq - 1))        # frames whose last code was generated
-        ref = apply_de_delay_pattern(span[: n_real + nq - 1])
+        segs = split_audio_segments(apply_de_delay_pattern(ids[b, start[b]:, 1:]), P)
+        ref = np.concatenate(segs, 0)
         np.testing.assert_array_equal(np.asarray(got[b], dtype=np.int64).reshape(-1, nq), ref)
+    assert len(got[0]) == 3 + 16 + 1 and len(got[1]) == 5 + 1            # prompt frames + gen-slot rows + the first delay-slot row
     assert finished == [True, True, True] and sum(pushes) == max(len(g) for g in got)
-    assert plan_push(frame_rows, finished, scanned, pushed, nq, 3, 6) is None
+    assert plan_push(frame_rows, finished, pushed, 3, 6) is None
