@@ -296,6 +296,85 @@ int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, int S0, cons
                       int64_t* gen_ids, int* n_steps, float* step_ms, mt_stream s);
 
 /* ------------------------------------------------------------------------------------------
+ * MOSS-TTS-Realtime step-wise decode (reference moss_tts_realtime/mossttsrealtime/):
+ * a Qwen3 backbone over [text | rvq audio] embedding sums and a Qwen3-shaped local transformer WITH rotary embedding that
+ * emits the rvq codes of a frame one after the other from the backbone's last hidden state.
+ * Replaces MossTTSRealtimeInference.prefill / step / finish (streaming_mossttsrealtime.py:121-299),
+ * generate_local_transformer :301-357, apply_repetition_penalty :359-375, sample_token :377-421 and the modules they
+ * call: MossTTSRealtime.forward (modeling_mossttsrealtime.py:101-142), MossTTSRealtimeLocalTransformerForCausalLM
+ * (modeling_mossttsrealtime_local.py:258-448).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  mt_lm_config lm;              /* backbone; n_vq = rvq, audio_head_size = audio_vocab_size (1027), capacity, weights_tiled */
+  int local_num_layers, local_intermediate_size, local_num_heads, local_num_kv_heads, local_head_dim;
+  float local_rms_norm_eps;
+  int max_frames;               /* history capacity: frames one session may generate */
+  int audio_eos_token;          /* channel-0 code that stops a row (:48) */
+  long long text_pad_id;        /* text token fed when the caller passes none (:236-237) */
+} mt_rt_config;
+
+/* bf16, [out,in] (tile-major when lm.weights_tiled).  The local transformer shares the backbone's hidden size. */
+typedef struct {
+  mt_lm_weights lm;                /* embed_tokens = embed_tokens[0], emb_ext = embed_tokens[1..rvq] stacked; no heads */
+  const void* const* l_w_qkv;      /* per local layer [lq+2lkv, H] */
+  const void* const* l_w_o;        /* [H, lq] */
+  const void* const* l_w_gate_up;  /* [2*LI, H] */
+  const void* const* l_w_down;     /* [H, LI] */
+  const void* const* l_ln_in;      /* [H] */
+  const void* const* l_ln_post;    /* [H] */
+  const void* const* l_q_norm;     /* [local_head_dim] */
+  const void* const* l_k_norm;
+  const void* l_final_norm;        /* [H] */
+  const void* l_embed;             /* local_transformer.model.embed_tokens stacked [rvq-1, audio_head_size, H] */
+  const void* const* l_heads;      /* local_lm_heads[c]: [audio_head_size, H], rvq entries */
+  const void* l_rope_cos;          /* [rvq, local_head_dim/2] bf16 */
+  const void* l_rope_sin;
+} mt_rt_weights;
+
+/* sample_token's arguments (:377) + the penalty of :335-341 */
+typedef struct {
+  int do_sample;
+  float temperature, top_p;
+  int top_k;                       /* 1..1024 when sampling */
+  float repetition_penalty;        /* 1.0 or 0 = none */
+  int repetition_window;           /* <= 0: the whole history */
+  unsigned int seed;
+} mt_rt_sample_params;
+
+typedef struct mt_rt mt_rt;
+int mt_rt_query_sizes(const mt_rt_config* cfg, long long* kv_bytes, long long* workspace_bytes);
+int mt_rt_create(const mt_rt_config* cfg, const mt_rt_weights* w, void* kv_cache, void* workspace, mt_rt** out);
+int mt_rt_destroy(mt_rt* h);
+
+/* prefill() (:121-218) from the point where the padded batch exists: input_ids [B,S0,1+rvq] int64 and attention_mask
+ * [B,S0] uint8 (device).  keep_cache = 0 starts a new conversation; 1 appends the turn behind the positions already in
+ * the KV cache (:177-179; host-synchronous: the filled length is read back).  Runs the backbone, then the depth loop with
+ * no history (gen_step 0).  audio_tokens [B,rvq] int64 (device) receives the first frame. */
+int mt_rt_prefill(mt_rt* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0, int keep_cache,
+                  const mt_rt_sample_params* p, int64_t* audio_tokens, mt_stream s);
+/* step() (:220-272): text_tokens [B] int64 (device) or NULL (text_pad for every row).  Asynchronous; once every row has
+ * stopped a step changes nothing and returns the last frame again (:232-233). */
+int mt_rt_step(mt_rt* h, const int64_t* text_tokens, const mt_rt_sample_params* p, int use_cuda_graph,
+               int64_t* audio_tokens, mt_stream s);
+/* finish() (:274-299): steps with no text until every row has stopped or max_steps frames were made.
+ * frames [max_steps, B, rvq] int64 (device); *n_steps = frames produced (host-synchronous at the end). */
+int mt_rt_finish(mt_rt* h, int max_steps, const mt_rt_sample_params* p, int use_cuda_graph, int64_t* frames, int* n_steps,
+                 mt_stream s);
+/* Session state read-back: stopping [B] uint8, attention mask [B, mask_ld >= len] uint8 (device, either may be NULL);
+ * *len / *step_idx / *finished (host, host-synchronous). */
+int mt_rt_state(mt_rt* h, uint8_t* stopping, uint8_t* mask, long long mask_ld, int* len, int* step_idx, int* finished,
+                mt_stream s);
+/* generate_local_transformer (:301-357) alone.  hidden [B,H] bf16 = backbone last_hidden_state of the newest position;
+ * history [B, gen_step, rvq] int64 or NULL = generated_tokens[:, :gen_step]; forced [B,rvq] int64 or NULL teacher-forces
+ * the chosen tokens; logits_out (optional) bf16 [rvq][B][audio_head_size] = every channel's RAW logits;
+ * audio_tokens [B,rvq] (optional when forced). */
+int mt_rt_local_generate(mt_rt* h, const void* hidden, int B, const int64_t* history, int gen_step,
+                         const mt_rt_sample_params* p, const int64_t* forced, void* logits_out, int64_t* audio_tokens,
+                         mt_stream s);
+/* backbone last_hidden_state [B,H] bf16 of the newest position (what prefill/step handed to the depth loop) */
+int mt_rt_last_hidden(mt_rt* h, int B, void* out, mt_stream s);
+
+/* ------------------------------------------------------------------------------------------
  * MOSS-Audio-Tokenizer: decode side (mt_rvq_dequant, mt_codec_decode) and encode side (mt_rlfq_quantize,
  * mt_codec_encode).  A handle is either a decoder (config.encoder = 0) or an encoder (1).
  * ------------------------------------------------------------------------------------------ */

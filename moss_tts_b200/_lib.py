@@ -29,6 +29,8 @@ EXPORTS = [
     "mt_codec_stream_bytes", "mt_codec_stream_begin", "mt_codec_stream_push", "mt_codec_stream_end",
     "mt_loudness_normalize", "mt_pack_unified_codes", "mt_pad_left",
     "mt_local_query_sizes", "mt_local_create", "mt_local_destroy", "mt_local_forward", "mt_local_generate",
+    "mt_rt_query_sizes", "mt_rt_create", "mt_rt_destroy", "mt_rt_prefill", "mt_rt_step", "mt_rt_finish", "mt_rt_state",
+    "mt_rt_local_generate", "mt_rt_last_hidden",
 ]
 
 
@@ -90,6 +92,26 @@ class LocalGenParamsC(C.Structure):
                 ("do_sample", C.POINTER(C.c_int)), ("temperature", C.POINTER(C.c_float)), ("top_p", C.POINTER(C.c_float)),
                 ("top_k", C.POINTER(C.c_int)), ("repetition_penalty", C.POINTER(C.c_float)), ("seed", C.c_uint),
                 ("use_cuda_graph", C.c_int), ("check_stop_every", C.c_int)]
+
+
+class RtConfigC(C.Structure):
+    _fields_ = [("lm", LMConfigC)] + [(n, C.c_int) for n in ("local_num_layers", "local_intermediate_size",
+                                                            "local_num_heads", "local_num_kv_heads", "local_head_dim")] + \
+               [("local_rms_norm_eps", C.c_float), ("max_frames", C.c_int), ("audio_eos_token", C.c_int),
+                ("text_pad_id", C.c_longlong)]
+
+
+class RtWeightsC(C.Structure):
+    _fields_ = [("lm", LMWeightsC)] + \
+               [(n, C.POINTER(C.c_void_p)) for n in ("l_w_qkv", "l_w_o", "l_w_gate_up", "l_w_down", "l_ln_in", "l_ln_post",
+                                                     "l_q_norm", "l_k_norm")] + \
+               [("l_final_norm", C.c_void_p), ("l_embed", C.c_void_p), ("l_heads", C.POINTER(C.c_void_p)),
+                ("l_rope_cos", C.c_void_p), ("l_rope_sin", C.c_void_p)]
+
+
+class RtSampleParamsC(C.Structure):
+    _fields_ = [("do_sample", C.c_int), ("temperature", C.c_float), ("top_p", C.c_float), ("top_k", C.c_int),
+                ("repetition_penalty", C.c_float), ("repetition_window", C.c_int), ("seed", C.c_uint)]
 
 
 _IntArr = C.c_int * MT_CODEC_MAX_STAGES

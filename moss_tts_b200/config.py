@@ -99,6 +99,58 @@ class LocalConfig(LMConfig):
 
 
 @dataclass
+class RealtimeConfig(LMConfig):
+    """MOSS-TTS-Realtime (reference moss_tts_realtime/mossttsrealtime/configuration_mossttsrealtime.py:35-112): a Qwen3
+    backbone whose input is the sum of one text and `rvq` audio embeddings (audio vocabulary 1027 = 1024 codes + pad 1024,
+    bos 1025, eos 1026) and a small Qwen3-shaped "local transformer" WITH rotary embedding that emits the `rvq` codes of
+    one frame sequentially from the backbone's last hidden state (streaming_mossttsrealtime.py:301-357).  The LMConfig
+    fields describe the backbone (`n_vq` = rvq); the local transformer shares its hidden size."""
+    n_vq: int = 16
+    audio_vocab_size: int = 1026          # audio_head_size = 1027 (configuration_mossttsrealtime.py:76-77)
+    local_num_layers: int = 4
+    local_intermediate_size: int = 6144
+    local_num_heads: int = 16
+    local_num_kv_heads: int = 8
+    local_head_dim: int = 128
+    local_rope_theta: float = 1_000_000.0
+    local_rms_norm_eps: float = 1e-6
+    audio_bos_token: int = 1025           # streaming_mossttsrealtime.py:47-51
+    audio_eos_token: int = 1026
+    text_pad_id: int = 151655
+    reference_audio_pad: int = 151654
+
+    @property
+    def rvq(self) -> int:
+        return self.n_vq
+
+    @property
+    def local_q_size(self) -> int:
+        return self.local_num_heads * self.local_head_dim
+
+    @property
+    def local_kv_size(self) -> int:
+        return self.local_num_kv_heads * self.local_head_dim
+
+    @staticmethod
+    def realtime_1p7b() -> "RealtimeConfig":
+        """Assumed released shape: public Qwen3-1.7B backbone + the local-transformer defaults of the reference config."""
+        return RealtimeConfig(hidden_size=2048, intermediate_size=6144, num_layers=28, num_heads=16, num_kv_heads=8,
+                              head_dim=128)
+
+    @staticmethod
+    def tiny(n_vq: int = 4) -> "RealtimeConfig":
+        return RealtimeConfig(hidden_size=128, intermediate_size=256, num_layers=2, num_heads=4, num_kv_heads=2,
+                              head_dim=64, n_vq=n_vq, local_num_layers=2, local_intermediate_size=320,
+                              local_num_heads=4, local_num_kv_heads=2, local_head_dim=64)
+
+    @staticmethod
+    def mid(n_vq: int = 16) -> "RealtimeConfig":
+        return RealtimeConfig(hidden_size=512, intermediate_size=1024, num_layers=2, num_heads=8, num_kv_heads=2,
+                              head_dim=128, n_vq=n_vq, local_num_layers=4, local_intermediate_size=1536,
+                              local_num_heads=4, local_num_kv_heads=2, local_head_dim=128)
+
+
+@dataclass
 class CodecStage:
     """One ProjectedTransformer stage followed by a patch upsample (reference
     modeling_moss_audio_tokenizer.py:888-953)."""

@@ -444,6 +444,188 @@ int gen_sample_step(const GenState& st, const bf16* text_logits, int vocab, cons
 }
 
 // ---------------------------------------------------------------------------------------------
+// MOSS-TTS-Realtime (reference moss_tts_realtime/mossttsrealtime/streaming_mossttsrealtime.py): session state and
+// the per-channel sampler of generate_local_transformer :301-357.
+//   rt_window_sets : ids of history[b, max(0, step - window) : step, c] as one bitmap per (row, channel) -- the set
+//                    apply_repetition_penalty :359-375 gathers / scatters (duplicates are penalised once)
+//   rt_sample      : penalty on the raw logits (greedy too), then sample_token :377-397 (argmax, or / temperature ->
+//                    top-k -> top-p -> inverse-CDF draw of this library)
+//   rt_begin_step  : step_ids = [text | last frame], mask column = !stopping (:244-247)
+//   rt_commit      : history append, stopping |= (channel 0 == eos), counters (:263-267)
+// ---------------------------------------------------------------------------------------------
+__global__ void rt_window_sets_kernel(RtState st, const int64_t* __restrict__ history, long long ld_frames,
+                                      const int* __restrict__ step_dev, int step_host, int window) {
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int b = blockIdx.x;
+  const int step = step_dev ? *step_dev : step_host;
+  uint32_t* bm = st.seen + static_cast<long long>(b) * st.R * st.words;
+  for (int i = threadIdx.x; i < st.R * st.words; i += blockDim.x) bm[i] = 0u;
+  __syncthreads();
+  if (!history || step <= 0) return;
+  const int t0 = window > 0 ? max(0, step - window) : 0;
+  const int n = (step - t0) * st.R;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const int t = t0 + i / st.R, c = i % st.R;
+    const long long v = history[(static_cast<long long>(b) * ld_frames + t) * st.R + c];
+    if (v >= 0 && v < st.words * 32) atomicOr(&bm[c * st.words + (v >> 5)], 1u << (v & 31));
+  }
+}
+
+template <bool W>
+__global__ void __launch_bounds__(kSampThreads, 3)
+rt_sample_kernel(RtState st, const bf16* __restrict__ logits, int V, int c, int do_sample, float temperature, float penalty,
+                 float top_p, int top_k, unsigned seed, const int* __restrict__ step_dev, int step_host,
+                 int64_t* __restrict__ out) {
+  __shared__ SampleShared sm;
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int warp = threadIdx.x >> 5;
+  const int b = W ? blockIdx.x * (kSampThreads / 32) + warp : blockIdx.x;
+  if (b >= st.B) return;
+  RowXform x;
+  x.row = logits + static_cast<long long>(b) * V; x.V = V; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
+  x.temp = do_sample ? temperature : 1.f; x.bitmap = nullptr; x.penalty = 1.f; x.penalty_first = 1;
+  if (penalty != 1.0f) {
+    x.bitmap = st.seen + (static_cast<long long>(b) * st.R + c) * st.words;
+    x.penalty = penalty;
+  }
+  const float u = mt_uniform(seed, step_dev ? *step_dev : step_host, b, c);
+  const int tok = W ? warp_pick(x, do_sample, top_k, top_p, u, sm.warp[warp]) : block_pick(x, do_sample, top_k, top_p, u, sm.blk);
+  if (W ? (threadIdx.x & 31) == 0 : threadIdx.x == 0) out[static_cast<long long>(b) * st.R + c] = tok;
+}
+
+__global__ void rt_prefill_init_kernel(RtState st, const uint8_t* __restrict__ attn_mask, int S0, int past) {
+  const int b = blockIdx.x;
+  for (int t = threadIdx.x; t < S0; t += blockDim.x)
+    st.mask[static_cast<long long>(b) * st.max_seq + past + t] = attn_mask[static_cast<long long>(b) * S0 + t] ? 1 : 0;
+  if (threadIdx.x == 0) {
+    st.stopping[b] = 0;
+    if (b == 0) { *st.len = past + S0; *st.step = 0; *st.done = 0; *st.pos = past + S0 - 1; }
+  }
+}
+
+__global__ void rt_set_text_kernel(RtState st, const int64_t* __restrict__ text_tokens, long long text_pad) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < st.B) st.text_in[b] = text_tokens ? text_tokens[b] : text_pad;
+}
+
+__global__ void rt_begin_step_kernel(RtState st) {
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int len = *st.len, C = st.R + 1;
+  for (int i = threadIdx.x; i < st.B * C; i += blockDim.x) {
+    const int b = i / C, c = i % C;
+    st.step_ids[i] = c == 0 ? st.text_in[b] : st.last[static_cast<long long>(b) * st.R + c - 1];
+  }
+  if (len < st.max_seq)
+    for (int b = threadIdx.x; b < st.B; b += blockDim.x) st.mask[static_cast<long long>(b) * st.max_seq + len] = st.stopping[b] ? 0 : 1;
+  if (threadIdx.x == 0) *st.pos = min(len, st.max_seq - 1);
+}
+
+__global__ void rt_commit_kernel(RtState st, int eos, int advance_len, int64_t* __restrict__ tokens_out) {
+  pdl_trigger();
+  pdl_wait();
+  const bool done = *st.done != 0;
+  __shared__ int any_running;
+  if (threadIdx.x == 0) any_running = 0;
+  __syncthreads();
+  const int step = *st.step;
+  for (int i = threadIdx.x; i < st.B * st.R; i += blockDim.x) {
+    const int b = i / st.R, c = i % st.R;
+    const long long t = st.last[i];
+    if (tokens_out) tokens_out[i] = t;                      // a finished session keeps returning its last frame (:232-233)
+    if (!done && step < st.max_frames) st.history[(static_cast<long long>(b) * st.max_frames + step) * st.R + c] = t;
+  }
+  if (done) return;
+  for (int b = threadIdx.x; b < st.B; b += blockDim.x) {
+    uint8_t sp = st.stopping[b];
+    if (st.last[static_cast<long long>(b) * st.R] == eos) sp = 1;
+    st.stopping[b] = sp;
+    if (!sp) atomicOr(&any_running, 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *st.step = step + 1;
+    if (advance_len) *st.len = *st.len + 1;
+    if (!any_running) *st.done = 1;
+  }
+}
+
+size_t rt_state_bytes(int B, int R, int max_frames, int max_seq, int audio_head) {
+  const int words = (audio_head + 31) / 32;
+  return 256 + align_up(B, 256) + align_up(static_cast<size_t>(B) * 8, 256) + align_up(static_cast<size_t>(B) * (R + 1) * 8, 256) +
+         align_up(static_cast<size_t>(B) * R * 8, 256) + align_up(static_cast<size_t>(B) * max_frames * R * 8, 256) +
+         align_up(static_cast<size_t>(B) * max_seq, 256) + align_up(static_cast<size_t>(B) * R * words * 4, 256);
+}
+
+RtState rt_state_carve(void* buf, int B, int R, int max_frames, int max_seq, int audio_head) {
+  RtState st{};
+  uint8_t* p = reinterpret_cast<uint8_t*>(buf);
+  const int words = (audio_head + 31) / 32;
+  st.len = reinterpret_cast<int*>(p); st.step = st.len + 1; st.done = st.len + 2; st.pos = st.len + 3; p += 256;
+  st.stopping = p; p += align_up(B, 256);
+  st.text_in = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * 8, 256);
+  st.step_ids = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * (R + 1) * 8, 256);
+  st.last = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * R * 8, 256);
+  st.history = reinterpret_cast<int64_t*>(p); p += align_up(static_cast<size_t>(B) * max_frames * R * 8, 256);
+  st.mask = p; p += align_up(static_cast<size_t>(B) * max_seq, 256);
+  st.seen = reinterpret_cast<uint32_t*>(p);
+  st.B = B; st.R = R; st.max_frames = max_frames; st.max_seq = max_seq; st.words = words;
+  return st;
+}
+
+int rt_prefill_init(const RtState& st, const uint8_t* attn_mask, int S0, int past, cudaStream_t s) {
+  rt_prefill_init_kernel<<<st.B, 256, 0, s>>>(st, attn_mask, S0, past);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+int rt_set_text(const RtState& st, const int64_t* text_tokens, long long text_pad, cudaStream_t s) {
+  rt_set_text_kernel<<<cdiv(st.B, 128), 128, 0, s>>>(st, text_tokens, text_pad);
+  count_launch();
+  MT_LAUNCH_CHECK();
+  return MT_OK;
+}
+
+int rt_begin_step(const RtState& st, cudaStream_t s) {
+  MT_CUDA(launch(rt_begin_step_kernel, dim3(1), dim3(1024), 0, s, st));
+  count_launch();
+  return MT_OK;
+}
+
+int rt_window_sets(const RtState& st, const int64_t* history, long long ld_frames, const int* step_dev, int step_host,
+                   int window, cudaStream_t s) {
+  MT_CUDA(launch(rt_window_sets_kernel, dim3(st.B), dim3(256), 0, s, st, history, ld_frames, step_dev, step_host, window));
+  count_launch();
+  return MT_OK;
+}
+
+int rt_sample(const RtState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
+              float top_p, int top_k, unsigned seed, const int* step_dev, int step_host, int64_t* out, cudaStream_t s) {
+  if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
+    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
+  if (V <= kWarpMaxV && (!do_sample || top_k <= kWarpMaxK))
+    MT_CUDA(launch(rt_sample_kernel<true>, dim3(cdiv(st.B, kSampThreads / 32)), dim3(kSampThreads), 0, s, st, logits, V, c,
+                   do_sample, temperature, penalty, top_p, top_k, seed, step_dev, step_host, out));
+  else
+    MT_CUDA(launch(rt_sample_kernel<false>, dim3(st.B), dim3(kSampThreads), 0, s, st, logits, V, c, do_sample, temperature,
+                   penalty, top_p, top_k, seed, step_dev, step_host, out));
+  count_launch();
+  return MT_OK;
+}
+
+int rt_commit(const RtState& st, int eos, int advance_len, int64_t* tokens_out, cudaStream_t s) {
+  MT_CUDA(launch(rt_commit_kernel, dim3(1), dim3(1024), 0, s, st, eos, advance_len, tokens_out));
+  count_launch();
+  return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // standalone sample_token (inference_utils.py:111-145) on [N,V] bf16 logits
 // ---------------------------------------------------------------------------------------------
 template <bool W>

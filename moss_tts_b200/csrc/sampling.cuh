@@ -69,6 +69,33 @@ int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_
                  float top_p, int top_k, unsigned seed, cudaStream_t s);
 int local_commit(const LocalState& st, int eos, int pad_code, int n_channels_sampled, cudaStream_t s);
 
+// Device-resident state of one MOSS-TTS-Realtime session (reference streaming_mossttsrealtime.py:63-86: attention_mask,
+// _generated_tokens, _is_stopping, _last_audio_tokens, _step_idx).
+struct RtState {
+  int *len, *step, *done, *pos;   // mask columns filled / frames generated (_step_idx) / all rows stopping / KV row of the step
+  uint8_t* stopping;              // [B] _is_stopping
+  int64_t* text_in;               // [B] text token of the next step (text_pad when the caller has none)
+  int64_t* step_ids;              // [B, 1+R] backbone input of a step: text token | previous frame (:244-246)
+  int64_t* last;                  // [B, R] newest frame (_last_audio_tokens); the depth loop writes it channel by channel
+  int64_t* history;               // [B, max_frames, R] _generated_tokens
+  uint8_t* mask;                  // [B, max_seq] attention_mask (a stopped row's later columns are 0, :247)
+  uint32_t* seen;                 // [B, R, words] ids inside the repetition window of each (row, channel)
+  int B, R, max_frames, max_seq, words;
+};
+size_t rt_state_bytes(int B, int R, int max_frames, int max_seq, int audio_head);
+RtState rt_state_carve(void* buf, int B, int R, int max_frames, int max_seq, int audio_head);
+// prefill: copies attn_mask [B,S0] behind the `past` columns already filled, resets the generation state
+int rt_prefill_init(const RtState& st, const uint8_t* attn_mask, int S0, int past, cudaStream_t s);
+int rt_set_text(const RtState& st, const int64_t* text_tokens, long long text_pad, cudaStream_t s);
+int rt_begin_step(const RtState& st, cudaStream_t s);
+// id sets of the last `window` frames (window <= 0: all) of history [B, ld_frames, R] before frame `step`
+int rt_window_sets(const RtState& st, const int64_t* history, long long ld_frames, const int* step_dev, int step_host,
+                   int window, cudaStream_t s);
+// channel c: apply_repetition_penalty (:359-375, also when greedy) -> sample_token (:377-397) -> out[b*R + c]
+int rt_sample(const RtState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
+              float top_p, int top_k, unsigned seed, const int* step_dev, int step_host, int64_t* out, cudaStream_t s);
+int rt_commit(const RtState& st, int eos, int advance_len, int64_t* tokens_out, cudaStream_t s);
+
 int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
                   float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
                   cudaStream_t s);

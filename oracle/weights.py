@@ -14,7 +14,7 @@ from typing import Dict
 
 import torch
 
-from moss_tts_b200.config import LMConfig, CodecConfig, LocalConfig
+from moss_tts_b200.config import LMConfig, CodecConfig, LocalConfig, RealtimeConfig
 
 
 def _gen(seed: int, name: str) -> torch.Generator:
@@ -103,6 +103,30 @@ def make_local_weights(cfg: LocalConfig, seed: int = 0, std: float = 0.02, eos_b
         w[p + "down_proj.weight"] = _normal(seed, p + "d", (H, AF), a)
         w[f"layer_norm_before_lm_heads.{c}.weight"] = _normal(seed, f"hn{c}", (H,), 0.1, 1.0)
         w[f"lm_heads.{c}.weight"] = _normal(seed, f"head{c}", (cfg.vocab_size if c == 0 else cfg.audio_head_size, H), std)
+    return w
+
+
+def make_realtime_weights(cfg: RealtimeConfig, seed: int = 0, std: float = 0.02) -> Dict[str, torch.Tensor]:
+    """fp32 master weights of MOSS-TTS-Realtime under the reference's state_dict keys
+    (moss_tts_realtime/mossttsrealtime/modeling_mossttsrealtime.py:82-99,
+    modeling_mossttsrealtime_local.py:258-268,381-389)."""
+    w: Dict[str, torch.Tensor] = {}
+    H, A = cfg.hidden_size, cfg.audio_head_size
+    w["embed_tokens.0.weight"] = _normal(seed, "emb0", (cfg.vocab_size, H), std)
+    for i in range(1, cfg.rvq + 1):
+        w[f"embed_tokens.{i}.weight"] = _normal(seed, f"emb{i}", (A, H), std)
+    for l in range(cfg.num_layers):
+        _qwen_layer(w, seed, f"language_model.layers.{l}.", H, cfg.intermediate_size, cfg.q_size, cfg.kv_size,
+                    cfg.head_dim, std)
+    w["language_model.norm.weight"] = _normal(seed, "gnorm", (H,), 0.1, 1.0)
+    for i in range(cfg.rvq - 1):
+        w[f"local_transformer.model.embed_tokens.{i}.weight"] = _normal(seed, f"lemb{i}", (A, H), 50 * std)
+    for l in range(cfg.local_num_layers):
+        _qwen_layer(w, seed, f"local_transformer.model.layers.{l}.", H, cfg.local_intermediate_size, cfg.local_q_size,
+                    cfg.local_kv_size, cfg.local_head_dim, 2 * std)
+    w["local_transformer.model.norm.weight"] = _normal(seed, "lnorm", (H,), 0.1, 1.0)
+    for i in range(cfg.rvq):
+        w[f"local_transformer.local_lm_heads.{i}.weight"] = _normal(seed, f"lhead{i}", (A, H), std)
     return w
 
 
