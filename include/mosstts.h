@@ -222,6 +222,16 @@ int mt_sample_tokens(const void* logits, long long ld, int N, int V, float tempe
                      const uint32_t* prev_bitmap, float repetition_penalty, float top_p, int top_k,
                      int do_sample, const float* uniforms, int64_t* out, mt_stream s);
 
+/* The same call for sampling WITHOUT a top-k filter (top_k <= 0, i.e. the reference's `top_k is None or <= 0`, :135) or with
+ * top_k > 1024 over long rows: a counting sort over the 65,536 possible bf16 values replaces the candidate list.
+ * scratch: mt_sample_full_scratch_bytes(N) bytes of device memory (256 KB per row), contents irrelevant.
+ * Any (top_k, V) mt_sample_tokens accepts is accepted here too (the scratch is then unused). */
+long long mt_sample_full_scratch_bytes(int N);
+int mt_sample_tokens_full(const void* logits, long long ld, int N, int V, float temperature,
+                          const uint32_t* prev_bitmap, float repetition_penalty, float top_p, int top_k,
+                          int do_sample, const float* uniforms, int64_t* out, void* scratch, long long scratch_bytes,
+                          mt_stream s);
+
 /* inference_utils.find_last_equal_C (:148-165): t [B,S] int64 -> out [B] int64 (-1 if absent). */
 int mt_find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out, mt_stream s);
 
@@ -270,8 +280,8 @@ int mt_local_destroy(mt_local* h);
  * backbone over input_ids [B,S0,1+n_vq], then the depth loop feeding frame_ids [B,1+n_vq] (device int64).
  * logits_out: bf16 [min(1+n_vq, 1+n_vq_for_inference)][B][ldv]; channel c fills its first vocab / audio_head_size
  * columns, audio channels carry -inf at the pad code (:411-412).  Parity tests compare these with the oracle. */
-int mt_local_forward(mt_local* h, const int64_t* input_ids, int B, int S0, int n_vq_for_inference,
-                     const int64_t* frame_ids, void* logits_out, long long ldv, mt_stream s);
+int mt_local_forward(mt_local* h, const int64_t* input_ids, const uint8_t* attention_mask /* [B,S0] or NULL */, int B, int S0,
+                     int n_vq_for_inference, const int64_t* frame_ids, void* logits_out, long long ldv, mt_stream s);
 
 /* generation_config of the reference (:359-370): per-channel host arrays of 1+n_vq entries.  Channels with
  * do_sample[c] == 0 take the argmax of the raw logits; the others apply RepetitionPenalty (c > 0 only, over the
@@ -288,9 +298,11 @@ typedef struct {
   unsigned int seed;
   int use_cuda_graph;
   int check_stop_every;
+  const uint8_t* attention_mask;   /* [B,S0] uint8 (device) or NULL = all ones.  Left padding is masked out of the keys and
+                                      every generated frame is visible, as HF's generation loop extends the mask (:391-395) */
 } mt_local_gen_params;
 
-/* input_ids [B,S0,1+n_vq] int64 (device; un-padded prompts: the attention mask is all ones).
+/* input_ids [B,S0,1+n_vq] int64 (device).
  * gen_ids [B, S0+max_new_tokens, 1+n_vq] int64 (device) receives prompt + generated frames; *n_steps = frames made. */
 int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, int S0, const mt_local_gen_params* p,
                       int64_t* gen_ids, int* n_steps, float* step_ms, mt_stream s);

@@ -23,7 +23,7 @@ EXPORTS = [
     "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_debug_set_attn_cluster", "mt_debug_set_trace", "mt_codec_debug_set_absmax", "mt_gemm", "mt_gemm_static_scratch",
     "mt_lm_query_sizes", "mt_lm_create", "mt_lm_destroy", "mt_lm_forward", "mt_lm_embed", "mt_lm_generate",
     "mt_lm_stream_begin", "mt_lm_stream_steps", "mt_lm_stream_end", "mt_stream_gather_frames", "mt_crossfade",
-    "mt_sample_tokens", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
+    "mt_sample_tokens", "mt_sample_tokens_full", "mt_sample_full_scratch_bytes", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
     "mt_codec_create", "mt_codec_destroy", "mt_codec_workspace_bytes", "mt_rvq_fold_tables",
     "mt_rvq_dequant", "mt_codec_decode", "mt_rlfq_quantize", "mt_codec_encode",
     "mt_codec_stream_bytes", "mt_codec_stream_begin", "mt_codec_stream_push", "mt_codec_stream_end",
@@ -91,7 +91,7 @@ class LocalGenParamsC(C.Structure):
     _fields_ = [("max_new_tokens", C.c_int), ("n_vq_for_inference", C.c_int), ("eos_token_id", C.c_int),
                 ("do_sample", C.POINTER(C.c_int)), ("temperature", C.POINTER(C.c_float)), ("top_p", C.POINTER(C.c_float)),
                 ("top_k", C.POINTER(C.c_int)), ("repetition_penalty", C.POINTER(C.c_float)), ("seed", C.c_uint),
-                ("use_cuda_graph", C.c_int), ("check_stop_every", C.c_int)]
+                ("use_cuda_graph", C.c_int), ("check_stop_every", C.c_int), ("attention_mask", C.c_void_p)]
 
 
 class RtConfigC(C.Structure):
@@ -172,6 +172,7 @@ def lib() -> C.CDLL:
         L = C.CDLL(LIB_PATH)
         L.mt_last_error.restype = C.c_char_p
         L.mt_launch_count.restype = C.c_longlong
+        L.mt_sample_full_scratch_bytes.restype = C.c_longlong
         if os.environ.get("MT_FORCE_SIMT") == "1":      # test-only: cross-check everything on the SIMT GEMM
             L.mt_debug_force_simt(1)
         _lib = L

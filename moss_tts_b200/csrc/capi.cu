@@ -42,6 +42,15 @@ extern "C" int mt_sample_tokens(const void* logits, long long ld, int N, int V, 
   return sample_tokens(reinterpret_cast<const bf16*>(logits), ld, N, V, temperature, prev_bitmap, repetition_penalty,
                        top_p, top_k, do_sample, uniforms, out, reinterpret_cast<cudaStream_t>(s));
 }
+extern "C" long long mt_sample_full_scratch_bytes(int N) { return static_cast<long long>(N) * static_cast<long long>(sample_full_scratch_bytes()); }
+extern "C" int mt_sample_tokens_full(const void* logits, long long ld, int N, int V, float temperature,
+                                     const uint32_t* prev_bitmap, float repetition_penalty, float top_p, int top_k,
+                                     int do_sample, const float* uniforms, int64_t* out, void* scratch, long long scratch_bytes,
+                                     mt_stream s) {
+  MT_CHECK(logits && out, "mt_sample_tokens_full: null argument");
+  return sample_tokens(reinterpret_cast<const bf16*>(logits), ld, N, V, temperature, prev_bitmap, repetition_penalty,
+                       top_p, top_k, do_sample, uniforms, out, reinterpret_cast<cudaStream_t>(s), scratch, scratch_bytes);
+}
 extern "C" int mt_find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out,
                                   mt_stream s) {
   MT_CHECK(t && out, "mt_find_last_equal: null argument");

@@ -42,7 +42,9 @@ static size_t carve_workspace(mt_lm* h, const mt_lm_config& c, void* ws) {
   auto al = cv.take<bf16>(static_cast<size_t>(c.max_batch) * c.n_vq * c.audio_head_size);
   auto sk = cv.take<float>(kSplitKBytes / 4);
   auto gs = cv.take<uint8_t>(gen_state_bytes(c.max_batch, 1 + c.n_vq, c.max_seq, c.audio_head_size));
+  auto fh = cv.take<uint32_t>(static_cast<size_t>(c.max_batch) * (sample_full_scratch_bytes() / 4));   // text_top_k = None
   if (h) {
+    h->full_hist = fh;
     h->x = x; h->xn = xn; h->qkv = qkv; h->q = q; h->attn = attn; h->gu = gu; h->act = act; h->delta = delta;
     h->last_h = last_h; h->text_logits = tl; h->audio_logits = al; h->splitk = sk; h->gen_state_buf = gs;
   }
@@ -265,9 +267,9 @@ static int make_sample_cfg(const mt_lm_config& c, const mt_gen_params* p, Sample
   // audio_top_k = None / <= 0 (no top-k filter, inference_utils.py:135): the pad code of every audio head is -inf
   // (modeling_moss_tts.py:295-300, 486-487), so keeping the audio_head_size - 1 real codes IS "no filter"
   if (sc.audio_do_sample && sc.audio_top_k <= 0 && c.audio_head_size - 1 <= kMaxTopK) sc.audio_top_k = c.audio_head_size - 1;
-  if ((sc.text_do_sample && (sc.text_top_k <= 0 || sc.text_top_k > kMaxTopK)) ||
-      (sc.audio_do_sample && (sc.audio_top_k <= 0 || sc.audio_top_k > kMaxTopK)))
-    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d", kMaxTopK);
+  // text_top_k = None / <= 0 / > 1024: the full-vocabulary counting-sort sampler (sampling_full.cuh)
+  if (sc.audio_do_sample && (sc.audio_top_k <= 0 || sc.audio_top_k > kMaxTopK))
+    return fail(MT_ERR_UNSUPPORTED, "audio sampling requires 1 <= top_k <= %d", kMaxTopK);
   return MT_OK;
 }
 
@@ -290,6 +292,7 @@ extern "C" int mt_lm_generate(mt_lm* h, const int64_t* input_ids, const uint8_t*
   }
   const TokenIds tk = token_ids(c);
   GenState st = gen_state_carve(h->gen_state_buf, B, 1 + c.n_vq, max_len, c.audio_head_size, gen_ids);
+  st.full_hist = h->full_hist;
   MT_TRY(gen_init(st, input_ids, attention_mask, S0, tk, start_indices, s));
   if (p->max_new_tokens == 0) return MT_OK;
 
@@ -399,6 +402,7 @@ extern "C" int mt_lm_stream_begin(mt_lm* h, const int64_t* input_ids, const uint
   MT_TRY(make_sample_cfg(c, p, ss.sc));
   ss.tk = token_ids(c);
   ss.st = gen_state_carve(h->gen_state_buf, B, 1 + c.n_vq, max_len, c.audio_head_size, gen_ids);
+  ss.st.full_hist = h->full_hist;
   ss.B = B; ss.S0 = S0; ss.max_len = max_len; ss.max_new = p->max_new_tokens; ss.use_graph = p->use_cuda_graph;
   MT_TRY(gen_init(ss.st, input_ids, attention_mask, S0, ss.tk, start_indices, s));
   MT_TRY(lm_forward_impl(h, input_ids, ss.st.mask, max_len, B, S0, 0, nullptr, S0, 1, h->text_logits, h->audio_logits, s));

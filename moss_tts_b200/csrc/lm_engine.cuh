@@ -14,6 +14,7 @@ struct mt_lm {
   // workspace views
   mt::bf16 *x, *xn, *qkv, *q, *attn, *gu, *act, *delta, *last_h, *text_logits, *audio_logits;
   float* splitk;
+  uint32_t* full_hist;                 // [max_batch][65536] scratch of the full-vocabulary text sampler
   void* gen_state_buf;
   mt::bf16 *k_cache, *v_cache;   // [L][B][kv][S][D] each
   size_t ws_bytes;

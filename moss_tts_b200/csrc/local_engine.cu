@@ -155,7 +155,7 @@ static int local_frame(mt_local* h, const LocalState& st, const bf16* hs, int B,
                                 cudaMemcpyDeviceToDevice, s));
     } else {
       MT_TRY(local_sample(st, h->logits, V, c, sm.do_sample[c], sm.temperature[c], sm.penalty[c], sm.top_p[c], sm.top_k[c],
-                          sm.seed, s));
+                          sm.seed, s, h->g->full_hist));
     }
     if (c + 1 < n_ch) {
       const bf16* table = c == 0 ? reinterpret_cast<const bf16*>(h->w.lm.embed_tokens)
@@ -238,8 +238,9 @@ extern "C" int mt_local_destroy(mt_local* h) {
 }
 
 
-extern "C" int mt_local_forward(mt_local* h, const int64_t* input_ids, int B, int S0, int n_vq_for_inference,
-                                const int64_t* frame_ids, void* logits_out, long long ldv, mt_stream stream) {
+extern "C" int mt_local_forward(mt_local* h, const int64_t* input_ids, const uint8_t* attention_mask, int B, int S0,
+                                int n_vq_for_inference, const int64_t* frame_ids, void* logits_out, long long ldv,
+                                mt_stream stream) {
   MT_CHECK(h && input_ids && frame_ids && logits_out, "mt_local_forward: null argument");
   const mt_lm_config& c = h->cfg.lm;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
@@ -249,7 +250,7 @@ extern "C" int mt_local_forward(mt_local* h, const int64_t* input_ids, int B, in
   MT_CHECK(ldv >= c.vocab_size && ldv >= c.audio_head_size, "mt_local_forward: ldv %lld is smaller than the widest head", ldv);
   const int n_ch = std::min(h->C, 1 + n_vq_for_inference);
   LocalState st = local_state_carve(h->state_buf, B, h->C, S0, c.audio_head_size, nullptr);
-  MT_TRY(local_init(st, input_ids, S0, s));
+  MT_TRY(local_init(st, input_ids, S0, s, attention_mask));
   MT_TRY(lm_forward_impl(h->g, input_ids, st.mask, S0, B, S0, 0, nullptr, S0, 1, nullptr, nullptr, s, nullptr, n_vq_for_inference));
   LocalSampling none{};
   return local_frame(h, st, S0 > 1 ? h->g->last_h : h->g->xn, B, n_ch, none, -1, s, frame_ids, reinterpret_cast<bf16*>(logits_out), ldv);
@@ -276,13 +277,11 @@ extern "C" int mt_local_generate(mt_local* h, const int64_t* input_ids, int B, i
     sm.penalty.push_back(p->repetition_penalty[ch]);
     if (ch < n_ch && sm.do_sample[ch]) {
       MT_CHECK(sm.temperature[ch] > 0.f, "generate: channel %d temperature must be > 0", ch);
-      if (sm.top_k[ch] <= 0 || sm.top_k[ch] > kMaxTopK)
-        return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (channel %d has %d)", kMaxTopK, ch, sm.top_k[ch]);
     }
   }
   *n_steps = 0;
   LocalState st = local_state_carve(h->state_buf, B, C, max_len, c.audio_head_size, gen_ids);
-  MT_TRY(local_init(st, input_ids, S0, s));
+  MT_TRY(local_init(st, input_ids, S0, s, p->attention_mask));
   if (p->max_new_tokens == 0) return MT_OK;
 
   std::vector<cudaEvent_t> ev;

@@ -10,7 +10,7 @@
 #include <cstddef>
 
 #include "sampling.cuh"
-#include "sampling_select.cuh"
+#include "sampling_full.cuh"
 
 namespace mt {
 
@@ -185,6 +185,7 @@ static_assert(offsetof(SelSmem<BlockG>, ebuf) >= sizeof(SampSmem),
 union SampleShared {
   BlockSmem blk;
   SelSmem<WarpG> warp[kSampThreads / 32];
+  FullSmem full;
 };
 
 // mode 2 (text channel inside audio): only the gen / delay slots survive the mask -- two candidates, no row scan.
@@ -286,7 +287,12 @@ gen_sample_kernel(GenState st, const bf16* __restrict__ text_logits, int vocab,
     }
     if (step == 0) x.ban[x.nban++] = 151662;              // hard-coded id in the reference (:462)
     if (step <= n_vq) x.ban[x.nban++] = tk.im_end;
-    const int tok = block_pick(x, sc.text_do_sample, sc.text_top_k, sc.text_top_p, mt_uniform(sc.seed, step, b, 0), sm.blk);
+    // no top-k filter, or one beyond the shared-memory candidate list: the full-vocabulary counting-sort sampler
+    const bool full = sc.text_do_sample && (sc.text_top_k <= 0 || sc.text_top_k > kMaxTopK);
+    const float u = mt_uniform(sc.seed, step, b, 0);
+    const int tok = (full && x.mode != 2)
+                        ? full_pick(x, sc.text_top_k, sc.text_top_p, u, st.full_hist + static_cast<size_t>(b) * kFullBuckets, sm.full)
+                        : block_pick(x, sc.text_do_sample, full ? 2 : sc.text_top_k, sc.text_top_p, u, sm.blk);
     if (leader) *dst = tok;
   } else {
     // ---- audio channel i = ch-1 (modeling_moss_tts.py:475-503); lengths are the pre-update ones
@@ -645,13 +651,41 @@ sample_tokens_kernel(const bf16* __restrict__ logits, long long ld, int N, int V
   if (W ? (threadIdx.x & 31) == 0 : threadIdx.x == 0) out[r] = tok;
 }
 
+__global__ void __launch_bounds__(kSampThreads, 3)
+sample_full_kernel(const bf16* __restrict__ logits, long long ld, int N, int V, float temperature,
+                   const uint32_t* __restrict__ bitmap, float penalty, float top_p, int top_k,
+                   const float* __restrict__ uniforms, int64_t* __restrict__ out, uint32_t* __restrict__ hist) {
+  __shared__ FullSmem sm;
+  const int r = blockIdx.x;
+  RowXform x;
+  x.row = logits + r * ld; x.V = V; x.temp = temperature; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
+  x.bitmap = penalty != 1.0f ? bitmap : nullptr; x.penalty = penalty; x.penalty_first = 0;
+  const int tok = full_pick(x, top_k, top_p, uniforms ? uniforms[r] : 0.f, hist + static_cast<size_t>(r) * kFullBuckets, sm);
+  if (threadIdx.x == 0) out[r] = tok;
+}
+
+size_t sample_full_scratch_bytes() { return kFullScratchPerRow; }
+
 int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
                   float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
-                  cudaStream_t s) {
+                  cudaStream_t s, void* scratch, long long scratch_bytes) {
   MT_CHECK(N > 0 && V > 0, "sample_tokens: empty input");
-  if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
-    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
   MT_CHECK(temperature > 0.f, "temperature must be > 0");
+  if (do_sample && (top_k <= 0 || top_k > kMaxTopK)) {
+    if (top_k <= 0 && V <= kMaxTopK) {
+      top_k = V;                                           // keeping every entry of a short row IS no filter
+    } else {
+      // no top-k filter (inference_utils.py:135) or a top-k beyond the shared-memory list: counting sort over the row
+      if (!scratch || scratch_bytes < static_cast<long long>(N * kFullScratchPerRow))
+        return fail(MT_ERR_ARG, "sampling with top_k = %d over %d logits needs %lld bytes of scratch (mt_sample_tokens_full)",
+                    top_k, V, static_cast<long long>(N * kFullScratchPerRow));
+      sample_full_kernel<<<N, kSampThreads, 0, s>>>(logits, ld, N, V, temperature, prev_bitmap, penalty, top_p, top_k, uniforms,
+                                                     out, reinterpret_cast<uint32_t*>(scratch));
+      count_launch();
+      MT_LAUNCH_CHECK();
+      return MT_OK;
+    }
+  }
   if (V <= kWarpMaxV && (!do_sample || top_k <= kWarpMaxK))
     sample_tokens_kernel<true><<<cdiv(N, kSampThreads / 32), kSampThreads, 0, s>>>(logits, ld, N, V, temperature, prev_bitmap, penalty,
                                                                                    top_p, top_k, do_sample, uniforms, out);
@@ -727,7 +761,8 @@ __global__ void local_commit_kernel(LocalState st, int eos, int pad_code, int n_
   }
 }
 
-__global__ void local_init_kernel(LocalState st, const int64_t* __restrict__ input_ids, int S0) {
+__global__ void local_init_kernel(LocalState st, const int64_t* __restrict__ input_ids, int S0,
+                                  const uint8_t* __restrict__ attn_mask) {
   const int b = blockIdx.x;
   const int64_t* src = input_ids + static_cast<long long>(b) * S0 * st.C;
   int64_t* g = st.gen_ids + static_cast<long long>(b) * st.max_len * st.C;
@@ -738,7 +773,9 @@ __global__ void local_init_kernel(LocalState st, const int64_t* __restrict__ inp
     if (c >= 1 && v >= 0 && v < st.bitmap_words * 32)
       atomicOr(&st.seen[(static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words + (v >> 5)], 1u << (v & 31));
   }
-  for (int t = threadIdx.x; t < st.max_len; t += blockDim.x) st.mask[static_cast<long long>(b) * st.max_len + t] = 1;
+  // the prompt's mask (left padding), ones for every generated frame (HF extends the mask it is given with ones)
+  for (int t = threadIdx.x; t < st.max_len; t += blockDim.x)
+    st.mask[static_cast<long long>(b) * st.max_len + t] = (attn_mask && t < S0) ? (attn_mask[static_cast<long long>(b) * S0 + t] ? 1 : 0) : 1;
   if (b == 0)
     for (int t = threadIdx.x; t < st.C; t += blockDim.x) st.ones[t] = 1;
   if (threadIdx.x == 0) {
@@ -767,17 +804,44 @@ LocalState local_state_carve(void* buf, int B, int C, int max_len, int audio_hea
   return st;
 }
 
-int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s) {
+int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s, const uint8_t* attn_mask) {
   MT_CUDA(cudaMemsetAsync(st.seen, 0, static_cast<size_t>(st.B) * (st.C - 1) * st.bitmap_words * 4, s));
-  MT_CUDA(launch(local_init_kernel, dim3(st.B), dim3(256), 0, s, st, input_ids, S0));
+  MT_CUDA(launch(local_init_kernel, dim3(st.B), dim3(256), 0, s, st, input_ids, S0, attn_mask));
   count_launch();
   return MT_OK;
 }
 
+__global__ void __launch_bounds__(kSampThreads, 3)
+local_sample_full_kernel(LocalState st, const bf16* __restrict__ logits, int V, int c, float temperature, float penalty,
+                         float top_p, int top_k, unsigned seed, uint32_t* __restrict__ hist) {
+  __shared__ FullSmem sm;
+  pdl_trigger();
+  pdl_wait();
+  if (*st.done) return;
+  const int b = blockIdx.x;
+  RowXform x;
+  x.row = logits + static_cast<long long>(b) * V; x.V = V; x.mode = 0; x.nban = 0; x.keep0 = x.keep1 = -1;
+  x.temp = temperature; x.bitmap = nullptr; x.penalty = 1.f; x.penalty_first = 1;
+  if (c > 0) { x.ban[0] = V - 1; x.nban = 1; }
+  if (c > 0 && penalty != 1.0f) {
+    x.bitmap = st.seen + (static_cast<long long>(b) * (st.C - 1) + (c - 1)) * st.bitmap_words;
+    x.penalty = penalty;
+  }
+  const int tok = full_pick(x, top_k, top_p, mt_uniform(seed, *st.step, b, c), hist + static_cast<size_t>(b) * kFullBuckets, sm);
+  if (threadIdx.x == 0) st.next_ids[static_cast<long long>(b) * st.C + c] = tok;
+}
+
 int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
-                 float top_p, int top_k, unsigned seed, cudaStream_t s) {
-  if (do_sample && (top_k <= 0 || top_k > kMaxTopK))
-    return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
+                 float top_p, int top_k, unsigned seed, cudaStream_t s, uint32_t* full_hist) {
+  if (do_sample && top_k <= 0 && V <= kMaxTopK) top_k = V;        // no top-k warper on a short row: keep everything
+  if (do_sample && (top_k <= 0 || top_k > kMaxTopK)) {
+    // no TopKLogitsWarper (or one beyond the candidate list) on a long row: full-vocabulary counting sort
+    if (!full_hist) return fail(MT_ERR_UNSUPPORTED, "sampling requires 1 <= top_k <= %d (got %d)", kMaxTopK, top_k);
+    MT_CUDA(launch(local_sample_full_kernel, dim3(st.B), dim3(kSampThreads), 0, s, st, logits, V, c, temperature, penalty, top_p,
+                   top_k, seed, full_hist));
+    count_launch();
+    return MT_OK;
+  }
   if (V <= kWarpMaxV && (!do_sample || top_k <= kWarpMaxK))
     MT_CUDA(launch(local_sample_kernel<true>, dim3(cdiv(st.B, kSampThreads / 32)), dim3(kSampThreads), 0, s, st, logits, V, c,
                    do_sample, temperature, penalty, top_p, top_k, seed));

@@ -27,6 +27,7 @@ struct GenState {
   uint8_t* mask;     // [B, max_len]
   uint32_t* seen0;   // repetition-penalty bitmaps over audio ids: channel 1 / channels 2..n_vq
   uint32_t* seen_rest;
+  uint32_t* full_hist;   // [B][65536] counting-sort scratch of the full-vocabulary text sampler (sampling_full.cuh), or null
   int B, C, max_len, bitmap_words;
 };
 
@@ -64,9 +65,9 @@ struct LocalState {
 };
 size_t local_state_bytes(int B, int C, int max_len, int audio_head);
 LocalState local_state_carve(void* buf, int B, int C, int max_len, int audio_head, int64_t* gen_ids);
-int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s);
+int local_init(const LocalState& st, const int64_t* input_ids, int S0, cudaStream_t s, const uint8_t* attn_mask = nullptr);
 int local_sample(const LocalState& st, const bf16* logits, int V, int c, int do_sample, float temperature, float penalty,
-                 float top_p, int top_k, unsigned seed, cudaStream_t s);
+                 float top_p, int top_k, unsigned seed, cudaStream_t s, uint32_t* full_hist = nullptr);
 int local_commit(const LocalState& st, int eos, int pad_code, int n_channels_sampled, cudaStream_t s);
 
 // Device-resident state of one MOSS-TTS-Realtime session (reference streaming_mossttsrealtime.py:63-86: attention_mask,
@@ -96,9 +97,11 @@ int rt_sample(const RtState& st, const bf16* logits, int V, int c, int do_sample
               float top_p, int top_k, unsigned seed, const int* step_dev, int step_host, int64_t* out, cudaStream_t s);
 int rt_commit(const RtState& st, int eos, int advance_len, int64_t* tokens_out, cudaStream_t s);
 
+// scratch: N * sample_full_scratch_bytes() bytes, needed only when do_sample and (top_k <= 0 or top_k > kMaxTopK)
+size_t sample_full_scratch_bytes();
 int sample_tokens(const bf16* logits, long long ld, int N, int V, float temperature, const uint32_t* prev_bitmap,
                   float penalty, float top_p, int top_k, int do_sample, const float* uniforms, int64_t* out,
-                  cudaStream_t s);
+                  cudaStream_t s, void* scratch = nullptr, long long scratch_bytes = 0);
 int find_last_equal(const int64_t* t, int B, int S, long long ld, long long value, int64_t* out, cudaStream_t s);
 int apply_delay_pattern(const int64_t* codes, int T, int n, long long pad, int64_t* out, cudaStream_t s);
 int apply_de_delay_pattern(const int64_t* delayed, int Td, int n, int64_t* out, cudaStream_t s);

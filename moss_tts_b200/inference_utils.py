@@ -3,7 +3,9 @@
 `sample_token` keeps the reference's argument names.  Differences that are part of the
 contract: logits must be bf16 CUDA tensors; the random draw is an
 inverse-CDF over (prob desc, index asc) driven by `uniforms` (or a seeded generator) rather
-than torch.multinomial's Philox stream; top_k must be in [1, 1024] when sampling (top_k=None: rows of at most 1024).
+than torch.multinomial's Philox stream.  Any top_k is accepted: 1..1024 runs on the shared-memory candidate list,
+`top_k=None` / `<= 0` (no filter, reference :135) and `top_k > 1024` on the full-vocabulary counting sort
+(csrc/sampling_full.cuh, mt_sample_tokens_full).
 """
 from __future__ import annotations
 
@@ -31,12 +33,17 @@ def _bitmap_from_tokens(prev_tokens: torch.Tensor, vocab: int) -> torch.Tensor:
 def _launch(x: torch.Tensor, bitmap, repetition_penalty, top_p, top_k, do_sample, uniforms, out: torch.Tensor) -> None:
     """x [N, V] bf16 (row stride x.stride(0), unit column stride) -> out [N] int64 (contiguous)."""
     N, V = x.shape
+    k = int(top_k or 0)
+    scratch = None
+    if do_sample and (k > 1024 or (k <= 0 and V > 1024)):
+        scratch = torch.empty(L.lib().mt_sample_full_scratch_bytes(N), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        L.check(L.lib().mt_sample_tokens(L.ptr(x), C.c_longlong(x.stride(0)), N, V, C.c_float(1.0), L.ptr(bitmap),
-                                         C.c_float(repetition_penalty if bitmap is not None else 1.0),
-                                         C.c_float(1.0 if top_p is None else top_p), int(top_k or 0), int(do_sample),
-                                         L.ptr(uniforms if do_sample else None), L.ptr(out), L.stream_ptr(x.device)),
-                "mt_sample_tokens")
+        L.check(L.lib().mt_sample_tokens_full(L.ptr(x), C.c_longlong(x.stride(0)), N, V, C.c_float(1.0), L.ptr(bitmap),
+                                              C.c_float(repetition_penalty if bitmap is not None else 1.0),
+                                              C.c_float(1.0 if top_p is None else top_p), k, int(do_sample),
+                                              L.ptr(uniforms if do_sample else None), L.ptr(out), L.ptr(scratch),
+                                              C.c_longlong(0 if scratch is None else scratch.numel()),
+                                              L.stream_ptr(x.device)), "mt_sample_tokens_full")
 
 
 def sample_token(logits: torch.Tensor, prev_tokens: Optional[torch.Tensor] = None, repetition_penalty: float = 1.0,
@@ -48,7 +55,8 @@ def sample_token(logits: torch.Tensor, prev_tokens: Optional[torch.Tensor] = Non
     if not logits.is_cuda:
         raise L.MossTTSNativeError("sample_token: logits must live on a CUDA device (no CPU path)")
     if logits.dtype != torch.bfloat16:
-        raise NotImplementedError("sample_token: the CUDA sampler takes bf16 logits (the model dtype)")
+        raise NotImplementedError("sample_token: the CUDA sampler takes bf16 logits (the model dtype; its rounding points are "
+                                  "the reference's bf16 ones)")
     shape = logits.shape[:-1]
     V = logits.shape[-1]
     N = 1
@@ -62,10 +70,7 @@ def sample_token(logits: torch.Tensor, prev_tokens: Optional[torch.Tensor] = Non
         raise AssertionError("Delay Pattern audio logits must be [B, H, V]")        # the reference's assert (:90)
     if do_sample:
         if top_k is None or top_k <= 0:
-            # no top-k filter (:135): keeping every entry of a row of at most 1024 IS no filter
-            if V > 1024:
-                raise NotImplementedError("sample_token: sampling without top_k needs V <= 1024 (full-vocabulary sort: not built)")
-            top_k = V
+            top_k = 0                                # no top-k filter (:135)
         if uniforms is None:
             uniforms = torch.rand(N, device=logits.device, generator=generator, dtype=torch.float32)
         uniforms = uniforms.to(device=logits.device, dtype=torch.float32).reshape(-1).contiguous()

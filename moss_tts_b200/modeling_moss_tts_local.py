@@ -7,9 +7,11 @@ reference's generation_config fields (`max_new_tokens`, `n_vq_for_inference`, `d
 libmosstts_sm100 (include/mosstts.h, mt_local_*).  No CPU fallback.
 
 Differences that are stated rather than hidden
-  * prompts must be un-padded (attention mask all ones): the reference's `_sample` extends whatever mask it is
-    given with ones and derives positions from the column index, so a left-padded batch attends to its padding
-    rows; that behaviour is not reproduced, it is rejected.
+  * left-padded prompts: the padding is masked out of the attention keys and every generated frame is visible (HF's
+    generation loop extends the mask it is given with ones).  Positions are the column index where HF derives them
+    from the mask's cumulative sum — a per-row constant shift rotary attention does not see (fp32 goldens with HF's
+    position_ids are reproduced exactly, tests/test_oracle_local.py).  Masks with holes other than left padding are
+    rejected (`ValueError`).
   * the local transformer is causal (what `attn_implementation="sdpa"` gives, the README's setting).
   * sampled channels need 1 <= top_k <= 1024.  `top_k=None` is accepted on audio channels (1025 logits of which
     the pad code is -inf, so top_k=1024 keeps every candidate) and rejected on the text channel.
@@ -186,9 +188,21 @@ class MossTTSLocalModel:
             pass
 
     # ---- reference surface ----------------------------------------------------------------------
+    def _mask(self, attention_mask, B, S0):
+        if attention_mask is None:
+            return None
+        m = attention_mask.to(torch.bool)
+        if tuple(m.shape) != (B, S0):
+            raise ValueError(f"attention_mask must be (batch_size, sequence_length) = ({B}, {S0})")
+        if bool(m.all()):
+            return None
+        if not bool((m[:, 1:] >= m[:, :-1]).all()) or not bool(m[:, -1].all()):
+            raise ValueError("attention_mask must be left padding (zeros only before the first real token)")
+        return m.to(device=self.device, dtype=torch.uint8).contiguous()
+
     @torch.inference_mode()
     def frame_logits(self, input_ids: torch.Tensor, frame_ids: torch.Tensor,
-                     n_vq_for_inference: Optional[int] = None) -> List[torch.Tensor]:
+                     n_vq_for_inference: Optional[int] = None, attention_mask=None) -> List[torch.Tensor]:
         """Teacher-forced logits of the frame that follows `input_ids` [B,S,1+n_vq] when the depth loop is fed
         `frame_ids` [B,1+n_vq] (one iteration of the reference loop :379-450): list of [B, V_c] bf16 tensors."""
         c = self.config
@@ -203,8 +217,9 @@ class MossTTSLocalModel:
         n_ch = min(C_, 1 + n_inf)
         ldv = max(c.vocab_size, c.audio_head_size)
         out = torch.empty(n_ch, B, ldv, dtype=torch.bfloat16, device=self.device)
+        am = self._mask(attention_mask, B, S0)
         with torch.cuda.device(self.device):
-            L.check(L.lib().mt_local_forward(self._engine, L.ptr(ids), B, S0, n_inf, L.ptr(fr), L.ptr(out),
+            L.check(L.lib().mt_local_forward(self._engine, L.ptr(ids), L.ptr(am), B, S0, n_inf, L.ptr(fr), L.ptr(out),
                                              C.c_longlong(ldv), L.stream_ptr(self.device)), "mt_local_forward")
         return [out[ch, :, :(c.vocab_size if ch == 0 else c.audio_head_size)] for ch in range(n_ch)]
 
@@ -220,8 +235,6 @@ class MossTTSLocalModel:
         C_ = c.n_vq + 1
         if input_ids.dim() != 3 or input_ids.shape[-1] != C_:
             raise ValueError("`Input_ids`'s shape should be exactly (batch_size, sequence_length, 1 + n_vq).")
-        if attention_mask is not None and not bool(attention_mask.to(torch.bool).all()):
-            raise NotImplementedError("MossTTSLocalModel.generate supports un-padded prompts only (attention mask all ones)")
 
         def pick(name, given, default):
             if given is not None:
@@ -256,8 +269,9 @@ class MossTTSLocalModel:
         max_len = S0 + max_new_tokens
         self._ensure_engine(B, max_len, B * S0)
         gen = torch.empty(B, max_len, C_, dtype=torch.int64, device=self.device)
+        am = self._mask(attention_mask, B, S0)
         gp = L.LocalGenParamsC(max_new_tokens, n_inf, -1 if eos_token_id is None else int(eos_token_id), ds, tm, tp, tk, rp,
-                               seed & 0xFFFFFFFF, int(use_cuda_graph), check_stop_every)
+                               seed & 0xFFFFFFFF, int(use_cuda_graph), check_stop_every, None if am is None else am.data_ptr())
         n_steps = C.c_int(0)
         step_ms = (C.c_float * max(1, max_new_tokens))() if record_step_times else None
         with torch.cuda.device(self.device):

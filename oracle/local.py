@@ -19,8 +19,10 @@ Notes that matter for parity
     `attn_implementation="sdpa"` that is causal attention, which is what is restated here.  The prefix is
     recomputed every depth step like the reference (`use_cache=False`, :205); a causal stack makes that
     equal to keeping the prefix K/V, which is what the CUDA path does.
-  * positions of the global backbone are the column index; only un-padded prompts (mask all ones) are
-    supported, like the CUDA path.
+  * left-padded prompts: HF's generation loop honours the attention mask it is given (padding keys are masked),
+    extends it with ones for every new frame and derives position_ids from its cumulative sum; the restatement
+    masks the padding and keeps column-index positions (a per-row constant shift, invisible to rotary attention
+    up to the rounding of the cos/sin tables).
   * sampling: greedy channels use no processor at all (:361-362).  Sampled channels apply penalty ->
     temperature, then the same top-k / top-p / inverse-CDF rules as oracle/sampling.py (lower index wins
     top-k ties, where HF's TopKLogitsWarper keeps every tie of the k-th value).
@@ -113,13 +115,18 @@ class OracleLocal:
             x = x + self.w[f"model.embedding_list.{i}.weight"][ids[..., i]]
         return x
 
-    def global_forward(self, ids, cache, past_len, n_vq_inf):
+    def global_forward(self, ids, cache, past_len, n_vq_inf, attention_mask=None):
+        """attention_mask [B, past_len + T] bool or None: left padding is masked out of the keys (HF extends the mask it
+        is given with ones, GenerationMixin._update_model_kwargs_for_generation).  Positions stay the column index: HF
+        derives them from the mask's cumulative sum, a per-row constant shift that rotary attention does not see."""
         B, T, _ = ids.shape
         qpos = torch.arange(T) + past_len
         ang = qpos.float()[:, None] * self.inv_freq[None, :]
         ang = torch.cat([ang, ang], dim=-1)
         rope = (ang.cos().to(self.dtype), ang.sin().to(self.dtype))
         allowed = (torch.arange(past_len + T)[None, :] <= qpos[:, None])[None, None]
+        if attention_mask is not None:
+            allowed = allowed & attention_mask[:, None, None, :past_len + T].bool()
         x = self.embed(ids, n_vq_inf)
         h = self.stack("model.language_model.", self.cfg.num_layers, x, allowed, rope, cache,
                        "model.language_model.norm.weight")
@@ -161,7 +168,8 @@ class OracleLocal:
     @torch.no_grad()
     def generate(self, input_ids, max_new_tokens: int, *, n_vq_for_inference: Optional[int] = None,
                  do_samples: Optional[Sequence[bool]] = None, layers: Optional[Sequence[dict]] = None,
-                 eos_token_id: Optional[int] = 151653, seed: int = 0, return_trace: bool = False):
+                 eos_token_id: Optional[int] = 151653, seed: int = 0, return_trace: bool = False,
+                 attention_mask: Optional[torch.Tensor] = None):
         """One frame per iteration (:379-450).  Returns [(start_length, ids[start_idx:])] (:466-475)."""
         cfg = self.cfg
         B, S0, C = input_ids.shape
@@ -175,7 +183,10 @@ class OracleLocal:
         trace = []
         for step in range(max_new_tokens):
             past_len = gen.shape[1] - cur.shape[1]
-            h_glob = self.global_forward(cur, cache, past_len, n_inf)
+            am = None
+            if attention_mask is not None:
+                am = torch.cat([attention_mask.bool(), torch.ones(B, gen.shape[1] - S0, dtype=torch.bool)], dim=1)
+            h_glob = self.global_forward(cur, cache, past_len, n_inf, am)
             cur_in = self.swiglu(h_glob, "speech_embedding_to_local_mlp.")
             local_in = torch.zeros(B, 0, cfg.local_hidden_size, dtype=self.dtype)
             nxt = torch.zeros(B, C, dtype=torch.int64)

@@ -59,7 +59,7 @@ def build_ref_local(cfg: LocalConfig, weights, dtype):
 
 
 @torch.no_grad()
-def ref_generate(model, input_ids, max_new_tokens, eos_token_id):
+def ref_generate(model, input_ids, max_new_tokens, eos_token_id, attention_mask=None):
     """CustomMixin._sample :379-450, greedy, executed by the reference's modules."""
     from transformers import DynamicCache
     cfg = model.config
@@ -72,8 +72,16 @@ def ref_generate(model, input_ids, max_new_tokens, eos_token_id):
     top2 = []           # per frame [C, B, 2] values / indices of the two largest logits (near-tie evidence)
     for _ in range(max_new_tokens):
         past = ids.shape[1] - cur.shape[1]
-        pos = torch.arange(past, ids.shape[1])[None].expand(B, -1)
-        out = model.model(input_ids=cur, attention_mask=torch.ones(B, ids.shape[1], dtype=torch.long),
+        if attention_mask is None:
+            am = torch.ones(B, ids.shape[1], dtype=torch.long)
+            pos = torch.arange(past, ids.shape[1])[None].expand(B, -1)
+        else:
+            # what HF's generation loop feeds a left-padded batch: the given mask extended with ones
+            # (_update_model_kwargs_for_generation) and position_ids = cumsum(mask) - 1, 1 on the padding
+            # (prepare_inputs_for_generation)
+            am = torch.cat([attention_mask.long(), torch.ones(B, ids.shape[1] - S0, dtype=torch.long)], dim=1)
+            pos = (am.cumsum(-1) - 1).masked_fill(am == 0, 1)[:, past:]
+        out = model.model(input_ids=cur, attention_mask=am,
                           position_ids=pos, past_key_values=cache, use_cache=True, output_hidden_states=True,
                           return_dict=True, n_vq_for_inference=n_inf)
         g = out.hidden_states[-1][:, -1, :]
@@ -106,13 +114,14 @@ def ref_generate(model, input_ids, max_new_tokens, eos_token_id):
     return ids, torch.stack([t[0] for t in top2]), torch.stack([t[1] for t in top2])
 
 
-def golden_local(name, cfg, dtype, *, batch, prompt_len, steps, seed):
+def golden_local(name, cfg, dtype, *, batch, prompt_len, steps, seed, left_pad=None):
     w = make_local_weights(cfg, seed=seed)
     eos = cfg.audio_end_token_id
     model = build_ref_local(cfg, w, dtype)
-    ids, _ = make_prompt(cfg, batch, prompt_len, seed=seed)
-    out, tv, ti = ref_generate(model, ids, steps, eos)
+    ids, mask = make_prompt(cfg, batch, prompt_len, seed=seed, left_pad=left_pad)
+    out, tv, ti = ref_generate(model, ids, steps, eos, mask if left_pad is not None else None)
     np.savez_compressed(os.path.join(OUT, name + ".npz"), input_ids=ids.numpy(), gen_ids=out.numpy(),
+                        attention_mask=mask.numpy(),
                         top2_val=tv.numpy(), top2_idx=ti.numpy(),
                         meta=json.dumps({"cfg": cfg.to_dict(), "dtype": str(dtype), "seed": seed, "steps": steps,
                                          "torch": torch.__version__,
@@ -123,10 +132,20 @@ def golden_local(name, cfg, dtype, *, batch, prompt_len, steps, seed):
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    only = sys.argv[1:]
+    if only:
+        global golden_local
+        _all = golden_local
+        golden_local = lambda name, *a, **k: _all(name, *a, **k) if name in only else None   # noqa: E731
     golden_local("local_tiny_f32", LocalConfig.tiny(4), torch.float32, batch=2, prompt_len=10, steps=8, seed=3)
     golden_local("local_tiny_bf16", LocalConfig.tiny(4), torch.bfloat16, batch=2, prompt_len=10, steps=8, seed=3)
     golden_local("local_mid_f32", LocalConfig.mid(8), torch.float32, batch=2, prompt_len=12, steps=6, seed=5)
     golden_local("local_mid_bf16", LocalConfig.mid(8), torch.bfloat16, batch=2, prompt_len=12, steps=6, seed=5)
+    # left-padded prompts (rows of 12, 9 and 7 real tokens)
+    golden_local("local_tiny_pad_f32", LocalConfig.tiny(4), torch.float32, batch=3, prompt_len=12, steps=6, seed=9,
+                 left_pad=[0, 3, 5])
+    golden_local("local_tiny_pad_bf16", LocalConfig.tiny(4), torch.bfloat16, batch=3, prompt_len=12, steps=6, seed=9,
+                 left_pad=[0, 3, 5])
 
 
 if __name__ == "__main__":

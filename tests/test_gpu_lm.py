@@ -208,8 +208,37 @@ def test_generate_sampling_without_audio_top_k_follows_oracle():
     for (sl, g_), (osl, og) in zip(out, o_out):
         assert sl == osl and torch.equal(g_.cpu()[0], og[0])
         assert int(g_[:, 1:].max()) <= 1024 and int(g_[:, 1:].min()) >= 0
-    with pytest.raises(NotImplementedError):
-        model.generate(ids, mask, max_new_tokens=4, text_temperature=1.0, text_top_k=None)     # full-vocabulary sort: not built
+
+
+@pytest.mark.parametrize("text_top_k,text_top_p", [(None, 0.9), (None, 1.0), (5000, 0.95)])
+def test_generate_text_sampling_without_top_k_follows_oracle(text_top_k, text_top_p):
+    """text_top_k=None / > 1024 (reference inference_utils.py:135 skips apply_top_k): the text channel samples from the
+    whole 151,936-entry row (full-vocabulary counting sort).  Prompts that do NOT end inside an audio span, so the text
+    row is really sampled (mode 1 bans only); compared step by step with the oracle driven by the same uniforms."""
+    cfg = LMConfig.tiny(n_vq=4)
+    w = make_lm_weights(cfg, seed=5)
+    model = MossTTSDelayModel(cfg, w, device=DEV)
+    oracle = OracleLM(cfg, w, torch.bfloat16)
+    ids, mask = make_prompt(cfg, 3, 12, seed=6)
+    ids[:, -1, 0] = torch.tensor([1234, 77, 4242])           # plain text last: no audio continuation
+    kw = dict(max_new_tokens=8, text_temperature=1.3, text_top_k=text_top_k, text_top_p=text_top_p,
+              audio_temperature=0, seed=11)
+    out = model.generate(ids, mask, **kw)
+    o_out = oracle.generate(ids, mask, **kw)
+    same = total = 0
+    for (sl, g_), (osl, og) in zip(out, o_out):
+        assert sl == osl
+        g_ = g_.cpu()
+        n = min(g_.shape[0], og.shape[0])
+        # rows agree until the first differing text token (after which the contexts differ)
+        diff = (g_[:n, 0] != og[:n, 0]).nonzero()
+        upto = int(diff[0]) if len(diff) else n
+        same += upto
+        total += n
+        assert upto >= sl + 1, "the first sampled text token must match the oracle's"
+        assert int(g_[:, 0].max()) < cfg.vocab_size
+    print(f"[text sampling top_k={text_top_k} top_p={text_top_p}] rows identical up to first divergence: {same}/{total}")
+    assert same >= 0.6 * total
 
 
 def test_get_input_embeddings_bit_exact():

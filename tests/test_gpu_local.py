@@ -197,8 +197,50 @@ def test_local_rejects_bad_inputs():
     with pytest.raises(ValueError):
         model.generate(torch.zeros(1, 4, 3, dtype=torch.int64))
     mask = torch.ones(2, 8, dtype=torch.bool)
-    mask[1, :2] = False
-    with pytest.raises(NotImplementedError):
+    mask[1, 3] = False                             # a hole that is not left padding
+    with pytest.raises(ValueError, match="left padding"):
         model.generate(ids, mask, max_new_tokens=2)
-    with pytest.raises(NotImplementedError):       # sampled text channel without top_k
-        model.generate(ids, max_new_tokens=2, do_samples=[True] + [False] * cfg.n_vq, layers=[{} for _ in range(5)])
+    # sampled text channel without top_k: the full-vocabulary sampler (no filter, like HF without a TopKLogitsWarper)
+    out = model.generate(ids, max_new_tokens=2, do_samples=[True] + [False] * cfg.n_vq, layers=[{} for _ in range(5)], seed=3)
+    o_out = OracleLocal(cfg, make_local_weights(cfg, seed=1), torch.bfloat16).generate(
+        ids, 2, do_samples=[True] + [False] * cfg.n_vq, layers=[{} for _ in range(5)], seed=3)
+    for (sl, a), (osl, b_) in zip(out, o_out):
+        assert sl == osl and int(a[sl + 1, 0]) == int(b_[sl + 1, 0])        # first sampled text token = the oracle's
+
+
+def test_local_left_padded_prompts_match_oracle_and_golden():
+    """a15: a left-padded batch (rows of 12, 9 and 7 real tokens).  The reference's modules were run with the mask HF's
+    generation loop builds (given mask + ones) and its cumulative-sum position_ids (tests/golden/local_tiny_pad_*.npz);
+    the CUDA path masks the padding in prefill and decode attention.  Greedy ids vs the oracle and vs the reference's:
+    exact or first divergence a near-tie; teacher-forced logits of frame 0 within 2e-2; padding really changes the result."""
+    g, meta, cfg = load_local_golden("local_tiny_pad_bf16")
+    w = make_local_weights(cfg, seed=meta["seed"])
+    model = MossTTSLocalModel(cfg, w, device=DEV)
+    ids, mask = torch.from_numpy(g["input_ids"]), torch.from_numpy(g["attention_mask"])
+    S0 = ids.shape[1]
+    kw = dict(max_new_tokens=meta["steps"], eos_token_id=cfg.audio_end_token_id)
+    out = model.generate(ids, mask, **kw)
+    o_out, trace = OracleLocal(cfg, w, torch.bfloat16).generate(ids, meta["steps"], eos_token_id=cfg.audio_end_token_id,
+                                                                return_trace=True, attention_mask=mask)
+    _check(out, o_out, trace, "local_tiny_pad_bf16")
+    for b, (sl, mine) in enumerate(out):
+        mine = mine.cpu().numpy()[sl + 1:]
+        ref = g["gen_ids"][b, S0:]
+        bad = sorted(map(tuple, np.argwhere(mine != ref)))
+        if bad:
+            f, c = bad[0]
+            v = g["top2_val"][f, c, b]
+            assert (v[0] - v[1]) <= 2 * bf16_ulp(v[0]), ("vs reference", b, f, c, v)
+    frame = torch.from_numpy(g["gen_ids"])[:, S0]
+    lg = model.frame_logits(ids, frame, attention_mask=mask)
+    want = OracleLocal(cfg, w, torch.bfloat16)
+    h = want.global_forward(ids, [None] * cfg.num_layers, 0, cfg.n_vq, mask)
+    cur = want.swiglu(h, "speech_embedding_to_local_mlp.")
+    ref0 = want.channel_logits(want.local_forward(cur[:, None, :]), 0)
+    assert (lg[0].float().cpu() - ref0.float()).abs().max().item() <= LOGIT_TOL
+    no_mask = model.frame_logits(ids, frame)
+    assert (no_mask[0][1:].float() - lg[0][1:].float()).abs().max().item() > 1e-2        # padded rows differ without the mask
+    assert torch.equal(no_mask[0][0], lg[0][0])                                          # the un-padded row does not
+    with pytest.raises(ValueError, match="left padding"):
+        bad_mask = mask.clone(); bad_mask[1, 6] = False
+        model.generate(ids, bad_mask, **kw)

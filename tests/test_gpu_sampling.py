@@ -58,6 +58,56 @@ def test_sampling_matches_oracle_draws(V, k, p):
     assert match / total >= 0.97, (match, total)
 
 
+@pytest.mark.parametrize("V,k,p", [(151936, None, 0.9), (151936, None, 1.0), (151936, 0, 0.5), (151936, 5000, 0.95),
+                                   (151936, 1025, 1.0), (4000, 2000, 0.8), (2050, None, 0.7)])
+def test_full_vocabulary_sampling_matches_oracle(V, k, p):
+    """a5: sample_token with top_k None / <= 0 (no filter, reference :135) or top_k > 1024: the counting-sort sampler
+    (csrc/sampling_full.cuh) against the oracle's full sort with the same uniforms.  u close to 1 draws the LAST kept
+    candidate, which pins the top-k / top-p cut itself; a draw may differ from the oracle's only by landing on a
+    neighbouring candidate of the same sorted order (bucket sums vs element-by-element fp32 sums)."""
+    n = 6
+    x = _rows(n, V, 77, scale=2.0)
+    g = torch.Generator().manual_seed(13)
+    match = total = 0
+    for rep in range(3):
+        u = torch.rand(n, generator=g)
+        if rep == 2:
+            u = torch.tensor([0.0, 0.9999999, 0.99999, 0.5, 1e-7, 0.999])
+        got = sample_token(x.to(DEV), top_p=p, top_k=k, do_sample=True, uniforms=u.to(DEV)).cpu()
+        for r in range(n):
+            cand, probs = S.filtered_distribution(x[r], k, p)
+            want = S.draw(cand, probs, float(u[r]))
+            total += 1
+            if int(got[r]) == want:
+                match += 1
+                continue
+            pos = {int(c): j for j, c in enumerate(cand.tolist())}
+            assert int(got[r]) in pos, (r, "outside the filtered support")
+            assert abs(pos[int(got[r])] - pos[want]) <= 2, (r, pos[int(got[r])], pos[want], len(cand))
+    print(f"[full-vocabulary sampling V={V} k={k} p={p}] {match}/{total} draws identical to the oracle")
+    assert match / total >= 0.9, (match, total)
+
+
+def test_full_vocabulary_sampling_with_penalty_and_ties():
+    """Repetition penalty (non-monotone transform) and massive ties (a quantised row) through the counting sort."""
+    V = 30000
+    g = torch.Generator().manual_seed(3)
+    x = (torch.randint(-8, 9, (4, V), generator=g).float() * 0.25).to(torch.bfloat16)       # 33 distinct values
+    prev = torch.randint(0, V, (4, 50), generator=g)
+    u = torch.tensor([0.3, 0.77, 0.001, 0.9999])
+    ids = S.penalty_set(prev)
+    for k, p in ((None, 0.6), (3000, 1.0), (None, 1.0)):
+        got = sample_token(x.to(DEV), prev_tokens=prev.to(DEV), repetition_penalty=1.5, top_k=k, top_p=p, do_sample=True,
+                           uniforms=u.to(DEV)).cpu()
+        for r in range(4):
+            row = S.apply_penalty_row(x[r], ids, 1.5)
+            cand, probs = S.filtered_distribution(row, k, p)
+            want = S.draw(cand, probs, float(u[r]))
+            pos = {int(c): j for j, c in enumerate(cand.tolist())}
+            assert int(got[r]) in pos
+            assert abs(pos[int(got[r])] - pos[want]) <= 2, (k, p, r, pos[int(got[r])], pos[want], len(cand))
+
+
 def test_sampling_distribution():
     """Empirical frequencies of one row follow the filtered distribution."""
     x = _rows(1, 1025, 21, scale=1.5)

@@ -92,3 +92,33 @@ def test_local_eos_and_partial_channels():
         assert (r0[1:, 0] == tok0).all() and (r0[1:, 1:] == cfg.audio_pad_code).all()
     part = o.generate(ids, 2, n_vq_for_inference=2, eos_token_id=None)
     assert (part[0][1][-2:, 3:] == 0).all()
+
+
+def test_local_oracle_left_padded_prompts():
+    """Left-padded batch (rows of 12, 9 and 7 real tokens): the reference modules were fed the mask extended with ones and
+    HF's cumulative-sum position_ids; the oracle masks the padding and keeps column positions.  fp32: ids exact, top
+    logits <= 2e-4 (the per-row position shift is invisible to rotary attention); bf16: exact or near-tie."""
+    g, meta, cfg = load_local_golden("local_tiny_pad_f32")
+    w = make_local_weights(cfg, seed=meta["seed"])
+    ids, mask = torch.from_numpy(g["input_ids"]), torch.from_numpy(g["attention_mask"])
+    assert not mask.all() and mask[:, -1].all()
+    out, trace = OracleLocal(cfg, w, torch.float32).generate(ids, meta["steps"], eos_token_id=cfg.audio_end_token_id,
+                                                             return_trace=True, attention_mask=mask)
+    S0 = ids.shape[1]
+    for b, (sl, rows) in enumerate(out):
+        assert np.array_equal(rows.numpy(), g["gen_ids"][b, S0 - sl - 1:]), b
+    for f, step in enumerate(trace):
+        for c, lg in enumerate(step):
+            np.testing.assert_allclose(lg.float().max(dim=-1).values.numpy(), g["top2_val"][f, c, :, 0], rtol=0, atol=2e-4)
+    # and the padding matters: ignoring the mask changes the logits
+    out2, trace2 = OracleLocal(cfg, w, torch.float32).generate(ids, 1, eos_token_id=cfg.audio_end_token_id, return_trace=True)
+    assert (trace2[0][0][1].float() - trace[0][0][1].float()).abs().max() > 1e-3
+    gb, metab, _ = load_local_golden("local_tiny_pad_bf16")
+    outb = OracleLocal(cfg, w, torch.bfloat16).generate(ids, metab["steps"], eos_token_id=cfg.audio_end_token_id,
+                                                        attention_mask=mask)
+    for b, (sl, rows) in enumerate(outb):
+        d = first_divergence(rows.numpy(), gb["gen_ids"][b, S0 - sl - 1:], sl + 1)
+        if d is not None:
+            f, c = d
+            v = gb["top2_val"][f, c, b]
+            assert (v[0] - v[1]) <= 2 * bf16_ulp(v[0]), (b, f, c, v)
