@@ -79,6 +79,9 @@ long long mt_debug_set_trace(void* buf, long long words);
  * slots[stage][0..3] = {LayerNorm output, q|k|v, attention output, GELU output} (NaN if any NaN).  NULL switches it off.
  * Used by the tests to prove the operands stay inside the fp16 range (65504) through all 68 released layers. */
 int mt_codec_debug_set_absmax(float* slots);
+/* Attention kernel of the fp16-operand codec path: 0 (default) = tcgen05 / TMEM / TMA FlashAttention (codec_attn_tc5.cu),
+ * 1 = the mma.sync FlashAttention-2 kernel (codec_attn.cu).  For A/B measurements and cross-checks; process-wide. */
+int mt_codec_debug_set_attention(int mode);
 
 /* ------------------------------------------------------------------------------------------
  * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:

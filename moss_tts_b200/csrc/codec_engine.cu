@@ -23,6 +23,9 @@ namespace mt {
 // mt_codec_debug_set_absmax: device floats [MT_CODEC_MAX_STAGES][4] = max |value| of the fp16 operands
 // {LayerNorm output, q|k|v, attention output, GELU output} of every stage, over all layers and launches since it was set
 static float* g_absmax = nullptr;
+// mt_codec_debug_set_attention: 0 = tcgen05 attention (codec_attn_tc5.cu, the product path), 1 = the mma.sync FlashAttention-2
+// kernel (codec_attn.cu) for A/B measurements and as a cross-check of the tensor-memory kernel
+static int g_attn_mode = 0;
 
 struct StageDims { long long x, qkv, ff, y; };
 
@@ -101,6 +104,7 @@ extern "C" int mt_codec_create(const mt_codec_config* cfg, const mt_codec_weight
 }
 extern "C" int mt_codec_destroy(mt_codec* h) { delete h; return MT_OK; }
 extern "C" int mt_codec_debug_set_absmax(float* slots) { mt::g_absmax = slots; return MT_OK; }
+extern "C" int mt_codec_debug_set_attention(int mode) { mt::g_attn_mode = mode; return MT_OK; }
 
 extern "C" int mt_codec_workspace_bytes(const mt_codec* h, int B, int T, long long* bytes) {
   MT_CHECK(h && bytes, "null argument");
@@ -162,6 +166,8 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
       __half* lr = ring + l * ring_layer_halves;
       MT_TRY(codec_kv_append_f16(qkv, lr, nb, static_cast<int>(Ts), heads, c.context[st], pos0, y, s));
       MT_TRY(codec_attention_ring_f16(qkv, lr, hbuf, nb, static_cast<int>(Ts), heads, c.context[st], pos0, s, y));
+    } else if (a16 && g_attn_mode == 0) {
+      MT_TRY(codec_attention_tc5(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
     } else if (a16) {
       MT_TRY(codec_attention_f16(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
     } else if (simt_attn || !table_fits) {

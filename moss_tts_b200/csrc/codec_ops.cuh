@@ -25,6 +25,11 @@ int codec_attention_tc(const float* qkv, float* out, int B, int T, int heads, in
 // fp16 flavour (codec_attn.cu): qkv [B*T, 3*heads*64] and out [B*T, heads*64] are IEEE half; RoPE table required
 int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk,
                         cudaStream_t s, const float* rope_table);
+// tcgen05 / TMEM / TMA flavour (codec_attn_tc5.cu): q and k of `qkv` are rotated IN PLACE first, then S = Q.K^T and P.V run
+// on the 5th-generation tensor cores.  The product path of the one-pass decode / encode; codec_attention_f16 stays the
+// kernel of the incremental ring-cache streaming path and the A/B cross-check (mt_codec_debug_set_attention(1)).
+int codec_attention_tc5(void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk, cudaStream_t s,
+                        const float* rope_table);
 // Streaming decode (RingKVCache :413-480, MHAState :488-499).  ring: one layer's cache [B][cap][2][heads*64] half, slot =
 // position % cap, K stored AFTER RoPE (as the reference caches it).  kv_append rotates the new tokens' keys (table row t =
 // position pos0 + t) and writes k, v into their slots; the attention then reads q from qkv (rotated on the way in) and

@@ -13,8 +13,8 @@ Differences that are stated rather than hidden
     position_ids are reproduced exactly, tests/test_oracle_local.py).  Masks with holes other than left padding are
     rejected (`ValueError`).
   * the local transformer is causal (what `attn_implementation="sdpa"` gives, the README's setting).
-  * sampled channels need 1 <= top_k <= 1024.  `top_k=None` is accepted on audio channels (1025 logits of which
-    the pad code is -inf, so top_k=1024 keeps every candidate) and rejected on the text channel.
+  * `top_k=None` (no TopKLogitsWarper): audio channels keep their 1024 real codes (the pad code is -inf); the text
+    channel, or any `top_k > 1024`, runs the full-vocabulary counting-sort sampler (csrc/sampling_full.cuh).
   * top-k ties: lower index wins (HF keeps every tie of the k-th value).
 """
 from __future__ import annotations

@@ -81,7 +81,13 @@ def filtered_distribution(row: torch.Tensor, top_k: Optional[int], top_p: Option
         # softmax in the row dtype (F.softmax on bf16 computes in fp32 and rounds once)
         probs = torch.softmax(logits.float(), dim=-1).to(dtype)
         # candidates are already sorted descending by logit == descending by prob
-        csum = torch.cumsum(probs.float(), dim=-1).to(dtype)      # fp32 accumulate, rounded output
+        # fp32 accumulate, rounded output.  Beyond the 1,024 candidates a top-k filter leaves (no top-k: the whole
+        # vocabulary) a sequential fp32 sum stagnates (adding 1e-8 to 0.9 is a no-op), which torch's own scans avoid
+        # on the GPU; there the restatement accumulates in float64, i.e. the sums are the true ones.
+        if probs.numel() > 1024:
+            csum = torch.cumsum(probs.double(), dim=-1).float().to(dtype)
+        else:
+            csum = torch.cumsum(probs.float(), dim=-1).to(dtype)
         thr = torch.tensor(top_p, dtype=dtype)                     # python scalar is cast to the tensor dtype
         remove = csum > thr
         remove = torch.cat([torch.zeros(1, dtype=torch.bool), remove[:-1]])
@@ -93,7 +99,13 @@ def filtered_distribution(row: torch.Tensor, top_k: Optional[int], top_p: Option
 
 
 def draw(cand: np.ndarray, probs: np.ndarray, u: float) -> int:
-    """Inverse-CDF draw in candidate order with fp32 running sums."""
+    """Inverse-CDF draw in candidate order with fp32 running sums (float64 beyond 1,024 candidates, where a
+    sequential fp32 sum stagnates; the CUDA path's bucket sums approximate the true sums to fp32 rounding)."""
+    if len(probs) > 1024:
+        cum = np.cumsum(np.asarray(probs, dtype=np.float64))
+        target = float(np.float32(u)) * cum[-1]
+        j = int(np.searchsorted(cum, target, side="right"))
+        return int(cand[min(j, len(cand) - 1)])
     total = np.float32(0)
     for p in probs:
         total = np.float32(total + np.float32(p))

@@ -146,3 +146,29 @@ def test_released_stage_shapes_one_layer():
     s32 = snr_db(ref, m32.decode(codes.to(DEV)).audio.cpu())
     print(f"[codec released-width, 1 layer/stage] TF32 layer GEMMs: SNR {s32:.1f} dB")
     assert s32 >= SNR_DB
+
+
+@pytest.mark.parametrize("B,T,chunk", [(1, 9, None), (2, 33, None), (3, 70, None), (2, 131, None), (1, 300, None),
+                                       (1, 131, 0.8), (1, 300, 0.48)])
+def test_tcgen05_attention_matches_mma_sync_kernel_and_oracle(mini, B, T, chunk):
+    """The tcgen05 / TMEM attention (codec_attn_tc5.cu, the product path) against the mma.sync FlashAttention-2 kernel it
+    replaces on the same inputs, and against the oracle: one-tile and multi-tile sequences, ragged last tiles, windows
+    shorter than the sequence (mini: 12/25/50/100-token windows), chunked decode masks, several samples per launch."""
+    from moss_tts_b200 import _lib as L
+    g, cfg, w, model, oracle = mini
+    gen = torch.Generator().manual_seed(100 + T)
+    codes = torch.randint(0, cfg.codebook_size, (cfg.num_quantizers, B, T), generator=gen)
+    kw = {} if chunk is None else {"chunk_duration": chunk}
+    try:
+        L.lib().mt_codec_debug_set_attention(1)
+        old = model.decode(codes.to(DEV), **kw).audio.cpu()
+    finally:
+        L.lib().mt_codec_debug_set_attention(0)
+    new = model.decode(codes.to(DEV), **kw).audio.cpu()
+    ref, _ = oracle.decode(codes, **kw)
+    s_old, s_new, s_pair = snr_db(ref, old), snr_db(ref, new), snr_db(old, new)
+    print(f"[attention B={B} T={T} chunk={chunk}] vs oracle: mma.sync {s_old:.1f} dB, tcgen05 {s_new:.1f} dB; "
+          f"tcgen05 vs mma.sync {s_pair:.1f} dB")
+    assert torch.isfinite(new).all()
+    assert s_new >= SNR_DB and s_new >= s_old - 1.0
+    assert s_pair >= 45.0
