@@ -7,14 +7,18 @@
 // [tokens, 3d] output (one tensor map, three column offsets; 128-byte swizzle), and the probabilities go back to the tensor
 // core THROUGH tensor memory (A operand of P.V read from TMEM), never through shared memory or registers of another warp.
 //
-// CTA = 128 consecutive queries of one (sample, head), one CTA per SM:
-//   warps 0-3  softmax: thread t owns TMEM lane t = query row t.  Per 128-key tile: S (fp32, 128 columns) is read twice
-//              (row max, then p = exp2(s * scale*log2e - m)), P is written as packed halves (64 columns), and the previous
-//              tile's O_j (64 columns) is folded into the register accumulator: o = o * alpha + O_j
-//   warp 4     TMA producer: Q once, then K_j / V_j into a 3-stage ring (2 x 16 KB per stage)
-//   warp 5     TMEM allocator + MMA issuer: S_{j+1} = Q.K_{j+1}^T is issued BEFORE P_j.V_j, so the tensor core computes the
-//              next scores while the softmax warps work on the current ones (S, P and O are double-buffered: 512 columns)
-// V is consumed as the MN-major B operand (a [128 keys x 64 dims] tile is 128 keys of one 128-byte row each: exactly the
+// CTA = 128 consecutive queries of one (sample, head) walking 64-key tiles; FOUR CTAs per SM (128 TMEM columns, 48 KB of shared
+// memory, < 86 registers each), so four independent S -> softmax -> P.V chains hide each other's hand-off latencies:
+//   warps 0-3  softmax: thread t owns TMEM lane t = query row t.  Per tile: S (fp32, 64 columns) is read twice (row max, then
+//              p = exp2(s * scale*log2e - m)) and P is written as packed halves OVER the first 32 columns of S (a column is
+//              overwritten only after this thread has read it).  O stays in tensor memory: P_j.V_j ACCUMULATES into it, and
+//              the running maximum m is only raised -- with O and the row sum rescaled by 2^(m_old - m_new) through a TMEM
+//              load / store -- when a tile exceeds it by more than 2^8 (p <= 256 is harmless in half precision); the final
+//              o = O / l is exact for any such stale maximum
+//   warp 4     TMA producer: Q once, then K_j / V_j into a 2-stage ring (2 x 8 KB per stage)
+//   warp 5     TMEM allocator + MMA issuer: P_j.V_j, then S_{j+1} = Q.K_{j+1}^T (tcgen05.mma instructions of one thread execute
+//              in issue order, so S_{j+1} overwrites the S / P columns only after P_j.V_j has consumed them)
+// V is consumed as the MN-major B operand (a [64 keys x 64 dims] tile is 64 keys of one 128-byte row each: exactly the
 // canonical MN-major SWIZZLE_128B layout with an 8-key group stride of 1024 B), so no transpose of V is ever made.
 // q and k must already carry their rotary embedding (codec_rope_qk_f16 rotates them in place after the in_proj GEMM).
 //
@@ -27,13 +31,16 @@ namespace mt {
 
 namespace {
 
-constexpr int kBQ = 128, kBK = 128, kD = 64, kStages = 3;
-constexpr int kTileBytes = kBK * kD * 2;                       // 16 KB: 128 rows of 128 bytes
+constexpr int kBQ = 128, kBK = 64, kD = 64, kStages = 2;
+constexpr int kQBytes = kBQ * kD * 2;                          // 16 KB: 128 rows of 128 bytes
+constexpr int kTileBytes = kBK * kD * 2;                       // 8 KB: 64 rows of 128 bytes
 constexpr int kThreads = 192;
-constexpr int kOffK = kTileBytes, kOffV = kOffK + kStages * kTileBytes, kOffBar = kOffV + kStages * kTileBytes;
-constexpr int kNumBars = 1 + 3 * kStages + 5 * 2;
-constexpr int kSmemBytes = kOffBar + kNumBars * 8 + 16 + 1024 + 8 * 1024;   // + alignment slack; > 113 KB keeps one CTA per SM
-constexpr uint32_t kColS = 0, kColO = 256, kColP = 384;        // TMEM columns: S[2] x 128 | O[2] x 64 | P[2] x 64
+constexpr int kOffK = kQBytes, kOffV = kOffK + kStages * kTileBytes, kOffBar = kOffV + kStages * kTileBytes;
+constexpr int kNumBars = 1 + 3 * kStages + 3;
+constexpr int kSmemBytes = kOffBar + kNumBars * 8 + 16 + 1024;      // + alignment slack: ~50 KB, four CTAs per SM
+constexpr uint32_t kTmemCols = 128;
+constexpr uint32_t kColS = 0, kColP = 0, kColO = 64;            // TMEM columns: S x 64 (P over its first 32) | O x 64
+constexpr float kRescaleThreshold = 8.f;                        // log2 units: the maximum is raised only past 2^8
 
 __device__ __forceinline__ int vis_lo5(int t, int T, int context, int chunk) {
   int lo = t - context + 1;
@@ -70,9 +77,9 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
-codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __restrict__ out, int T, int heads, int context,
-                           int chunk, float scale_log2e) {
+__global__ void __launch_bounds__(kThreads, 4)
+codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_constant__ CUtensorMap tmkv,
+                           __half* __restrict__ out, int T, int heads, int context, int chunk, float scale_log2e) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
@@ -80,12 +87,10 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
   uint64_t* k_full = q_full + 1;
   uint64_t* v_full = k_full + kStages;
   uint64_t* kv_empty = v_full + kStages;
-  uint64_t* s_full = kv_empty + kStages;     // [2] MMA -> softmax
-  uint64_t* s_free = s_full + 2;             // [2] softmax -> MMA
-  uint64_t* p_full = s_free + 2;             // [2] softmax -> MMA
-  uint64_t* o_full = p_full + 2;             // [2] MMA -> softmax
-  uint64_t* o_free = o_full + 2;             // [2] softmax -> MMA
-  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(o_free + 2);
+  uint64_t* s_full = kv_empty + kStages;     // MMA -> softmax
+  uint64_t* p_full = s_full + 1;             // softmax -> MMA (S read, P written, O rescaled if needed)
+  uint64_t* o_full = p_full + 1;             // MMA -> softmax: P_j.V_j has been added to O
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(o_full + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // heavy tiles (late queries see the most keys) first
@@ -98,17 +103,17 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
   const int n_tiles = (last_q - k_begin) / kBK + 1;
 
   if (warp == 4 && lane == 0) {
-    ptx::prefetch_tmap(&tm);
+    ptx::prefetch_tmap(&tmq);
+    ptx::prefetch_tmap(&tmkv);
     ptx::mbar_init(q_full, 1);
     for (int i = 0; i < kStages; ++i) { ptx::mbar_init(&k_full[i], 1); ptx::mbar_init(&v_full[i], 1); ptx::mbar_init(&kv_empty[i], 1); }
-    for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(&s_full[i], 1); ptx::mbar_init(&o_full[i], 1);
-      ptx::mbar_init(&s_free[i], 4); ptx::mbar_init(&p_full[i], 4); ptx::mbar_init(&o_free[i], 4);
-    }
+    ptx::mbar_init(s_full, 1);
+    ptx::mbar_init(p_full, 4);
+    ptx::mbar_init(o_full, 1);
     ptx::fence_barrier_init();
   }
   if (warp == 5) {
-    ptx::tmem_alloc(tmem_holder, 512);
+    ptx::tmem_alloc(tmem_holder, kTmemCols);
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
@@ -121,16 +126,16 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
     // ===== TMA producer =====
     if (lane == 0) {
       pdl_wait();
-      ptx::mbar_expect_tx(q_full, kTileBytes);
-      ptx::tma_load_2d(smem, &tm, q_full, h * kD, tok0 + q0, ptx::kEvictNormal);
+      ptx::mbar_expect_tx(q_full, kQBytes);
+      ptx::tma_load_2d(smem, &tmq, q_full, h * kD, tok0 + q0, ptx::kEvictNormal);
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % kStages;
         if (j >= kStages) ptx::mbar_wait(&kv_empty[st], ((j / kStages) & 1) ^ 1);
         const int row = tok0 + k_begin + j * kBK;
         ptx::mbar_expect_tx(&k_full[st], kTileBytes);
-        ptx::tma_load_2d(smem + kOffK + st * kTileBytes, &tm, &k_full[st], d + h * kD, row, ptx::kEvictLast);
+        ptx::tma_load_2d(smem + kOffK + st * kTileBytes, &tmkv, &k_full[st], d + h * kD, row, ptx::kEvictLast);
         ptx::mbar_expect_tx(&v_full[st], kTileBytes);
-        ptx::tma_load_2d(smem + kOffV + st * kTileBytes, &tm, &v_full[st], 2 * d + h * kD, row, ptx::kEvictLast);
+        ptx::tma_load_2d(smem + kOffV + st * kTileBytes, &tmkv, &v_full[st], 2 * d + h * kD, row, ptx::kEvictLast);
       }
     }
   } else if (warp == 5) {
@@ -140,30 +145,28 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
       constexpr uint32_t idesc_o = ptx::make_idesc(0, kBQ, kD) | (1u << 16);     // B (= V) MN-major
       const uint64_t qdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem));
       auto issue_s = [&](int j) {
-        const int st = j % kStages, buf = j & 1;
+        const int st = j % kStages;
         ptx::mbar_wait(&k_full[st], (j / kStages) & 1);
-        if (j >= 2) ptx::mbar_wait(&s_free[buf], ((j >> 1) & 1) ^ 1);
         ptx::tc_fence_after();
         const uint64_t kdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kOffK + st * kTileBytes));
 #pragma unroll
-        for (int k = 0; k < kD / 16; ++k) mma_f16_ss(tmem_base + kColS + buf * kBK, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
-        ptx::mma_commit(&s_full[buf]);
+        for (int k = 0; k < kD / 16; ++k) mma_f16_ss(tmem_base + kColS, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
+        ptx::mma_commit(s_full);
       };
       ptx::mbar_wait(q_full, 0);
       issue_s(0);
       for (int j = 0; j < n_tiles; ++j) {
-        const int st = j % kStages, buf = j & 1;
-        if (j + 1 < n_tiles) issue_s(j + 1);
+        const int st = j % kStages;
         ptx::mbar_wait(&v_full[st], (j / kStages) & 1);
-        ptx::mbar_wait(&p_full[buf], (j >> 1) & 1);
-        if (j >= 2) ptx::mbar_wait(&o_free[buf], ((j >> 1) & 1) ^ 1);
+        ptx::mbar_wait(p_full, j & 1);
         ptx::tc_fence_after();
         const uint64_t vdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kOffV + st * kTileBytes));
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)      // 16 keys per instruction: 8 packed-half columns of P, 2 KB of V rows
-          mma_f16_ts(tmem_base + kColO + buf * kD, tmem_base + kColP + buf * (kBK / 2) + 8 * k, vdesc + 128 * k, idesc_o, k != 0);
-        ptx::mma_commit(&o_full[buf]);
+          mma_f16_ts(tmem_base + kColO, tmem_base + kColP + 8 * k, vdesc + 128 * k, idesc_o, (j | k) != 0);
+        ptx::mma_commit(o_full);
         ptx::mma_commit(&kv_empty[st]);
+        if (j + 1 < n_tiles) issue_s(j + 1);    // in issue order behind P_j.V_j: the S / P columns are free by then
       }
     }
   } else {
@@ -171,36 +174,15 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
     const int row = q0 + warp * 32 + lane;
     const int lo = vis_lo5(min(row, T - 1), T, context, chunk);
     const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
-    float o[kD];
-#pragma unroll
-    for (int i = 0; i < kD; ++i) o[i] = 0.f;
-    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    // rows of one warp share the tile loop; a tile needs the element mask when it touches the diagonal or the window edge
+    const uint32_t s_addr = lane_addr + kColS;
+    float m = -INFINITY, l = 0.f;
+    // a tile needs the element mask when it touches the diagonal or the window edge of some row of the CTA
     const int lo_max = vis_lo5(min(q0 + kBQ - 1, T - 1), T, context, chunk);
 
-    auto fold_o = [&](int j, float alpha) {
-      const int buf = j & 1;
-      ptx::mbar_wait(&o_full[buf], (j >> 1) & 1);
-      ptx::tc_fence_after();
-#pragma unroll
-      for (int c0 = 0; c0 < kD; c0 += 32) {
-        uint32_t r[32];
-        ptx::tmem_ld32(lane_addr + kColO + buf * kD + c0, r);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c0 + i] = o[c0 + i] * alpha + __uint_as_float(r[i]);
-      }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&o_free[buf]);
-    };
-
     for (int j = 0; j < n_tiles; ++j) {
-      const int buf = j & 1;
       const int k0 = k_begin + j * kBK;
       const bool masked = (k0 + kBK - 1 > q0) || (k0 < lo_max);
-      const uint32_t s_addr = lane_addr + kColS + buf * kBK;
-      ptx::mbar_wait(&s_full[buf], (j >> 1) & 1);
+      ptx::mbar_wait(s_full, j & 1);
       ptx::tc_fence_after();
       // pass 1: row maximum of the visible scores
       float mx = -INFINITY;
@@ -220,9 +202,27 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
           for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
         }
       }
-      const float m_new = fmaxf(m, mx * scale_log2e);
-      const float m_use = m_new == -INFINITY ? 0.f : m_new;     // a row that has seen nothing yet: everything stays zero
-      const float alpha = ex2(m - m_use);
+      mx *= scale_log2e;
+      // raise the running maximum only when this tile exceeds it by more than 2^8: O (in TMEM) and l are rescaled then
+      const bool raise = mx > m + kRescaleThreshold || (m == -INFINITY && mx > -INFINITY);
+      if (__any_sync(0xffffffffu, raise)) {
+        const float alpha = raise ? ex2(m - mx) : 1.f;          // m = -inf: 0 (nothing accumulated yet)
+        if (raise) { m = mx; l *= alpha; }
+        if (j > 0) {
+          ptx::mbar_wait(o_full, (j - 1) & 1);                  // P_{j-1}.V_{j-1} has landed in O
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int c0 = 0; c0 < kD; c0 += 16) {
+            uint32_t r[16];
+            ptx::tmem_ld16(lane_addr + kColO + c0, r);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st16(lane_addr + kColO + c0, r);
+          }
+        }
+      }
+      const float m_use = m == -INFINITY ? 0.f : m;             // a row that has seen nothing yet: everything stays zero
       // pass 2: p = 2^(s * scale * log2(e) - m), packed halves -> TMEM (the A operand of P.V)
       float sum = 0.f;
 #pragma unroll
@@ -230,7 +230,6 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
         uint32_t r[32];
         ptx::tmem_ld32(s_addr + c0, r);
         ptx::tmem_ld_wait();
-        uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           float p0 = ex2(__uint_as_float(r[i]) * scale_log2e - m_use);
@@ -240,42 +239,49 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tm, __half* __res
             if (k < lo || k > row) p0 = 0.f;
             if (k + 1 < lo || k + 1 > row) p1 = 0.f;
           }
-          const __half2 hp = __floats2half2_rn(p0, p1);
-          const float2 back = __half22float2(hp);            // the row sum is the sum of what the tensor core will see
-          sum += back.x + back.y;
-          pk[i >> 1] = *reinterpret_cast<const uint32_t*>(&hp);
+          sum += p0 + p1;
+          r[i >> 1] = pack_f16(p0, p1);                      // packed in place: r[0..15] become the 16 P columns
         }
-        tmem_st16(lane_addr + kColP + buf * (kBK / 2) + (c0 >> 1), pk);
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pk[i] = r[i];
+        tmem_st16(lane_addr + kColP + (c0 >> 1), pk);        // over S columns this thread has already consumed
       }
       tmem_st_wait();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) { ptx::mbar_arrive(&s_free[buf]); ptx::mbar_arrive(&p_full[buf]); }
-      l = l * alpha + sum;
-      m = m_new;
-      // the previous tile's O_{j-1} = P_{j-1}.V_{j-1} (relative to the maximum of that time) joins the accumulator
-      if (j > 0) fold_o(j - 1, alpha_prev);
-      alpha_prev = alpha;
+      if (lane == 0) ptx::mbar_arrive(p_full);
+      l += sum;
     }
-    fold_o(n_tiles - 1, alpha_prev);
+    // ---- o = O / l
+    ptx::mbar_wait(o_full, (n_tiles - 1) & 1);
+    ptx::tc_fence_after();
     pdl_wait();                               // `out` may still be read by the kernel before the producer of qkv
-    if (row < T) {
-      const float inv = 1.f / l;
-      __half* dst = out + static_cast<long long>(tok0 + row) * d + h * kD;
+    const float inv = 1.f / l;
+    __half* dst = out + static_cast<long long>(tok0 + row) * d + h * kD;
 #pragma unroll
-      for (int c = 0; c < kD; c += 8) {
-        uint4 v;
-        v.x = pack_f16(o[c] * inv, o[c + 1] * inv);
-        v.y = pack_f16(o[c + 2] * inv, o[c + 3] * inv);
-        v.z = pack_f16(o[c + 4] * inv, o[c + 5] * inv);
-        v.w = pack_f16(o[c + 6] * inv, o[c + 7] * inv);
-        *reinterpret_cast<uint4*>(dst + c) = v;
+    for (int c0 = 0; c0 < kD; c0 += 16) {
+      uint32_t r[16];
+      ptx::tmem_ld16(lane_addr + kColO + c0, r);
+      ptx::tmem_ld_wait();
+      if (row < T) {
+        uint4 v0, v1;
+        v0.x = pack_f16(__uint_as_float(r[0]) * inv, __uint_as_float(r[1]) * inv);
+        v0.y = pack_f16(__uint_as_float(r[2]) * inv, __uint_as_float(r[3]) * inv);
+        v0.z = pack_f16(__uint_as_float(r[4]) * inv, __uint_as_float(r[5]) * inv);
+        v0.w = pack_f16(__uint_as_float(r[6]) * inv, __uint_as_float(r[7]) * inv);
+        v1.x = pack_f16(__uint_as_float(r[8]) * inv, __uint_as_float(r[9]) * inv);
+        v1.y = pack_f16(__uint_as_float(r[10]) * inv, __uint_as_float(r[11]) * inv);
+        v1.z = pack_f16(__uint_as_float(r[12]) * inv, __uint_as_float(r[13]) * inv);
+        v1.w = pack_f16(__uint_as_float(r[14]) * inv, __uint_as_float(r[15]) * inv);
+        *reinterpret_cast<uint4*>(dst + c0) = v0;
+        *reinterpret_cast<uint4*>(dst + c0 + 8) = v1;
       }
     }
   }
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 5) ptx::tmem_dealloc(tmem_base, 512);
+  if (warp == 5) ptx::tmem_dealloc(tmem_base, kTmemCols);
 }
 
 // interleaved-pair RoPE (:255-300) of q and k in place: qkv [M, 3d] half, table row = token index inside its sample
@@ -325,18 +331,21 @@ int codec_attention_tc5(void* qkv, void* out, int B, int T, int heads, int hd, i
                    reinterpret_cast<const float4*>(rope_table), total));
     count_launch();
   }
-  // one tensor map per (buffer, shape): the engine calls with the same qkv buffer for every layer of a stage
-  struct Cached { const void* base; long long M; int d; CUtensorMap tm; };
+  // tensor maps per (buffer, shape): Q boxes of 128 rows, K / V boxes of 64 rows (the engine calls with the same qkv buffer
+  // for every layer of a stage)
+  struct Cached { const void* base; long long M; int d; CUtensorMap tmq, tmkv; };
   static thread_local Cached cache[8];
   static thread_local int next = 0;
-  const CUtensorMap* tm = nullptr;
+  const Cached* tm = nullptr;
   for (auto& c : cache)
-    if (c.base == qkv && c.M == M && c.d == d) { tm = &c.tm; break; }
+    if (c.base == qkv && c.M == M && c.d == d) { tm = &c; break; }
   if (!tm) {
     Cached& c = cache[next++ % 8];
-    MT_TRY(make_tmap_2d(&c.tm, qkv, MT_DTYPE_F16, M, 3ll * d, 3ll * d, kBK));
+    c.base = nullptr;
+    MT_TRY(make_tmap_2d(&c.tmq, qkv, MT_DTYPE_F16, M, 3ll * d, 3ll * d, kBQ));
+    MT_TRY(make_tmap_2d(&c.tmkv, qkv, MT_DTYPE_F16, M, 3ll * d, 3ll * d, kBK));
     c.base = qkv; c.M = M; c.d = d;
-    tm = &c.tm;
+    tm = &c;
   }
   static bool attr_set = false;
   if (!attr_set) {
@@ -344,7 +353,7 @@ int codec_attention_tc5(void* qkv, void* out, int B, int T, int heads, int hd, i
     attr_set = true;
   }
   const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(hd));
-  MT_CUDA(launch(codec_attention_tc5_kernel, dim3(cdiv(T, kBQ), heads, B), dim3(kThreads), kSmemBytes, s, *tm,
+  MT_CUDA(launch(codec_attention_tc5_kernel, dim3(cdiv(T, kBQ), heads, B), dim3(kThreads), kSmemBytes, s, tm->tmq, tm->tmkv,
                  reinterpret_cast<__half*>(out), T, heads, context, chunk, scale_log2e));
   count_launch();
   return MT_OK;

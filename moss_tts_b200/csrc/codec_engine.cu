@@ -158,6 +158,9 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
     const mt_codec_layer& L = h->layers[st][l];
     MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
     if (probe) MT_TRY(absmax_f16(hbuf, M * d, probe + 0, s));
+    // the tcgen05 attention takes q and k already rotated (a rotary epilogue inside the in_proj GEMM was measured: the
+    // per-row table reads cost the short-K GEMM +80 us per launch, more than the separate in-place pass)
+    const bool tc5 = a16 && !ring && g_attn_mode == 0;
     MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32));
     if (probe) MT_TRY(absmax_f16(qkv, M * 3 * d, probe + 1, s));
     if (ring) {
@@ -166,7 +169,7 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
       __half* lr = ring + l * ring_layer_halves;
       MT_TRY(codec_kv_append_f16(qkv, lr, nb, static_cast<int>(Ts), heads, c.context[st], pos0, y, s));
       MT_TRY(codec_attention_ring_f16(qkv, lr, hbuf, nb, static_cast<int>(Ts), heads, c.context[st], pos0, s, y));
-    } else if (a16 && g_attn_mode == 0) {
+    } else if (tc5) {
       MT_TRY(codec_attention_tc5(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
     } else if (a16) {
       MT_TRY(codec_attention_f16(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
