@@ -130,7 +130,7 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid
       ptx::tma_load_2d(smem, &tmq, q_full, h * kD, tok0 + q0, ptx::kEvictNormal);
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % kStages;
-        if (j >= kStages) ptx::mbar_wait(&kv_empty[st], ((j / kStages) & 1) ^ 1);
+        if (j >= kStages) ptx::mbar_wait_suspend(&kv_empty[st], ((j / kStages) & 1) ^ 1);
         const int row = tok0 + k_begin + j * kBK;
         ptx::mbar_expect_tx(&k_full[st], kTileBytes);
         ptx::tma_load_2d(smem + kOffK + st * kTileBytes, &tmkv, &k_full[st], d + h * kD, row, ptx::kEvictLast);
@@ -146,19 +146,19 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid
       const uint64_t qdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem));
       auto issue_s = [&](int j) {
         const int st = j % kStages;
-        ptx::mbar_wait(&k_full[st], (j / kStages) & 1);
+        ptx::mbar_wait_suspend(&k_full[st], (j / kStages) & 1);
         ptx::tc_fence_after();
         const uint64_t kdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kOffK + st * kTileBytes));
 #pragma unroll
         for (int k = 0; k < kD / 16; ++k) mma_f16_ss(tmem_base + kColS, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
         ptx::mma_commit(s_full);
       };
-      ptx::mbar_wait(q_full, 0);
+      ptx::mbar_wait_suspend(q_full, 0);
       issue_s(0);
       for (int j = 0; j < n_tiles; ++j) {
         const int st = j % kStages;
-        ptx::mbar_wait(&v_full[st], (j / kStages) & 1);
-        ptx::mbar_wait(p_full, j & 1);
+        ptx::mbar_wait_suspend(&v_full[st], (j / kStages) & 1);
+        ptx::mbar_wait_suspend(p_full, j & 1);
         ptx::tc_fence_after();
         const uint64_t vdesc = ptx::make_smem_desc_sw128(ptx::smem_u32(smem + kOffV + st * kTileBytes));
 #pragma unroll
@@ -182,7 +182,7 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid
     for (int j = 0; j < n_tiles; ++j) {
       const int k0 = k_begin + j * kBK;
       const bool masked = (k0 + kBK - 1 > q0) || (k0 < lo_max);
-      ptx::mbar_wait(s_full, j & 1);
+      ptx::mbar_wait_suspend(s_full, j & 1);
       ptx::tc_fence_after();
       // pass 1: row maximum of the visible scores
       float mx = -INFINITY;
@@ -209,7 +209,7 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid
         const float alpha = raise ? ex2(m - mx) : 1.f;          // m = -inf: 0 (nothing accumulated yet)
         if (raise) { m = mx; l *= alpha; }
         if (j > 0) {
-          ptx::mbar_wait(o_full, (j - 1) & 1);                  // P_{j-1}.V_{j-1} has landed in O
+          ptx::mbar_wait_suspend(o_full, (j - 1) & 1);                  // P_{j-1}.V_{j-1} has landed in O
           ptx::tc_fence_after();
 #pragma unroll
           for (int c0 = 0; c0 < kD; c0 += 16) {
@@ -254,7 +254,7 @@ codec_attention_tc5_kernel(const __grid_constant__ CUtensorMap tmq, const __grid
       l += sum;
     }
     // ---- o = O / l
-    ptx::mbar_wait(o_full, (n_tiles - 1) & 1);
+    ptx::mbar_wait_suspend(o_full, (n_tiles - 1) & 1);
     ptx::tc_fence_after();
     pdl_wait();                               // `out` may still be read by the kernel before the producer of qkv
     const float inv = 1.f / l;

@@ -63,6 +63,27 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   } while (!done);
 }
 
+// Same wait for warps that share their scheduler with working warps (several CTAs per SM): the hardware may suspend the
+// thread for up to `hint_ns` per try instead of returning at once, so a waiting warp does not burn issue slots spinning.
+__device__ __forceinline__ void mbar_wait_suspend(uint64_t* bar, uint32_t parity, uint32_t hint_ns = 20000) {
+  uint32_t done = 0;
+#if MT_MBAR_WATCHDOG
+  uint32_t spins = 0;
+#endif
+  do {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, P1;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+        : "memory");
+#if MT_MBAR_WATCHDOG
+    if (!done && ++spins > (1u << 22)) __trap();
+#endif
+  } while (!done);
+}
+
 // ---- TMA --------------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
