@@ -5,6 +5,7 @@
   stream  incremental streaming decode: per-push latency (SURVEY §8f rank 3 building block)
   synth  streaming synthesis: generate_stream at the 8B / released-codec shapes, time to first audio
          and total time vs generate + one-shot decode
+  rt  MOSS-TTS-Realtime step-wise decode: ms per frame at the assumed 1.7B shape
   enc codec ENCODE sweep B in {1,16,64} x {1,10,30} s of 24 kHz audio -> 32 codebooks
 One JSON line per measurement; device-timed with CUDA events after a warm-up call.
 
@@ -180,6 +181,42 @@ def c5(args, dev):
                           "audio_s_per_s": B * max(n - cfg.n_vq, 0) / 12.5 / (ms * 1e-3)}), flush=True)
 
 
+def rt(args, dev):
+    """MOSS-TTS-Realtime step-wise decode at the assumed released shape (Qwen3-1.7B backbone + the
+    reference config's 4-layer local transformer, rvq 16): prefill of a 96-position prompt, then finish() for 125 frames
+    with the reference's default sampling (T 0.8, top-p 0.6, top-k 30, penalty 1.1 over a 50-frame window)."""
+    from moss_tts_b200.config import RealtimeConfig
+    from moss_tts_b200.modeling_mossttsrealtime import MossTTSRealtimeInference, MossTTSRealtimeModel
+    import numpy as np
+    cfg = RealtimeConfig.realtime_1p7b()
+    model = MossTTSRealtimeModel.random_init(cfg, device=dev, seed=2468)
+    frames = 32 if args.quick else 125
+    for B in ((1, 16) if args.quick else (1, 16, 64, 128)):
+        rng = np.random.default_rng(B)
+        prompts = []
+        for _ in range(B):
+            p = np.full((92, cfg.rvq + 1), cfg.audio_pad_code, dtype=np.int64)
+            p[:, 0] = rng.integers(0, cfg.pad_token_id, 92)
+            p[:40, 0] = cfg.reference_audio_pad
+            p[:40, 1:] = rng.integers(0, 1024, (40, cfg.rvq))
+            prompts.append(p)
+        prefixes = [rng.integers(0, cfg.pad_token_id, 4).tolist() for _ in range(B)]
+        for mode, kw in (("sampled (reference defaults)", {}), ("greedy + penalty", {"do_sample": False})):
+            inf = MossTTSRealtimeInference(model, None, max_length=frames + 4, channels=cfg.rvq, max_batch=B, seed=1,
+                                           audio_eos_token=4095)            # never emitted: every run makes all frames
+            inf.prefill(prompts, prefixes, **kw)
+            inf.finish(max_steps=4, **kw)                                    # graph capture / warm-up
+            inf = MossTTSRealtimeInference(model, None, max_length=frames + 4, channels=cfg.rvq, max_batch=B, seed=1,
+                                           audio_eos_token=4095)
+            ms_pre, _ = timed(lambda: inf.prefill(prompts, prefixes, **kw))
+            ms, outs = timed(lambda: inf.finish(max_steps=frames, **kw))
+            n = len(outs)
+            print(json.dumps({"config": "MOSS-TTS-Realtime step-wise decode", "shape": "assumed Qwen3-1.7B backbone + local 4L (rvq 16)",
+                              "mode": mode, "B": B, "frames": n, "prefill_plus_first_frame_ms": ms_pre, "ms_total": ms,
+                              "ms_per_frame": ms / max(n, 1), "audio_s_per_s": B * n / 12.5 / (ms * 1e-3),
+                              "x_realtime_per_stream": n / 12.5 / (ms * 1e-3), "weight_GB": model.weight_bytes() / 1e9}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--what", default="c3,c4,c5")
@@ -188,7 +225,7 @@ def main():
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(0)
     for w in args.what.split(","):
-        {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream, "synth": synth}[w](args, dev)
+        {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream, "synth": synth, "rt": rt}[w](args, dev)
         torch.cuda.empty_cache()
 
 
