@@ -88,6 +88,7 @@ int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s);
 
 // Persistent decode-orientation kernel (M <= 256): one CTA per SM streams (weight tile, K split) units (gemm_dec.cu).
 int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s);
+int dec_grid_ctas(int M, int N, int K, long long workspace_bytes);
 // Deterministic reduction of [splits][M][N] fp32 partials + epilogue (gemm_tc.cu).
 int splitk_reduce(const Epi& ep, int splits, cudaStream_t s);
 

@@ -271,6 +271,15 @@ int dec_pick_splits(int tiles, int k_blocks, long long per_split_bytes, long lon
   return best;
 }
 
+// CTAs the decode-orientation kernel launches for a bf16 [M,K] x [N,K]^T Linear handed to a fused consumer (split-K partials):
+// every CTA owns ~200 KB of shared memory, so two of these kernels can never share an SM (lm_attn.cu's early-read rule)
+int dec_grid_ctas(int M, int N, int K, long long workspace_bytes) {
+  const int k_blocks = cdiv(K, 64), tiles = cdiv(N, kTileA);
+  const int splits = dec_pick_splits(tiles, k_blocks, static_cast<long long>(M) * N * 4, workspace_bytes, false);
+  const int units = tiles * splits;
+  return units < kNumSMs ? units : kNumSMs;
+}
+
 int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s) {
   const int esz = dtype_bytes(p.dtype_in);
   const int k_elems = 128 / esz;

@@ -51,7 +51,7 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
                    const bf16* __restrict__ rope_sin, bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
                    const uint8_t* __restrict__ mask, long long mask_ld, bf16* __restrict__ out, int n_heads, int n_kv,
                    const int* __restrict__ pos_dev, int pos_host, int spad, int max_seq, float eps, float scale,
-                   unsigned long long* __restrict__ trace, int exp_flags, int cs) {
+                   unsigned long long* __restrict__ trace, int exp_flags, int cs, int early_pos) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
   constexpr int E = D / 32;
   const int G = n_heads / n_kv;
@@ -78,15 +78,9 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
   };
   stamp(0);
   pdl_trigger();
-  pdl_wait();
-  stamp(1);
   const int b = item / n_kv, kvh = item % n_kv;
   const int heads_total = n_heads + 2 * n_kv;
   const long long row_w = static_cast<long long>(heads_total) * D;
-
-  // ---- the q/k/v inputs of this block are requested first (they do not depend on the position): a warp owns
-  // heads warp, warp + kWarps, ... (G query heads, then the k and the v head); lane owns elements lane + 32e.
-  // Every load of the first four splits is in flight before anything else is asked of the memory system.
   constexpr int kSlots = (kMaxG + 2 + kWarps - 1) / kWarps;
   long long idx0[kSlots];
   bool live[kSlots];
@@ -97,46 +91,24 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
     const int hh = i < G ? kvh * G + i : (i == G ? n_heads + kvh : n_heads + n_kv + kvh);
     idx0[sl] = b * row_w + static_cast<long long>(hh) * D + lane;
   }
-  float t0[kSlots][4][E];
-#pragma unroll
-  for (int sl = 0; sl < kSlots; ++sl)
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-#pragma unroll
-      for (int e = 0; e < E; ++e) {
-        if (partials) t0[sl][u][e] = (live[sl] && u < nsplit) ? __ldcg(partials + u * split_stride + idx0[sl] + 32 * e) : 0.f;
-        else t0[sl][u][e] = (live[sl] && u == 0) ? bf2f(qkv[idx0[sl] + 32 * e]) : 0.f;
-      }
   float gq[E], gk[E];
 #pragma unroll
   for (int e = 0; e < E; ++e) {
     gq[e] = bf2f(q_gain[lane + 32 * e]);
     gk[e] = bf2f(k_gain[lane + 32 * e]);
   }
-
-  const int pos = pos_dev ? *pos_dev : pos_host;
-  const int nkeys = pos + 1;
-  int kbeg = 0, kend = nkeys;                          // this CTA's keys
-  if constexpr (CL) {
-    const int per = (((nkeys + cs - 1) / cs) + 15) & ~15;
-    kbeg = min(rank * per, nkeys);
-    kend = min(kbeg + per, nkeys);
-  }
-  const bool owner = kbeg <= pos && pos < kend;        // the CTA that appends (and reads) row `pos`
   bf16* kbase = k_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
   bf16* vbase = v_cache + (static_cast<long long>(b) * n_kv + kvh) * max_seq * D;
 
-  // the K/V rows of this (row, kv head) come from HBM (the cache is far larger than L2 and 15 GB of weights
-  // pass through between two visits): ask L2 for all of them now, so that the dependent phases below
-  // (scores -> softmax -> P.V) find them on chip
-  // (one bulk prefetch per tensor: the rows [0, pos) of a (row, kv head) are contiguous)
-  if (!CL && threadIdx.x < 2 && pos > 0 && !(exp_flags & 1)) {
-    const bf16* p = threadIdx.x ? vbase : kbase;
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(pos * D * 2) : "memory");
-  }
-
-  // first score tile of this warp: its K rows are requested now and land while the prep below runs.
-  // Row `pos` (the token being appended) does not exist yet: clamp to pos-1 and patch after the barrier.
+  // ---- everything that depends only on the POSITION (not on this step's q/k/v): the position itself, the rotary
+  // row, the K/V rows of the earlier positions.  With `early_pos` set all of it is requested BEFORE the dependency wait,
+  // so these round trips -- position -> rotary row / first K tile from HBM -- overlap the producer's tail instead of
+  // sitting behind it.  The caller sets it only when the writers of that data are KNOWN to have finished although this
+  // kernel has not waited yet (see attn_decode in lm_ops.cuh): with programmatic dependent launch a chain of small
+  // kernels can be resident, all waiting, while a kernel many launches back is still running.
+  int pos = 0, nkeys = 0, kbeg = 0, kend = 0, kfirst = 0;
+  bool owner = false, early_k = false;
+  float rc[E], rs[E];
   // The dot product over the head dim does not care in which MMA k-slot a dim sits as long as Q uses the same
   // order: lane (g, t4) reads 16 contiguous bytes (dims 32c + 8 t4 .. +7) of its key row per chunk c, and k-step
   // s = 2c + h takes dims +4h, +4h+1 as k-slots (2 t4, 2 t4 + 1) and dims +4h+2, +4h+3 as slots (2 t4 + 8, + 9).
@@ -151,22 +123,60 @@ attn_decode_kernel(const bf16* __restrict__ qkv, const float* __restrict__ parti
       for (int c = 0; c < D / 32; ++c) kq[n][c] = kr[4 * c];
     }
   };
-  const int kfirst = kbeg + 16 * warp;
-  const bool early_k = kfirst < kend && !(exp_flags & 2);
-  if (early_k) load_k(kfirst, max(pos - 1, 0));
+  auto position_work = [&]() {
+    pos = pos_dev ? *pos_dev : pos_host;
+    nkeys = pos + 1;
+    kbeg = 0; kend = nkeys;                             // this CTA's keys
+    if constexpr (CL) {
+      const int per = (((nkeys + cs - 1) / cs) + 15) & ~15;
+      kbeg = min(rank * per, nkeys);
+      kend = min(kbeg + per, nkeys);
+    }
+    owner = kbeg <= pos && pos < kend;                  // the CTA that appends (and reads) row `pos`
+    // the K/V rows of this (row, kv head) come from HBM (the cache is far larger than L2 and 15 GB of weights
+    // pass through between two visits): optionally ask L2 for all of them now
+    // (one bulk prefetch per tensor: the rows [0, pos) of a (row, kv head) are contiguous)
+    if (!CL && threadIdx.x < 2 && pos > 0 && !(exp_flags & 1)) {
+      const bf16* p = threadIdx.x ? vbase : kbase;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(pos * D * 2) : "memory");
+    }
+#pragma unroll
+    for (int e = 0; e < E; ++e) {
+      if (rope_cos) {
+        const int jh = (lane + 32 * e) % (D / 2);
+        rc[e] = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
+        rs[e] = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
+      } else {
+        rc[e] = 1.f; rs[e] = 0.f;
+      }
+    }
+    // first score tile of this warp: its K rows are requested now and land while the prep below runs.
+    // Row `pos` (the token being appended) does not exist yet: clamp to pos-1 and patch after the barrier.
+    kfirst = kbeg + 16 * warp;
+    early_k = kfirst < kend && !(exp_flags & 2);
+    if (early_k) load_k(kfirst, max(pos - 1, 0));
+  };
+  const bool early = early_pos && !(exp_flags & 4);
+  if (early) position_work();
+  pdl_wait();
+  stamp(1);
+
+  // ---- the q/k/v inputs of this block: a warp owns heads warp, warp + kWarps, ... (G query heads, then the k and the v
+  // head); lane owns elements lane + 32e.  Every load of the first four splits is in flight before anything else is asked
+  // of the memory system.
+  float t0[kSlots][4][E];
+#pragma unroll
+  for (int sl = 0; sl < kSlots; ++sl)
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int e = 0; e < E; ++e) {
+        if (partials) t0[sl][u][e] = (live[sl] && u < nsplit) ? __ldcg(partials + u * split_stride + idx0[sl] + 32 * e) : 0.f;
+        else t0[sl][u][e] = (live[sl] && u == 0) ? bf2f(qkv[idx0[sl] + 32 * e]) : 0.f;
+      }
+  if (!early) position_work();
 
   // ---- prep: sum the split-K partials (split order 0, 1, 2, ... kept), RMSNorm, RoPE, append k/v
-  float rc[E], rs[E];
-#pragma unroll
-  for (int e = 0; e < E; ++e) {
-    if (rope_cos) {
-      const int jh = (lane + 32 * e) % (D / 2);
-      rc[e] = bf2f(rope_cos[static_cast<long long>(pos) * (D / 2) + jh]);
-      rs[e] = bf2f(rope_sin[static_cast<long long>(pos) * (D / 2) + jh]);
-    } else {
-      rc[e] = 1.f; rs[e] = 0.f;
-    }
-  }
   float xs[kSlots][E];
   if (partials) {
     float a[kSlots][E];
@@ -480,6 +490,8 @@ static size_t attn_smem_bytes(int G, int D, int max_keys, int cs, int* spad_out)
   return fixed + static_cast<size_t>(G) * spad * 6;
 }
 
+bool attn_early_reads_safe(int ctas_qkv, int ctas_between) { return ctas_qkv + ctas_between > kNumSMs + 8; }
+
 bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys) {
   if ((D != 64 && D != 128) || n_heads % n_kv || n_heads / n_kv > kMaxG) return false;
   return attn_smem_bytes(n_heads / n_kv, D, max_keys, attn_decode_cluster(B, n_kv, max_keys), nullptr) <= 200 * 1024;
@@ -488,7 +500,7 @@ bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys) {
 int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
                 const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* k_cache, bf16* v_cache,
                 const uint8_t* mask, long long mask_ld, bf16* out, int B, int n_heads, int n_kv, int D,
-                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s) {
+                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s, int early_pos) {
   const int G = n_heads / n_kv;
   const int cs = attn_decode_cluster(B, n_kv, max_keys);
   int spad = 0;
@@ -517,11 +529,11 @@ int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long sp
     cfg.numAttrs = pdl_enabled() ? 2 : 1;
     MT_CUDA(cudaLaunchKernelEx(&cfg, kern, qkv, partials, nsplit, split_stride, q_gain, k_gain, rope_cos, rope_sin, k_cache,
                                v_cache, mask, mask_ld, out, n_heads, n_kv, pos_dev, pos_host, spad, max_seq, eps, scale,
-                               trace, exp_flags, cs));
+                               trace, exp_flags, cs, early_pos));
   } else {
     MT_CUDA(launch(kern, dim3(B * n_kv), dim3(kWarps * 32), smem, s, qkv, partials, nsplit, split_stride, q_gain, k_gain,
                    rope_cos, rope_sin, k_cache, v_cache, mask, mask_ld, out, n_heads, n_kv, pos_dev, pos_host, spad,
-                   max_seq, eps, scale, trace, exp_flags, 1));
+                   max_seq, eps, scale, trace, exp_flags, 1, early_pos));
   }
   count_launch();
   return MT_OK;

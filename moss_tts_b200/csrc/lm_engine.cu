@@ -100,6 +100,8 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
   const long long MH = static_cast<long long>(M) * H;
 
   const bool fused_attn = T == 1 && attn_decode_fits(B, c.num_heads, c.num_kv_heads, D, max_keys);
+  // layers >= 1 may read the position / rotary row / old K rows before their dependency wait (lm_ops.cuh: attn_decode)
+  const bool early_reads = fused_attn && attn_early_reads_safe(dec_grid_ctas(M, nqkv, H, kSplitKBytes), dec_grid_ctas(M, 2 * I, H, kSplitKBytes));
   MT_TRY(embed_sum(ids, reinterpret_cast<const bf16*>(h->w.embed_tokens), reinterpret_cast<const bf16*>(h->w.emb_ext),
                    h->x, M, H, n_vq_embed < 0 ? c.n_vq : n_vq_embed, c.audio_head_size, c.vocab_size, s, 1 + c.n_vq));
   MT_TRY(add_rmsnorm(nullptr, h->x, nullptr, 0, 0, nullptr, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, M, H, eps, s));
@@ -114,7 +116,7 @@ int lm_forward_impl(mt_lm* h, const int64_t* ids, const uint8_t* mask, long long
                            reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
                            reinterpret_cast<const bf16*>(h->w.rope_cos), reinterpret_cast<const bf16*>(h->w.rope_sin), kc, vc,
                            mask, mask_ld, h->attn, B, c.num_heads, c.num_kv_heads, D, past_len_dev, past_len, max_keys,
-                           c.max_seq, eps, s));
+                           c.max_seq, eps, s, l > 0 && early_reads));     // layer 0 follows the kernel that writes the position too closely
     } else {
       MT_TRY(qkv_post(h->qkv, sp ? h->splitk : nullptr, sp, static_cast<long long>(M) * nqkv,
                       reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),

@@ -28,7 +28,15 @@ bool attn_decode_fits(int B, int n_heads, int n_kv, int D, int max_keys);
 int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long split_stride, const bf16* q_gain,
                 const bf16* k_gain, const bf16* rope_cos, const bf16* rope_sin, bf16* k_cache, bf16* v_cache,
                 const uint8_t* mask, long long mask_ld, bf16* out, int B, int n_heads, int n_kv, int D,
-                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s);
+                const int* pos_dev, int pos_host, int max_keys, int max_seq, float eps, cudaStream_t s, int early_pos = 0);
+// early_pos = 1: the kernel may read the position, the rotary row and the K rows [0, pos) BEFORE its programmatic dependency
+// wait.  Safe only when their writers have certainly finished by the time this kernel's blocks run, which the launch order
+// alone does not give (a chain of waiting kernels can be resident).  The engines' rule: this attention follows a decode GEMM
+// G1 (the qkv projection); a decode GEMM CTA owns > half an SM's shared memory, so once all c1 CTAs of G1 are resident any
+// earlier GEMM X has at most 148 - c1 CTAs left; if X launched more than that, one of its CTAs has exited, i.e. X passed
+// its own dependency wait, i.e. everything launched before X has completed.  early_pos is set when such an X (the gate|up
+// GEMM of the previous layer / previous depth step) lies between the writers and this kernel: c(X) + c(G1) > 148.
+bool attn_early_reads_safe(int ctas_qkv, int ctas_between);
 int silu_mul(const bf16* gu, const float* partials, int nsplit, long long split_stride, bf16* act, int M, int I,
              cudaStream_t s);
 int fill_audio_pad(bf16* logits, long long rows, int head_size, cudaStream_t s);

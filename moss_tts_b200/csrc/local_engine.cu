@@ -100,6 +100,8 @@ static int local_depth_step(mt_local* h, int B, int c, int sp_in, const uint8_t*
   const size_t layer_stride = static_cast<size_t>(cf.lm.max_batch) * cf.lm.num_kv_heads * C * D;
   const long long BL = static_cast<long long>(B) * LH;
   float* pk = h->g->splitk;
+  // K rows of the earlier channels were written a whole depth step ago, behind at least one gate|up GEMM (lm_ops.cuh)
+  const int early = attn_early_reads_safe(dec_grid_ctas(B, nqkv, LH, kSplitKBytes), dec_grid_ctas(B, 2 * LF, LH, kSplitKBytes));
   // x = input ; xn = norm(x)
   MT_TRY(add_rmsnorm(nullptr, h->delta, sp_in ? pk : nullptr, sp_in, BL, h->x, reinterpret_cast<const bf16*>(h->ln_in[0]),
                      h->xn, B, LH, eps, s));
@@ -109,7 +111,7 @@ static int local_depth_step(mt_local* h, int B, int c, int sp_in, const uint8_t*
     MT_TRY(attn_decode(h->qkv, sp ? pk : nullptr, sp, static_cast<long long>(B) * nqkv,
                        reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]), nullptr,
                        nullptr, h->k_cache + l * layer_stride, h->v_cache + l * layer_stride, ones_mask, mask_ld, h->attn, B,
-                       cf.lm.num_heads, cf.lm.num_kv_heads, D, nullptr, c, c + 1, C, eps, s));
+                       cf.lm.num_heads, cf.lm.num_kv_heads, D, nullptr, c, c + 1, C, eps, s, early));
     MT_TRY(lm_linear(h->g, h->attn, B, qs, h->w_o[l], &h->tm_o[l], LH, h->delta, &sp, s));
     MT_TRY(add_rmsnorm(h->x, h->delta, sp ? pk : nullptr, sp, BL, h->x, reinterpret_cast<const bf16*>(h->ln_post[l]), h->xn,
                        B, LH, eps, s));

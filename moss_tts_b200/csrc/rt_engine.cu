@@ -114,6 +114,8 @@ int depth_step(mt_rt* h, const bf16* x_in, int B, int c, cudaStream_t s) {
   const size_t layer_stride = static_cast<size_t>(cf.lm.max_batch) * cf.local_num_kv_heads * R * D;
   const long long BH = static_cast<long long>(B) * H;
   float* pk = h->g->splitk;
+  // K rows of the earlier channels were written a whole depth step ago, behind at least one gate|up GEMM (lm_ops.cuh)
+  const int early = attn_early_reads_safe(dec_grid_ctas(B, nqkv, H, kSplitKBytes), dec_grid_ctas(B, 2 * LI, H, kSplitKBytes));
   MT_TRY(add_rmsnorm(nullptr, x_in, nullptr, 0, 0, h->x, reinterpret_cast<const bf16*>(h->ln_in[0]), h->xn, B, H, eps, s));
   for (int l = 0; l < cf.local_num_layers; ++l) {
     int sp = 0;
@@ -122,7 +124,7 @@ int depth_step(mt_rt* h, const bf16* x_in, int B, int c, cudaStream_t s) {
                        reinterpret_cast<const bf16*>(h->q_norm[l]), reinterpret_cast<const bf16*>(h->k_norm[l]),
                        reinterpret_cast<const bf16*>(h->w.l_rope_cos), reinterpret_cast<const bf16*>(h->w.l_rope_sin),
                        h->k_cache + l * layer_stride, h->v_cache + l * layer_stride, h->ones, 0, h->attn, B,
-                       cf.local_num_heads, cf.local_num_kv_heads, D, nullptr, c, c + 1, R, eps, s));
+                       cf.local_num_heads, cf.local_num_kv_heads, D, nullptr, c, c + 1, R, eps, s, early));
     MT_TRY(lm_linear(h->g, h->attn, B, qs, h->w_o[l], &h->tm_o[l], H, h->delta, &sp, s));
     MT_TRY(add_rmsnorm(h->x, h->delta, sp ? pk : nullptr, sp, BH, h->x, reinterpret_cast<const bf16*>(h->ln_post[l]), h->xn,
                        B, H, eps, s));
