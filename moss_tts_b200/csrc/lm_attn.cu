@@ -508,7 +508,7 @@ int attn_decode(const bf16* qkv, const float* partials, int nsplit, long long sp
   MT_CHECK(smem <= 200 * 1024, "attn_decode: %d keys do not fit in shared memory", max_keys);
   auto kern = cs > 1 ? (D == 128 ? attn_decode_kernel<128, true> : attn_decode_kernel<64, true>)
                      : (D == 128 ? attn_decode_kernel<128, false> : attn_decode_kernel<64, false>);
-  static const int exp_flags = exp_env("MT_ATTN_EXP", 1);   // bit 0: no bulk L2 prefetch of the K/V rows (measured 1.3 % faster over 150 steps), bit 1: no early K tile
+  static const int exp_flags = exp_env("MT_ATTN_EXP", 1);   // bit 0: no bulk L2 prefetch of the K/V rows (measured 1.3 % faster over 150 steps, also when issued before the dependency wait), bit 1: no early K tile, bit 2: no reads before the dependency wait
   static size_t smem_set[4] = {0, 0, 0, 0};
   size_t& cur = smem_set[(D == 128) + 2 * (cs > 1)];
   if (smem > 48 * 1024 && smem > cur) {
