@@ -24,15 +24,34 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 
-def timed(fn, reps=1):
+RANK = int(os.environ.get("RANK", 0))
+WORLD = int(os.environ.get("WORLD_SIZE", 1))
+LOCAL = int(os.environ.get("LOCAL_RANK", 0))
+
+
+def _barrier():
+    if WORLD > 1:
+        import torch.distributed as dist
+        dist.barrier()
     torch.cuda.synchronize()
+
+
+def timed(fn, reps=1):
+    """Device time of `reps` calls; under torchrun (request-sharded runs of C4 / C5): barrier on both sides, max over ranks."""
+    _barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(reps):
         r = fn()
     e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / reps, r
+    _barrier()
+    ms = e0.elapsed_time(e1) / reps
+    if WORLD > 1:
+        import torch.distributed as dist
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms, r
 
 
 def c3(args, dev):
@@ -136,8 +155,9 @@ def c4(args, dev):
     from moss_tts_b200.modeling_moss_tts_local import MossTTSLocalModel
     import bench
     cfg = LocalConfig.local_1p7b(32)
-    model = MossTTSLocalModel.random_init(cfg, device=dev, seed=4321)
-    B = 32 if args.quick else 128
+    model = MossTTSLocalModel.random_init(cfg, device=dev, seed=4321 + RANK)
+    B_total = 32 if args.quick else 128
+    B = B_total // WORLD                                  # request sharding: one group of utterances per GPU
     frames = 16 if args.quick else 125
     bench.PROMPT_LEN = 96
     ids, _ = bench.make_prompts(cfg, B, seed=0)
@@ -146,10 +166,12 @@ def c4(args, dev):
     model.generate(ids, **kw)
     ms, out = timed(lambda: model.generate(ids, **kw))
     steps = sorted(model.last_step_ms[2:])
-    print(json.dumps({"config": "C4 MossTTSLocal greedy", "shape": "assumed Qwen3-1.7B backbone + local 4L/1536/8960/2048",
-                      "B": B, "frames": frames, "ms_total": ms, "prefill_plus_first_frame_ms": model.last_step_ms[0],
-                      "ms_per_frame_median": steps[len(steps) // 2], "audio_s_per_s": B * frames / 12.5 / (ms * 1e-3),
-                      "weight_GB": model.weight_bytes() / 1e9}), flush=True)
+    if RANK == 0:
+        print(json.dumps({"config": "C4 MossTTSLocal greedy", "shape": "assumed Qwen3-1.7B backbone + local 4L/1536/8960/2048",
+                          "n_gpus": WORLD, "B_total": B_total, "B_per_gpu": B, "frames": frames, "ms_total": ms,
+                          "prefill_plus_first_frame_ms": model.last_step_ms[0], "ms_per_frame_median": steps[len(steps) // 2],
+                          "audio_s_per_s": B * WORLD * frames / 12.5 / (ms * 1e-3), "weight_GB": model.weight_bytes() / 1e9,
+                          "sharding": "request-sharded, no in-step collective; timing = max over ranks"}), flush=True)
 
 
 def c5(args, dev):
@@ -157,8 +179,8 @@ def c5(args, dev):
     from moss_tts_b200.modeling_moss_tts import MossTTSDelayModel
     import bench
     cfg = LMConfig.delay_8b(n_vq=16)
-    model = MossTTSDelayModel.random_init(cfg, device=dev, seed=77, never_stop=True)
-    B = 4
+    model = MossTTSDelayModel.random_init(cfg, device=dev, seed=77 + RANK, never_stop=True)
+    B = 4                                                 # per GPU; BASELINE config 5 shards 32 utterances over 8 GPUs
     steps = 400 if args.quick else 3765
     bench.PROMPT_LEN = 512
     ids, mask = bench.make_prompts(cfg, B, seed=0)
@@ -175,10 +197,11 @@ def c5(args, dev):
         st = model.last_step_ms
         n = model.last_n_steps
         tail = sorted(st[-200:])
-        print(json.dumps({"config": "C5 MossTTSDelay n_vq=16 long context", "mode": name, "B": B, "prompt": 512,
+        if RANK == 0:
+          print(json.dumps({"config": "C5 MossTTSDelay n_vq=16 long context", "mode": name, "n_gpus": WORLD, "B_per_gpu": B, "B_total": B * WORLD, "prompt": 512,
                           "steps_run": n, "ms_total": ms, "prefill_ms": st[0], "ms_per_step_first_200": sorted(st[2:202])[100],
                           "ms_per_step_last_200": tail[len(tail) // 2], "final_kv_len": 512 + n,
-                          "audio_s_per_s": B * max(n - cfg.n_vq, 0) / 12.5 / (ms * 1e-3)}), flush=True)
+                          "audio_s_per_s": B * WORLD * max(n - cfg.n_vq, 0) / 12.5 / (ms * 1e-3)}), flush=True)
 
 
 def rt(args, dev):
@@ -222,11 +245,17 @@ def main():
     ap.add_argument("--what", default="c3,c4,c5")
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(0)
+    dev = torch.device("cuda", LOCAL)
+    torch.cuda.set_device(LOCAL)
+    if WORLD > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
     for w in args.what.split(","):
         {"c3": c3, "c4": c4, "c5": c5, "enc": enc, "stream": stream, "synth": synth, "rt": rt}[w](args, dev)
         torch.cuda.empty_cache()
+    if WORLD > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
