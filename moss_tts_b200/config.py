@@ -138,6 +138,14 @@ class RealtimeConfig(LMConfig):
                               head_dim=128)
 
     @staticmethod
+    def wide(num_layers: int = 2) -> "RealtimeConfig":
+        """Every per-layer shape of the assumed 1.7 B model (backbone and the full 4-layer local transformer), with
+        `num_layers` of the backbone's 28 layers: the shape of the reference-executed golden rt_wide_bf16."""
+        c = RealtimeConfig.realtime_1p7b()
+        c.num_layers = num_layers
+        return c
+
+    @staticmethod
     def tiny(n_vq: int = 4) -> "RealtimeConfig":
         return RealtimeConfig(hidden_size=128, intermediate_size=256, num_layers=2, num_heads=4, num_kv_heads=2,
                               head_dim=64, n_vq=n_vq, local_num_layers=2, local_intermediate_size=320,

@@ -163,6 +163,11 @@ def golden_rt(name, cfg, dtype, *, batch, lens, prefix_lens, steps, seed, penalt
 
 def main():
     os.makedirs(OUT, exist_ok=True)
+    only = sys.argv[1:]
+    if only:
+        global golden_rt
+        _all = golden_rt
+        golden_rt = lambda name, *a, **k: _all(name, *a, **k) if name in only else None   # noqa: E731
     t4 = RealtimeConfig.tiny(4)
     golden_rt("rt_tiny_f32", t4, torch.float32, batch=2, lens=[9, 6], prefix_lens=[3, 2], steps=10, seed=11,
               penalty=1.3, window=3, eos_from=(1, 5))
@@ -173,6 +178,10 @@ def main():
               penalty=1.1, window=50)
     golden_rt("rt_mid_bf16", mid, torch.bfloat16, batch=3, lens=[12, 12, 7], prefix_lens=[4, 4, 2], steps=8, seed=13,
               penalty=1.1, window=50)
+    # every per-layer shape of the assumed 1.7 B model (H 2048, 16q/8kv x 128, I 6144, V_t 151936, the full 4-layer local
+    # transformer, rvq 16) with 2 of the 28 backbone layers: the widths the decode GEMMs split K at and attn_decode<128> runs
+    golden_rt("rt_wide_bf16", RealtimeConfig.wide(2), torch.bfloat16, batch=3, lens=[20, 14, 9], prefix_lens=[4, 3, 2],
+              steps=6, seed=17, penalty=1.1, window=50)
 
 
 if __name__ == "__main__":
