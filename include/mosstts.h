@@ -482,16 +482,21 @@ int mt_rlfq_quantize(mt_codec* h, const float* hidden, int B, int T, const int64
 int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, const int64_t* code_lengths, int nq, int chunk_frames,
                     int64_t* codes, float* hidden, void* workspace, long long workspace_bytes, mt_stream s);
 
-/* Incremental streaming decode: `with model.streaming(batch_size): model._decode_frame(chunk)` per push
- * (:1393-1400; StreamingModule :121-177, RingKVCache :413-480, MHAState :488-499 - how moss_tts_realtime's
+/* Incremental streaming: `with model.streaming(batch_size): model._decode_frame(chunk)` / `model._encode_frame(chunk)` per
+ * push (:1393-1400; StreamingModule :121-177, RingKVCache :413-480, MHAState :488-499 - how moss_tts_realtime's
  * AudioStreamDecoder drives the codec).  Every layer keeps a ring cache of `context` tokens (K after RoPE, V; half) in the
- * caller's `cache` buffer (mt_codec_stream_bytes; contents need no initialisation); a push of T <= context frames appends
- * and attends, wav [B, T*downsample] receives the new samples.  Decoder handles with layer_gemm_f16 = 1 only. */
+ * caller's `cache` buffer (mt_codec_stream_bytes; contents need no initialisation); a push of T frames (at most `context`
+ * tokens at every stage) appends and attends.  Decoder stream: wav [B, T*downsample] receives the new samples.  Encoder
+ * stream (a handle created with cfg.encoder = 1): mt_codec_stream_push_encode takes wav [B, T*downsample] and writes the
+ * new codes [nq, B, T] and, if hidden != NULL, encoder_hidden_states [B, T, code_dim].  layer_gemm_f16 = 1 only. */
 typedef struct mt_codec_stream mt_codec_stream;
 int mt_codec_stream_bytes(const mt_codec* h, int B, long long* bytes);
 int mt_codec_stream_begin(mt_codec* h, int B, void* cache, long long cache_bytes, mt_codec_stream** out);
 int mt_codec_stream_push(mt_codec_stream* st, const int64_t* codes /* [nq, B, T] */, int nq, int T, float* wav,
                          void* workspace, long long workspace_bytes, mt_stream s);
+int mt_codec_stream_push_encode(mt_codec_stream* st, const float* wav /* [B, T*downsample] */, int T,
+                                const int64_t* code_lengths /* [B] or NULL */, int nq, int64_t* codes, float* hidden,
+                                void* workspace, long long workspace_bytes, mt_stream s);
 int mt_codec_stream_end(mt_codec_stream* st);
 
 /* AudioStreamDecoder._apply_crossfade (moss_tts_realtime/mossttsrealtime/streaming_mossttsrealtime.py:776-799):

@@ -26,7 +26,7 @@ EXPORTS = [
     "mt_sample_tokens", "mt_sample_tokens_full", "mt_sample_full_scratch_bytes", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",
     "mt_codec_create", "mt_codec_destroy", "mt_codec_workspace_bytes", "mt_rvq_fold_tables",
     "mt_rvq_dequant", "mt_codec_decode", "mt_rlfq_quantize", "mt_codec_encode",
-    "mt_codec_stream_bytes", "mt_codec_stream_begin", "mt_codec_stream_push", "mt_codec_stream_end",
+    "mt_codec_stream_bytes", "mt_codec_stream_begin", "mt_codec_stream_push", "mt_codec_stream_push_encode", "mt_codec_stream_end",
     "mt_loudness_normalize", "mt_pack_unified_codes", "mt_pad_left",
     "mt_local_query_sizes", "mt_local_create", "mt_local_destroy", "mt_local_forward", "mt_local_generate",
     "mt_rt_query_sizes", "mt_rt_create", "mt_rt_destroy", "mt_rt_prefill", "mt_rt_step", "mt_rt_finish", "mt_rt_state",

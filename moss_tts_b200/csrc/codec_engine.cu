@@ -302,7 +302,8 @@ extern "C" int mt_rlfq_quantize(mt_codec* h, const float* hidden, int B, int T, 
 
 // encode `nb` samples starting at batch offset b0: wav [B, T*samples_per_frame] -> codes [nq, B, T]
 static int encode_group(mt_codec* h, const float* wav, int B, int T, int b0, int nb, const int64_t* lengths, int nq,
-                        int chunk_frames, int64_t* codes, float* hidden_out, float* ws, cudaStream_t s) {
+                        int chunk_frames, int64_t* codes, float* hidden_out, float* ws, cudaStream_t s,
+                        const StreamRef* sr = nullptr) {
   const mt_codec_config& c = h->cfg;
   long long xs, qs, fs, ys, es;
   per_sample_floats(c, T, &xs, &qs, &fs, &ys, &es);
@@ -322,8 +323,12 @@ static int encode_group(mt_codec* h, const float* wav, int B, int T, int b0, int
     MT_CHECK(width * p == c.input_dim[st], "encoder stage %d: input_dim %d != %d channels x patch %d", st, c.input_dim[st], width, p);
     const float* stage_in = in;
     if (width != 1 && p != 1) { MT_TRY(patchify(in, e, M, width, p, s)); stage_in = e; }   // one channel: the reshape is the identity
-    MT_TRY(run_stage_layers(h, st, stage_in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
-                            x, hbuf, qkv, ff, y, ys * nb, s));
+    if (sr)
+      MT_TRY(run_stage_layers(h, st, stage_in, M, nb, Ts, 0, x, hbuf, qkv, ff, y, ys * nb, s, sr->cache + sr->stage_off[st],
+                              sr->layer_halves[st], sr->frames_done * (Ts / T)));
+    else
+      MT_TRY(run_stage_layers(h, st, stage_in, M, nb, Ts, chunk_frames > 0 ? chunk_frames * static_cast<int>(Ts / T) : 0,
+                              x, hbuf, qkv, ff, y, ys * nb, s));
     const bool last = st + 1 == c.num_stages;
     float* direct = last && hidden_out ? hidden_out + static_cast<long long>(b0) * T * od : nullptr;
     if (h->w.output_proj[st]) {
@@ -362,7 +367,7 @@ extern "C" int mt_codec_encode(mt_codec* h, const float* wav, int B, int T, cons
 }
 
 // ---------------------------------------------------------------------------------------------
-// incremental streaming decode (model.streaming(batch_size) + _decode_frame per push)
+// incremental streaming (model.streaming(batch_size) + _decode_frame / _encode_frame per push)
 // ---------------------------------------------------------------------------------------------
 struct mt_codec_stream {
   mt_codec* h;
@@ -391,7 +396,6 @@ extern "C" int mt_codec_stream_bytes(const mt_codec* h, int B, long long* bytes)
 
 extern "C" int mt_codec_stream_begin(mt_codec* h, int B, void* cache, long long cache_bytes, mt_codec_stream** out) {
   MT_CHECK(h && cache && out && B > 0, "mt_codec_stream_begin: bad argument");
-  MT_CHECK(!h->cfg.encoder, "mt_codec_stream_begin: streaming is implemented for the decoder");
   if (!h->cfg.layer_gemm_f16) return fail(MT_ERR_UNSUPPORTED, "codec streaming needs a codec built with layer_gemm_f16 = 1");
   long long need = 0;
   MT_TRY(mt_codec_stream_bytes(h, B, &need));
@@ -403,18 +407,51 @@ extern "C" int mt_codec_stream_begin(mt_codec* h, int B, void* cache, long long 
   return MT_OK;
 }
 
+// every stage's ring holds `context` tokens: a push of T frames is T * (stage rate / frame rate) tokens there
+static int stream_push_fits(const mt_codec* h, int T, const char* who) {
+  const mt_codec_config& c = h->cfg;
+  long long Ts = c.encoder ? static_cast<long long>(T) * h->upsample_total : T;
+  for (int st = 0; st < c.num_stages; ++st) {
+    if (c.encoder) Ts /= c.patch[st];
+    MT_CHECK(Ts <= c.context[st], "%s: %d frames are %lld tokens at stage %d, more than its ring of %d tokens of context",
+             who, T, Ts, st, c.context[st]);
+    if (!c.encoder) Ts *= c.patch[st];
+  }
+  return MT_OK;
+}
+
 extern "C" int mt_codec_stream_push(mt_codec_stream* st, const int64_t* codes, int nq, int T, float* wav, void* workspace,
                                     long long workspace_bytes, mt_stream stream) {
   MT_CHECK(st && codes && wav && workspace, "mt_codec_stream_push: null argument");
   mt_codec* h = st->h;
+  MT_CHECK(!h->cfg.encoder, "mt_codec_stream_push: this stream belongs to an encoder (mt_codec_stream_push_encode)");
   MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
   MT_CHECK(T > 0, "mt_codec_stream_push: empty push");
-  MT_CHECK(T <= h->cfg.context[0], "mt_codec_stream_push: %d frames exceed the ring capacity (%d frames of context)", T, h->cfg.context[0]);
+  MT_TRY(stream_push_fits(h, T, "mt_codec_stream_push"));
   long long need = 0;
   MT_TRY(mt_codec_workspace_bytes(h, st->B, T, &need));
   MT_CHECK(workspace_bytes >= need, "mt_codec_stream_push: workspace of %lld bytes, %lld needed", workspace_bytes, need);
   StreamRef sr{st->cache, st->stage_off, st->layer_halves, st->frames_done};
   MT_TRY(decode_group(h, codes, nq, st->B, T, 0, st->B, 0, wav, reinterpret_cast<float*>(workspace),
+                      reinterpret_cast<cudaStream_t>(stream), &sr));
+  st->frames_done += T;
+  return MT_OK;
+}
+
+extern "C" int mt_codec_stream_push_encode(mt_codec_stream* st, const float* wav, int T, const int64_t* code_lengths, int nq,
+                                           int64_t* codes, float* hidden, void* workspace, long long workspace_bytes,
+                                           mt_stream stream) {
+  MT_CHECK(st && wav && codes && workspace, "mt_codec_stream_push_encode: null argument");
+  mt_codec* h = st->h;
+  MT_CHECK(h->cfg.encoder && h->has_quant, "mt_codec_stream_push_encode: this stream belongs to a decoder (mt_codec_stream_push)");
+  MT_CHECK(nq > 0 && nq <= h->cfg.num_quantizers, "nq %d out of range (codec has %d quantizers)", nq, h->cfg.num_quantizers);
+  MT_CHECK(T > 0, "mt_codec_stream_push_encode: empty push");
+  MT_TRY(stream_push_fits(h, T, "mt_codec_stream_push_encode"));
+  long long need = 0;
+  MT_TRY(mt_codec_workspace_bytes(h, st->B, T, &need));
+  MT_CHECK(workspace_bytes >= need, "mt_codec_stream_push_encode: workspace of %lld bytes, %lld needed", workspace_bytes, need);
+  StreamRef sr{st->cache, st->stage_off, st->layer_halves, st->frames_done};
+  MT_TRY(encode_group(h, wav, st->B, T, 0, st->B, code_lengths, nq, 0, codes, hidden, reinterpret_cast<float*>(workspace),
                       reinterpret_cast<cudaStream_t>(stream), &sr));
   st->frames_done += T;
   return MT_OK;

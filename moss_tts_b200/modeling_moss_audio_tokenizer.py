@@ -303,23 +303,35 @@ class MossAudioTokenizerModel:
     # ---- streaming (reference :1393-1400, StreamingModule :121-177, RingKVCache :413-480) ------------------
     @contextmanager
     def streaming(self, batch_size: int = 1):
-        """`with model.streaming(batch_size): model._decode_frame(chunk)` per push: every decoder layer keeps a ring
-        cache of `context` tokens on the device between pushes (mt_codec_stream_*).  Decode side only."""
-        if getattr(self, "_stream", None) is not None:
+        """`with model.streaming(batch_size): model._decode_frame(chunk)` / `model._encode_frame(chunk)` per push: every
+        decoder and encoder layer keeps a ring cache of `context` tokens on the device between pushes (mt_codec_stream_*;
+        the reference's _start_streaming reaches every StreamingModule of both halves, :1375-1391)."""
+        if getattr(self, "_streaming", False):
             raise RuntimeError("MossAudioTokenizerModel is already streaming!")
-        need = C.c_longlong(0)
-        L.check(L.lib().mt_codec_stream_bytes(self._engine, int(batch_size), C.byref(need)), "mt_codec_stream_bytes")
-        cache = torch.empty(need.value, dtype=torch.uint8, device=self.device)
-        h = C.c_void_p()
-        L.check(L.lib().mt_codec_stream_begin(self._engine, int(batch_size), L.ptr(cache), C.c_longlong(cache.numel()),
-                                              C.byref(h)), "mt_codec_stream_begin")
-        self._stream, self._stream_batch, self._stream_cache = h, int(batch_size), cache
+        self._streaming = True
+        opened = []
         try:
+            for engine in (self._engine, self._enc_engine):
+                if engine is None:
+                    opened.append((None, None))
+                    continue
+                need = C.c_longlong(0)
+                L.check(L.lib().mt_codec_stream_bytes(engine, int(batch_size), C.byref(need)), "mt_codec_stream_bytes")
+                cache = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+                h = C.c_void_p()
+                L.check(L.lib().mt_codec_stream_begin(engine, int(batch_size), L.ptr(cache), C.c_longlong(cache.numel()),
+                                                      C.byref(h)), "mt_codec_stream_begin")
+                opened.append((h, cache))
+            (self._stream, self._stream_cache), (self._enc_stream, self._enc_stream_cache) = opened
+            self._stream_batch = int(batch_size)
             yield
         finally:
             torch.cuda.current_stream(self.device).synchronize()
-            L.lib().mt_codec_stream_end(self._stream)
-            self._stream = self._stream_cache = None
+            for h, _ in opened:
+                if h is not None:
+                    L.lib().mt_codec_stream_end(h)
+            self._stream = self._stream_cache = self._enc_stream = self._enc_stream_cache = None
+            self._streaming = False
 
     def _stream_push(self, codes: torch.Tensor, codes_lengths: torch.Tensor) -> MossAudioTokenizerDecoderOutput:
         nq, B, T = codes.shape
@@ -382,7 +394,23 @@ class MossAudioTokenizerModel:
         code_lens = code_lens.contiguous()
         codes = torch.empty(nq, B, Tf, dtype=torch.int64, device=self.device)
         hidden = torch.empty(B, Tf, self.config.code_dim, dtype=torch.float32, device=self.device)
-        if B * Tf > 0:
+        if getattr(self, "_enc_stream", None) is not None:
+            if chunk_frames:
+                raise RuntimeError("encoder is already streaming!")    # the reference would enter encoder_module.streaming() again (:1612)
+            if B != self._stream_batch:
+                raise ValueError(f"streaming batch size is {self._stream_batch}, got {B}")
+            if Tf > 0:
+                ws = self._workspace(B, Tf, self._enc_engine)
+                need = C.c_longlong(0)
+                L.check(L.lib().mt_codec_workspace_bytes(self._enc_engine, B, Tf, C.byref(need)), "mt_codec_workspace_bytes")
+                if ws.numel() < need.value:
+                    raise L.MossTTSNativeError("codec workspace too small for a streaming push of the whole batch")
+                with torch.cuda.device(self.device):
+                    L.check(L.lib().mt_codec_stream_push_encode(self._enc_stream, L.ptr(wav), Tf, L.ptr(code_lens), nq,
+                                                                L.ptr(codes), L.ptr(hidden), L.ptr(ws),
+                                                                C.c_longlong(ws.numel()), L.stream_ptr(self.device)),
+                            "mt_codec_stream_push_encode")
+        elif B * Tf > 0:
             ws = self._workspace(B, Tf, self._enc_engine)
             with torch.cuda.device(self.device):
                 L.check(L.lib().mt_codec_encode(self._enc_engine, L.ptr(wav), B, Tf, L.ptr(code_lens), nq, int(chunk_frames),

@@ -50,6 +50,27 @@ def main():
     print("stream golden ok", rec["wav_stream"].shape, "stream-vs-full maxdiff",
           float(np.abs(rec["wav_stream"] - rec["wav_full"]).max()))
 
+    # ---- incremental streaming ENCODE: `with model.streaming(B): model._encode_frame(chunk)` over the same uneven pushes
+    # (the encoder's transformers keep their ring caches between pushes; the quantiser is per frame)
+    wav = torch.randn(2, 1, T * cfg.downsample_rate, generator=_gen(32, "stream_enc")) * 0.3
+    enc = {"versions": _versions(), "cfg": json.dumps(cfg.to_dict()), "seed": 11, "wav": wav.numpy(), "pushes": np.asarray(PUSHES)}
+    codes_s, hid_s = [], []
+    with torch.no_grad(), model.streaming(batch_size=2):
+        pos = 0
+        for n in PUSHES:
+            o = model._encode_frame(wav[:, :, pos * cfg.downsample_rate: (pos + n) * cfg.downsample_rate])
+            codes_s.append(o.audio_codes)
+            hid_s.append(o.encoder_hidden_states)
+            pos += n
+    enc["codes_stream"] = torch.cat(codes_s, dim=-1).numpy()
+    enc["hidden_stream"] = torch.cat(hid_s, dim=-1).numpy()
+    with torch.no_grad():
+        full = model._encode_frame(wav)
+    enc["codes_full"] = full.audio_codes.numpy()
+    np.savez_compressed(os.path.join(OUT, "codec_enc_stream_mini.npz"), **enc)
+    print("encode stream golden ok", enc["codes_stream"].shape, "codes differing from the one-pass encode:",
+          int((enc["codes_stream"] != enc["codes_full"]).sum()), "of", enc["codes_full"].size)
+
 
 if __name__ == "__main__":
     main()

@@ -146,3 +146,43 @@ def test_released_encoder_shapes_one_layer():
     assert s >= SNR_DB and np.array_equal(out.audio_codes_lengths.cpu().numpy(), lens_o.numpy())
     co, margins = oracle.quantize(out.encoder_hidden_states.cpu().contiguous(), lens_o, return_margins=True)
     _assert_codes(out.audio_codes.cpu().numpy(), co.numpy(), margins.numpy(), lens_o.numpy(), "released-width encode")
+
+
+def test_streaming_encode_pushes_match_reference_streaming():
+    """`with model.streaming(B): model._encode_frame(push)` over uneven pushes (3, 10, 1, 7, 12, 2, 5 frames; the
+    12-token rings wrap) through mt_codec_stream_push_encode, against the reference's own streaming run
+    (tests/golden/codec_enc_stream_mini.npz): hidden states >= 40 dB, our codes = the oracle's quantiser on our hidden
+    states up to near-ties, and the stream genuinely differs from the one-pass encode."""
+    g = np.load(os.path.join(GOLDEN, "codec_enc_stream_mini.npz"), allow_pickle=False)
+    cfg = CodecConfig.from_dict(json.loads(str(g["cfg"])))
+    w = make_codec_weights(cfg, seed=int(g["seed"]))
+    model, oracle = MossAudioTokenizerModel(cfg, w, device=DEV), OracleCodec(cfg, w)
+    wav = torch.from_numpy(g["wav"]).to(DEV)
+    B, D = wav.shape[0], cfg.downsample_rate
+    hs, cs, f = [], [], 0
+    with model.streaming(B):
+        for n in [int(x) for x in g["pushes"]]:
+            out = model._encode_frame(wav[..., f * D:(f + n) * D])
+            assert out.audio_codes.shape == (cfg.num_quantizers, B, n)
+            hs.append(out.encoder_hidden_states.cpu()); cs.append(out.audio_codes.cpu()); f += n
+        with pytest.raises(ValueError):
+            model._encode_frame(wav[:1, ..., :D])                                   # batch size fixed by streaming()
+        with pytest.raises(Exception, match="ring"):
+            model._encode_frame(wav[..., : 13 * D])                                 # 13 frames > the 12-token ring
+    hidden, codes = torch.cat(hs, dim=-1), torch.cat(cs, dim=-1)
+    s = snr_db(torch.from_numpy(g["hidden_stream"]), hidden)
+    one = model._encode_frame(wav)                                                  # the rings are gone: one-pass again
+    s_one = snr_db(torch.from_numpy(g["hidden_stream"]), one.encoder_hidden_states.cpu())
+    print(f"[streaming encode] hidden SNR vs reference streaming {s:.1f} dB (one-pass encode vs the same: {s_one:.1f} dB)")
+    assert s >= SNR_DB and s_one < 30.0
+    lens = torch.full((B,), f, dtype=torch.long)
+    codes_o, margins = oracle.quantize(hidden.contiguous(), lens, return_margins=True)
+    _assert_codes(codes.numpy(), codes_o.numpy(), margins.numpy(), lens.numpy(), "streaming encode, own hidden")
+    agree = float((codes.numpy()[0] == g["codes_stream"][0]).mean())
+    print(f"[streaming encode] first-quantiser agreement with the reference's streamed codes: {agree:.3f}")
+    assert agree >= 0.8
+    # encode and decode streams live side by side under one streaming() (reference: every StreamingModule starts)
+    with model.streaming(B):
+        e = model._encode_frame(wav[..., : 4 * D])
+        d = model._decode_frame(e.audio_codes)
+        assert d.audio.shape == (B, 1, 4 * D) and torch.isfinite(d.audio).all()

@@ -62,3 +62,19 @@ def test_chunked_encode_closed_form_matches_reference_streaming():
     assert np.abs(hidden.numpy()[:, :, :n] - g["chunk_hidden"]).max() <= 2e-5 * max(1.0, np.abs(g["chunk_hidden"]).max())
     assert np.array_equal(codes.numpy()[:, :, :n], g["chunk_codes"])
     assert not np.array_equal(g["chunk_codes"], g["codes"][:, :1, :n])      # and it genuinely differs from unchunked
+
+
+def test_streaming_encode_pushes_closed_form_matches_reference_streaming():
+    """`with model.streaming(B): model._encode_frame(chunk)` over uneven pushes (3, 10, 1, 7, 12, 2, 5 frames; the
+    12-frame rings wrap several times): the oracle's per-push closed form (a query sees keys >= end-of-its-push - context)
+    against the reference's own streaming run — hidden states <= 2e-5, codes equal except where the reference's own
+    top-2 code distances are within 1e-5 (argmax near-ties), and genuinely different from the one-pass encode."""
+    g = np.load(os.path.join(GOLDEN, "codec_enc_stream_mini.npz"), allow_pickle=False)
+    cfg = CodecConfig.from_dict(json.loads(str(g["cfg"])))
+    o = OracleCodec(cfg, make_codec_weights(cfg, seed=int(g["seed"])))
+    pushes = [int(n) for n in g["pushes"]]
+    codes, lens, hidden, margins = o.encode_frame(torch.from_numpy(g["wav"]), chunk_frames=pushes, return_margins=True)
+    assert np.abs(hidden.numpy() - g["hidden_stream"]).max() <= 2e-5
+    diff = codes.numpy() != g["codes_stream"]
+    assert diff.sum() <= 2 and (margins.numpy()[diff] <= 1e-5).all(), (int(diff.sum()), margins.numpy()[diff])
+    assert (g["codes_stream"] != g["codes_full"]).mean() > 0.3

@@ -56,7 +56,7 @@ def test_realtime_golden_exercises_stop_and_window():
     assert meta["window"] < g["frames"].shape[1] and meta["penalty"] != 1.0
 
 
-@pytest.mark.parametrize("name", ["rt_tiny_bf16", "rt_mid_bf16"])
+@pytest.mark.parametrize("name", ["rt_tiny_bf16", "rt_mid_bf16", "rt_wide_bf16"])
 def test_realtime_oracle_bf16(name):
     """bf16: exact, or every divergence (teacher-forced along the reference's trajectory) is a near-tie of the
     reference's own top-2 logits (<= 2 bf16 ulp; the oracle restates eager attention, accumulation orders differ)."""
