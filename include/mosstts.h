@@ -82,6 +82,12 @@ int mt_codec_debug_set_absmax(float* slots);
 /* Attention kernel of the fp16-operand codec path: 0 (default) = tcgen05 / TMEM / TMA FlashAttention (codec_attn_tc5.cu),
  * 1 = the mma.sync FlashAttention-2 kernel (codec_attn.cu).  For A/B measurements and cross-checks; process-wide. */
 int mt_codec_debug_set_attention(int mode);
+/* Token-major GEMM kernels (M > 256: prefill, every codec Linear).  mode 0 (default) = chosen by shape: CTA pairs (256 x 256
+ * tiles on tcgen05.mma.cta_group::2, gemm_pair.cu) for K >= 2048, the one-SM 128 x 256 kernel (gemm_big.cu) for the codec's
+ * short-K Linears; 1 = pairs wherever M >= 256; 4 = never pairs; + 2 = the per-lane row-store epilogue in place of the
+ * warp-transposed (coalesced) one.  All combinations give bit-identical results.  For A/B measurements and cross-checks;
+ * process-wide. */
+int mt_gemm_debug_set_pair(int mode);
 
 /* ------------------------------------------------------------------------------------------
  * Linear layer:  out[M,N] = epilogue( x[M,K] * w[N,K]^T )       (every nn.Linear on the path:

@@ -20,7 +20,7 @@ MT_CODEC_MAX_STAGES = 8
 MT_GEMM_STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 EXPORTS = [
-    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_debug_set_attn_cluster", "mt_debug_set_trace", "mt_codec_debug_set_absmax", "mt_codec_debug_set_attention", "mt_gemm", "mt_gemm_static_scratch",
+    "mt_version", "mt_last_error", "mt_launch_count", "mt_debug_force_simt", "mt_debug_set_pdl", "mt_debug_set_attn_cluster", "mt_debug_set_trace", "mt_codec_debug_set_absmax", "mt_codec_debug_set_attention", "mt_gemm_debug_set_pair", "mt_gemm", "mt_gemm_static_scratch",
     "mt_lm_query_sizes", "mt_lm_create", "mt_lm_destroy", "mt_lm_forward", "mt_lm_embed", "mt_lm_generate",
     "mt_lm_stream_begin", "mt_lm_stream_steps", "mt_lm_stream_end", "mt_stream_gather_frames", "mt_crossfade",
     "mt_sample_tokens", "mt_sample_tokens_full", "mt_sample_full_scratch_bytes", "mt_find_last_equal", "mt_apply_delay_pattern", "mt_apply_de_delay_pattern",

@@ -10,6 +10,8 @@ extern "C" const char* mt_last_error(void) { return mt::last_error(); }
 extern "C" long long mt_launch_count(void) { return g_launches; }
 extern "C" int mt_debug_force_simt(int on) { g_force_simt = on != 0; return MT_OK; }
 
+extern "C" int mt_gemm_debug_set_pair(int mode) { mt::g_gemm_pair_mode = mode; return MT_OK; }
+
 extern "C" int mt_debug_set_pdl(int on) { mt::set_pdl(on); return MT_OK; }
 extern "C" int mt_debug_set_attn_cluster(int cs) {
   if (cs != 0 && cs != 1 && cs != 2 && cs != 4 && cs != 8) return MT_ERR_ARG;

@@ -54,6 +54,7 @@ struct Epi {
   const float* scale; int round_bf16;
   int M, N;                       // logical output extent
   float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
+  int direct_store;               // token-major kernels: 1 = per-lane row stores (A/B of the warp-transposed epilogue)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }
@@ -85,6 +86,11 @@ static inline int mma_kind(int dtype) { return dtype == MT_DTYPE_BF16 ? 1 : (dty
 
 // Persistent 128x256-tile kernel for token-major problems (M > 256): prefill and the codec (gemm_big.cu).
 int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s);
+// The same problems on CTA pairs: 256x256 tiles, tcgen05.mma.cta_group::2 (gemm_pair.cu); mt_gemm_debug_set_pair(1) keeps
+// the one-SM kernel for A/B measurements.
+bool linear_pair_applies(const LinearPlan& p);
+int linear_pair(const LinearPlan& p, const Epi& ep, cudaStream_t s);
+extern int g_gemm_pair_mode;
 
 // Persistent decode-orientation kernel (M <= 256): one CTA per SM streams (weight tile, K split) units (gemm_dec.cu).
 int linear_dec(const LinearPlan& p, Epi ep, cudaStream_t s);

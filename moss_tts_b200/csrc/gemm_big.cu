@@ -11,6 +11,7 @@
 // epilogue as in the MMAs.  Warp w may only touch TMEM lanes 32*(w%4)..+31, so the 8 epilogue warps
 // split a tile as (lane quarter = w%4) x (column half = (w-2)/4).
 #include "gemm.cuh"
+#include "gemm_epi.cuh"
 #include "ptx.cuh"
 
 namespace mt {
@@ -22,7 +23,9 @@ constexpr int kEpiWarps = 8;
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kABytes = kBM * kKBytes, kBBytes = kBN * kKBytes, kStageBytes = kABytes + kBBytes;
 constexpr int kBarOffset = kStages * kStageBytes;
-constexpr int kSmemTotal = kBarOffset + (2 * kStages + 4) * 8 + 16 + 1024;
+constexpr int kEpiOffset = kBarOffset + (2 * kStages + 4) * 8 + 32;     // 8 warps x 4 KB: epilogue transposition tiles (16-byte aligned)
+constexpr int kSmemTotal = kEpiOffset + kEpiWarps * kEpiTileFloats * 4 + 1024;
+static_assert(kSmemTotal <= 232448, "shared memory budget");
 
 template <int KIND /*1 bf16, 2 tf32, 3 fp16*/>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -149,13 +152,16 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     // ===== epilogue =====
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
     const int half = (warp - 2) >> 2;          // column half
+    float* tile = reinterpret_cast<float*>(smem + kEpiOffset) + (warp - 2) * kEpiTileFloats;
+    const bool coalesced = epi_coalesced_ok(ep);
     pdl_wait();                                // residual reads / output writes follow the previous kernel
     int mt = 0, nt = 0;
     for (int i = 0; tile_of(i, mt, nt); ++i) {
       const int buf = i & 1;
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
       ptx::tc_fence_after();
-      const int m = mt * kBM + q * 32 + lane;
+      const int m0 = mt * kBM + q * 32;
+      const int m = m0 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBN + half * (kBN / 2);
 #pragma unroll 1
       for (int c0 = 0; c0 < kBN / 2; c0 += 32) {
@@ -163,84 +169,8 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         ptx::tmem_ld32(taddr + c0, r);
         ptx::tmem_ld_wait();
         const int n0 = nt * kBN + half * (kBN / 2) + c0;
-        if (m < M && n0 < N) {
-          const bool full_chunk = n0 + 32 <= N;
-          float v[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (ep.bias) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] += ep.bias[n0 + j];
-          }
-          if (ep.act == 1) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-          }
-          if (ep.round_bf16) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = rbf(v[j]);
-          }
-          if (ep.scale) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] *= ep.scale[n0 + j];
-          }
-          if (ep.residual) {
-            if (ep.out_f32 == 1) {
-              const float* rr = reinterpret_cast<const float*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
-              if (full_chunk && (ep.ldr & 3) == 0) {
-#pragma unroll
-                for (int j = 0; j < 32; j += 4) {
-                  const float4 x = *reinterpret_cast<const float4*>(rr + j);
-                  v[j] = x.x + v[j]; v[j + 1] = x.y + v[j + 1]; v[j + 2] = x.z + v[j + 2]; v[j + 3] = x.w + v[j + 3];
-                }
-              } else {
-                for (int j = 0; j < 32; ++j) if (n0 + j < N) v[j] = rr[j] + v[j];
-              }
-            } else if (ep.out_f32 == 2) {
-              const __half* rr = reinterpret_cast<const __half*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
-              for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] = __half2float(rr[j]) + v[j];
-            } else {
-              const bf16* rr = reinterpret_cast<const bf16*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0;
-              for (int j = 0; j < 32; ++j) if (full_chunk || n0 + j < N) v[j] = bf2f(rr[j]) + v[j];
-            }
-          }
-          if (ep.out_f32 == 1) {
-            float* dst = reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
-            if (full_chunk && (ep.ldo & 3) == 0) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = v[j];
-            }
-          } else if (ep.out_f32 == 2) {
-            __half* dst = reinterpret_cast<__half*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
-            if (full_chunk && (ep.ldo & 7) == 0) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 pk;
-                pk.x = pack_f16(v[j], v[j + 1]); pk.y = pack_f16(v[j + 2], v[j + 3]);
-                pk.z = pack_f16(v[j + 4], v[j + 5]); pk.w = pack_f16(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(dst + j) = pk;
-              }
-            } else {
-              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = __float2half_rn(v[j]);
-            }
-          } else {
-            bf16* dst = reinterpret_cast<bf16*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
-            if (full_chunk && (ep.ldo & 7) == 0) {
-#pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 pk;
-                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
-                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(dst + j) = pk;
-              }
-            } else {
-              for (int j = 0; j < 32; ++j) if (n0 + j < N) dst[j] = f2bf(v[j]);
-            }
-          }
-        }
+        if (coalesced && n0 + 32 <= N) { if (m0 < M) epi_chunk32_warp(ep, m0, n0, M, r, tile, lane); }
+        else if (m < M && n0 < N) epi_chunk32(ep, m, n0, N, r);
       }
       // this warp is done reading the accumulator: hand it back to the MMA warp
       ptx::tc_fence_before();

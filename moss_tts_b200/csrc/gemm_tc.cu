@@ -123,6 +123,7 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   ep.out = p.out; ep.ldo = p.ldo; ep.out_f32 = out_kind(p.dtype_out);
   ep.bias = p.bias; ep.act = p.act; ep.residual = p.residual; ep.ldr = p.ldr; ep.scale = p.scale;
   ep.round_bf16 = p.round_bf16; ep.M = p.M; ep.N = p.N; ep.partial = nullptr;
+  ep.direct_store = (g_gemm_pair_mode & 2) ? 1 : 0;
 
   if (p.impl == MT_GEMM_SIMT || g_force_simt) {
     if (p.out_splits) { *p.out_splits = 1; ep.partial = p.workspace; }
@@ -144,7 +145,8 @@ int linear(const LinearPlan& p, cudaStream_t s) {
     const int k_elems = 128 / dtype_bytes(p.dtype_in);
     MT_CHECK(p.K % k_elems == 0, "linear: tile-major weights need K %% %d == 0 (K=%d)", k_elems, p.K);
   }
-  return p.M <= 256 ? linear_dec(p, ep, s) : linear_big(p, ep, s);
+  if (p.M <= 256) return linear_dec(p, ep, s);
+  return linear_pair_applies(p) ? linear_pair(p, ep, s) : linear_big(p, ep, s);
 }
 
 int splitk_reduce(const Epi& ep, int splits, cudaStream_t s) {

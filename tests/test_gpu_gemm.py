@@ -161,3 +161,49 @@ def test_gemm_tile_major_weights(M, N, K, dt, impl):
     b = gemm(x, tile_major(w), out_dtype=torch.float32, impl=impl | L.MT_GEMM_W_TILED | L.MT_GEMM_W_STATIC,
              workspace_mb=0, N=N)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("M,N,K,dt", [(256, 256, 64, torch.bfloat16), (257, 300, 192, torch.bfloat16), (6144, 6144, 1024, torch.bfloat16),
+                                      (6144, 4096, 4096, torch.bfloat16), (1000, 3072, 768, torch.float16), (8000, 1280, 5120, torch.float16),
+                                      (16000, 768, 768, torch.float16), (700, 240, 768, torch.float32), (6000, 2304, 768, torch.float32),
+                                      (40000, 768, 256, torch.float16)])
+def test_gemm_cta_pair_kernel_matches_one_sm_kernel(M, N, K, dt):
+    """gemm_pair.cu (CTA pairs, 256 x 256 tiles, tcgen05.mma.cta_group::2: the product path for K >= 2048) against the one-SM
+    kernel with both of its epilogues (warp-transposed coalesced stores / per-lane row stores) and a torch fp32 reference:
+    same K order inside the tensor core and the same arithmetic per element, so all outputs are bit-identical; ragged M / N
+    tiles, ring wrap-around, more pair tiles than pairs, every epilogue."""
+    g = torch.Generator(device=DEV).manual_seed(M + 3 * N + K)
+    x = torch.randn(M, K, device=DEV, generator=g).to(dt)
+    w = (torch.randn(N, K, device=DEV, generator=g) * K ** -0.5).to(dt)
+    res = torch.randn(M, N, device=DEV, generator=g)
+    scale = torch.rand(N, device=DEV, generator=g)
+    bias = torch.randn(N, device=DEV, generator=g)
+    half_out = torch.float16 if dt == torch.float16 else (torch.bfloat16 if dt == torch.bfloat16 else torch.float32)
+    cases = [dict(out_dtype=torch.float32), dict(out_dtype=torch.float32, residual=res, scale=scale),
+             dict(out_dtype=half_out, act=1, bias=bias)]
+    if dt == torch.bfloat16:
+        from moss_tts_b200.modeling_moss_tts import tile_major
+        if K % 64 == 0:
+            cases.append(dict(out_dtype=torch.float32, impl=L.MT_GEMM_AUTO | L.MT_GEMM_W_TILED | L.MT_GEMM_W_STATIC, N=N, tiled=True))
+    ref = x.float() @ w.float().T
+    tol = (2e-3 if dt != torch.float32 else 1e-2) * max(1.0, ref.abs().max().item())
+    for kw in cases:
+        kw = dict(kw)
+        ww = tile_major(w) if kw.pop("tiled", False) else w
+        try:
+            L.lib().mt_gemm_debug_set_pair(4 + 2)            # one-SM kernel, per-lane row stores (the round-1 form)
+            old = gemm(x, ww, **kw)
+            L.lib().mt_gemm_debug_set_pair(4)                # one-SM kernel, warp-transposed epilogue
+            mid = gemm(x, ww, **kw)
+            L.lib().mt_gemm_debug_set_pair(1)                # CTA pairs
+            new = gemm(x, ww, **kw)
+            again = gemm(x, ww, **kw)
+        finally:
+            L.lib().mt_gemm_debug_set_pair(0)
+        assert torch.equal(old, mid), (kw.keys(), (old.float() - mid.float()).abs().max().item())
+        assert torch.equal(new, gemm(x, ww, **kw))           # the product's choice for this shape
+        assert torch.isfinite(new.float()).all()
+        assert torch.equal(old, new), (kw.keys(), (old.float() - new.float()).abs().max().item())
+        if set(kw) <= {"out_dtype", "impl", "N"} and kw["out_dtype"] == torch.float32:
+            assert (new - ref).abs().max().item() <= tol
+        assert torch.equal(new, again)           # deterministic
