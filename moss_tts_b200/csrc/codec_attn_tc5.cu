@@ -319,11 +319,11 @@ bool codec_attention_tc5_supported(int hd, long long rows, int d) {
 
 // qkv is rotated IN PLACE (q and k), then attended: out [B*T, heads*64] half
 int codec_attention_tc5(void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk, cudaStream_t s,
-                        const float* rope_table) {
+                        const float* rope_table, bool pre_rotated) {
   MT_CHECK(hd == kD && rope_table, "codec_attention_tc5: head_dim 64 and a RoPE table are required");
   const int d = heads * kD;
   const long long M = static_cast<long long>(B) * T;
-  {
+  if (!pre_rotated) {
     const long long total = M * (2 * d / 8);
     int blocks = static_cast<int>(cdivll(total, 256));
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;

@@ -62,11 +62,13 @@ static void per_sample_floats(const mt_codec_config& c, int T, long long* xs, lo
 
 static int codec_linear(const void* x, long long M, int K, const void* w, int N, void* out, long long ldo,
                         int act, const float* residual, const float* scale, cudaStream_t s, int din = MT_DTYPE_F32,
-                        int dout = MT_DTYPE_F32) {
+                        int dout = MT_DTYPE_F32, const float* rope = nullptr, int rope_T = 0, int rope_cols = 0) {
   LinearPlan p;
   p.dtype_in = din; p.dtype_out = dout;
   p.M = static_cast<int>(M); p.N = N; p.K = K; p.x = x; p.ldx = K; p.w = w; p.ldw = K; p.out = out; p.ldo = ldo;
   p.act = act; p.residual = residual; p.ldr = ldo; p.scale = scale;
+  p.w_static = true;                       // codec weights never change while the handle is alive
+  p.rope = rope; p.rope_T = rope_T; p.rope_cols = rope_cols;
   return linear(p, s);
 }
 
@@ -158,10 +160,14 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
     const mt_codec_layer& L = h->layers[st][l];
     MT_TRY(layernorm(x, L.norm1_w, L.norm1_b, hbuf, M, d, s, h16));
     if (probe) MT_TRY(absmax_f16(hbuf, M * d, probe + 0, s));
-    // the tcgen05 attention takes q and k already rotated (a rotary epilogue inside the in_proj GEMM was measured: the
-    // per-row table reads cost the short-K GEMM +80 us per launch, more than the separate in-place pass)
+    // the tcgen05 attention takes q and k already rotated.  Since the token-major GEMMs' epilogue walks its tile row-major
+    // (gemm_epi.cuh) the rotation is part of the in_proj epilogue: coalesced table reads, the fp32 accumulators rotated
+    // before their one rounding to half (with the per-lane-row epilogue of round 1 the same fusion cost +80 us per launch).
+    // Otherwise codec_attention_tc5 rotates q and k in place first.
     const bool tc5 = a16 && !ring && g_attn_mode == 0;
-    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32));
+    const bool rope_in_gemm = tc5 && M > 256 && !g_force_simt && !(g_gemm_pair_mode & (2 | 16)) && d % 64 == 0;
+    MT_TRY(codec_linear(hbuf, M, d, L.in_proj, 3 * d, qkv, 3 * d, 0, nullptr, nullptr, s, din, a16 ? MT_DTYPE_F16 : MT_DTYPE_F32,
+                        rope_in_gemm ? y : nullptr, static_cast<int>(Ts), 2 * d));
     if (probe) MT_TRY(absmax_f16(qkv, M * 3 * d, probe + 1, s));
     if (ring) {
       // streaming push: the layer's ring cache takes the new keys / values, the new queries attend to the ring
@@ -170,7 +176,7 @@ static int run_stage_layers(mt_codec* h, int st, const float* in, long long M, i
       MT_TRY(codec_kv_append_f16(qkv, lr, nb, static_cast<int>(Ts), heads, c.context[st], pos0, y, s));
       MT_TRY(codec_attention_ring_f16(qkv, lr, hbuf, nb, static_cast<int>(Ts), heads, c.context[st], pos0, s, y));
     } else if (tc5) {
-      MT_TRY(codec_attention_tc5(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
+      MT_TRY(codec_attention_tc5(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y, rope_in_gemm));
     } else if (a16) {
       MT_TRY(codec_attention_f16(qkv, hbuf, nb, static_cast<int>(Ts), heads, 64, c.context[st], chunk, s, y));
     } else if (simt_attn || !table_fits) {

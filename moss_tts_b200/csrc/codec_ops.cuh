@@ -29,7 +29,7 @@ int codec_attention_f16(const void* qkv, void* out, int B, int T, int heads, int
 // on the 5th-generation tensor cores.  The product path of the one-pass decode / encode; codec_attention_f16 stays the
 // kernel of the incremental ring-cache streaming path and the A/B cross-check (mt_codec_debug_set_attention(1)).
 int codec_attention_tc5(void* qkv, void* out, int B, int T, int heads, int hd, int context, int chunk, cudaStream_t s,
-                        const float* rope_table);
+                        const float* rope_table, bool pre_rotated = false);
 // Streaming decode (RingKVCache :413-480, MHAState :488-499).  ring: one layer's cache [B][cap][2][heads*64] half, slot =
 // position % cap, K stored AFTER RoPE (as the reference caches it).  kv_append rotates the new tokens' keys (table row t =
 // position pos0 + t) and writes k, v into their slots; the attention then reads q from qkv (rotated on the way in) and

@@ -37,6 +37,10 @@ struct LinearPlan {
   // w is stored tile-major: [ceil(N/128)][K/k_elems][128][k_elems] (k_elems = 64 bf16 / 32 fp32), so
   // each TMA box is 16 KB of consecutive HBM addresses.  ldw is ignored; w_tmap must match.
   bool w_tiled = false;
+  // Token-major kernels, 16-bit output, no activation: rotary embedding applied to output columns [0, rope_cols) in the
+  // epilogue (interleaved pairs inside 64-wide heads; rope = [rope_T][32] (cos, sin) floats, row = token index % rope_T) --
+  // the codec's in_proj hands the attention kernel rotated q and k.
+  const float* rope = nullptr; int rope_T = 0, rope_cols = 0;
   // Decode orientation only: when *tile_filter_flag == 0 (device int) only output features
   // [tile_lo, tile_hi] (rounded out to 128-row weight tiles) are computed; the rest of `out` is left
   // untouched.  nullptr = always compute everything.
@@ -55,6 +59,7 @@ struct Epi {
   int M, N;                       // logical output extent
   float* partial;                 // != nullptr: write raw fp32 partials [split][M][N]
   int direct_store;               // token-major kernels: 1 = per-lane row stores (A/B of the warp-transposed epilogue)
+  const float4* rope; int rope_T, rope_cols;   // != nullptr: rotate columns [0, rope_cols) (see LinearPlan::rope)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f)); }

@@ -2,6 +2,7 @@
 // accumulator bits in r[] -> bias / GELU(erf) / bf16 round / LayerScale / residual -> fp32, fp16 or bf16 store.
 #pragma once
 #include "gemm.cuh"
+#include "ptx.cuh"
 
 namespace mt {
 
@@ -125,28 +126,48 @@ __device__ __forceinline__ bool epi_coalesced_ok(const Epi& ep) {
   return ok;
 }
 
-__device__ __forceinline__ void epi_chunk32_warp(const Epi& ep, int m0, int n0, int M, const uint32_t (&r)[32], float* tile,
-                                                 int lane) {
-  // residual of this chunk, row-major over the warp (issued first: nothing below depends on it until the final add)
-  float4 res32[8];
-  uint4 res16[4];
-  if (ep.residual) {
-    if (ep.out_f32 == 1) {
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int m = m0 + i * 4 + (lane >> 3);
-        if (m < M)
-          res32[i] = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0 + (lane & 7) * 4);
-      }
-    } else {
+// residual of one 32 x 32 chunk, row-major over the warp.  The kernels request chunk c + 1 (and chunk 0 of the next tile,
+// before they wait for its accumulator) while chunk c is processed: the loads have a whole chunk of work to land behind.
+struct EpiRes {
+  uint4 w[8];        // fp32 residual: 8 x float4 (rows i * 4 + lane / 8); 16-bit residual: w[0..3] (rows i * 8 + lane / 4)
+};
+__device__ __forceinline__ void epi_res_load(const Epi& ep, int m0, int n0, int M, int lane, EpiRes& res) {
+  if (ep.rope) {
+    // rotary epilogue (16-bit output, no residual): the (cos, sin) pairs of the lane's four (row, 8-column group) cells
+    if (n0 < ep.rope_cols) {
+      const int grp = ((n0 + (lane & 3) * 8) & 63) >> 3;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int m = m0 + i * 8 + (lane >> 2);
-        if (m < M)
-          res16[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0 + (lane & 3) * 8);
+        if (m < M) {
+          const float4* cs = ep.rope + static_cast<long long>(m % ep.rope_T) * 16 + 2 * grp;
+          res.w[2 * i] = *reinterpret_cast<const uint4*>(cs);
+          res.w[2 * i + 1] = *reinterpret_cast<const uint4*>(cs + 1);
+        }
       }
     }
+    return;
   }
+  if (!ep.residual) return;
+  if (ep.out_f32 == 1) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int m = m0 + i * 4 + (lane >> 3);
+      if (m < M)
+        res.w[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const float*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0 + (lane & 7) * 4);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int m = m0 + i * 8 + (lane >> 2);
+      if (m < M)
+        res.w[i] = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(ep.residual) + static_cast<long long>(m) * ep.ldr + n0 + (lane & 3) * 8);
+    }
+  }
+}
+
+__device__ __forceinline__ void epi_chunk32_warp(const Epi& ep, int m0, int n0, int M, const uint32_t (&r)[32], float* tile,
+                                                 int lane, const EpiRes& res) {
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
@@ -178,7 +199,10 @@ __device__ __forceinline__ void epi_chunk32_warp(const Epi& ep, int m0, int n0, 
       const int m = m0 + row;
       float4 a = tile4[row * 8 + ((lane & 7) ^ (row & 7))];
       if (m < M) {
-        if (ep.residual) { a.x = res32[i].x + a.x; a.y = res32[i].y + a.y; a.z = res32[i].z + a.z; a.w = res32[i].w + a.w; }
+        if (ep.residual) {
+          a.x = __uint_as_float(res.w[i].x) + a.x; a.y = __uint_as_float(res.w[i].y) + a.y;
+          a.z = __uint_as_float(res.w[i].z) + a.z; a.w = __uint_as_float(res.w[i].w) + a.w;
+        }
         *reinterpret_cast<float4*>(reinterpret_cast<float*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0 + c) = a;
       }
     }
@@ -190,8 +214,18 @@ __device__ __forceinline__ void epi_chunk32_warp(const Epi& ep, int m0, int n0, 
       const float4 lo = tile4[row * 8 + ((2 * (lane & 3)) ^ (row & 7))], hi = tile4[row * 8 + ((2 * (lane & 3) + 1) ^ (row & 7))];
       float a[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
       if (m < M) {
-        if (ep.residual) {
-          const uint32_t w[4] = {res16[i].x, res16[i].y, res16[i].z, res16[i].w};
+        if (ep.rope && n0 + c < ep.rope_cols) {
+          // rotary embedding of a q | k column group (interleaved pairs, 64-wide heads): the in_proj epilogue of the codec
+          // rotates the fp32 accumulators, one rounding to half instead of the separate pass's two
+          const float4 cs0 = *reinterpret_cast<const float4*>(&res.w[2 * i]), cs1 = *reinterpret_cast<const float4*>(&res.w[2 * i + 1]);
+          const float x0 = a[0], x1 = a[1], x2 = a[2], x3 = a[3], x4 = a[4], x5 = a[5], x6 = a[6], x7 = a[7];
+          a[0] = x0 * cs0.x - x1 * cs0.y; a[1] = x0 * cs0.y + x1 * cs0.x;
+          a[2] = x2 * cs0.z - x3 * cs0.w; a[3] = x2 * cs0.w + x3 * cs0.z;
+          a[4] = x4 * cs1.x - x5 * cs1.y; a[5] = x4 * cs1.y + x5 * cs1.x;
+          a[6] = x6 * cs1.z - x7 * cs1.w; a[7] = x6 * cs1.w + x7 * cs1.z;
+        }
+        if (ep.residual && !ep.rope) {
+          const uint32_t w[4] = {res.w[i].x, res.w[i].y, res.w[i].z, res.w[i].w};
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             if (ep.out_f32 == 2) {
@@ -210,6 +244,25 @@ __device__ __forceinline__ void epi_chunk32_warp(const Epi& ep, int m0, int n0, 
     }
   }
   __syncwarp();                                 // the tile is rewritten by the next chunk
+}
+
+// One accumulator tile of an epilogue warp: its 32 token rows (m0 ..) x COLS features from n_base, accumulator at `taddr`.
+// `cur` holds the residual of chunk 0, requested by the caller BEFORE it waited for the accumulator.
+template <int COLS>
+__device__ __forceinline__ void epi_tile_warp(const Epi& ep, bool coalesced, int m0, int n_base, int M, int N, uint32_t taddr,
+                                              float* tile, int lane, EpiRes& cur) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < COLS; c0 += 32) {
+    const int n0 = n_base + c0;
+    EpiRes nxt = cur;
+    if (c0 + 32 < COLS && coalesced && n0 + 64 <= N && m0 < M) epi_res_load(ep, m0, n0 + 32, M, lane, nxt);
+    uint32_t r[32];
+    ptx::tmem_ld32(taddr + c0, r);
+    ptx::tmem_ld_wait();
+    if (coalesced && n0 + 32 <= N) { if (m0 < M) epi_chunk32_warp(ep, m0, n0, M, r, tile, lane, cur); }
+    else if (m0 + lane < M && n0 < N) epi_chunk32(ep, m0 + lane, n0, N, r);
+    cur = nxt;
+  }
 }
 
 }  // namespace mt

@@ -225,20 +225,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int mt = 0, nt = 0;
     for (int i = 0; tile_of(i, mt, nt); ++i) {
       const int buf = i & 1;
+      const int m0 = mt * kTileM + static_cast<int>(rank) * kPM + q * 32;
+      const int n_base = nt * kTileN + half * (kTileN / 2);
+      EpiRes res;
+      if (coalesced && n_base + 32 <= N && m0 < M) epi_res_load(ep, m0, n_base, M, lane, res);   // lands behind the wait
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
       ptx::tc_fence_after();
-      const int m0 = mt * kTileM + static_cast<int>(rank) * kPM + q * 32;
-      const int m = m0 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kTileN + half * (kTileN / 2);
-#pragma unroll 1
-      for (int c0 = 0; c0 < kTileN / 2; c0 += 32) {
-        uint32_t r[32];
-        ptx::tmem_ld32(taddr + c0, r);
-        ptx::tmem_ld_wait();
-        const int n0 = nt * kTileN + half * (kTileN / 2) + c0;
-        if (coalesced && n0 + 32 <= N) { if (m0 < M) epi_chunk32_warp(ep, m0, n0, M, r, tile, lane); }
-        else if (m < M && n0 < N) epi_chunk32(ep, m, n0, N, r);
-      }
+      epi_tile_warp<kTileN / 2>(ep, coalesced, m0, n_base, M, N, taddr, tile, lane, res);
       // this warp is done reading the accumulator: hand it back to the pair's MMA thread
       ptx::tc_fence_before();
       __syncwarp();

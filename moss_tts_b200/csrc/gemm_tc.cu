@@ -124,6 +124,14 @@ int linear(const LinearPlan& p, cudaStream_t s) {
   ep.bias = p.bias; ep.act = p.act; ep.residual = p.residual; ep.ldr = p.ldr; ep.scale = p.scale;
   ep.round_bf16 = p.round_bf16; ep.M = p.M; ep.N = p.N; ep.partial = nullptr;
   ep.direct_store = (g_gemm_pair_mode & 2) ? 1 : 0;
+  ep.rope = reinterpret_cast<const float4*>(p.rope); ep.rope_T = p.rope_T; ep.rope_cols = p.rope_cols;
+  if (p.rope) {
+    // the rotation lives in the warp-transposed epilogue of the token-major tcgen05 kernels only
+    MT_CHECK(p.M > 256 && p.impl != MT_GEMM_SIMT && !g_force_simt && !ep.direct_store && p.act == 0 && !p.out_splits && !p.residual &&
+                 out_kind(p.dtype_out) != 1 && p.N % 32 == 0 && p.ldo % 8 == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0 &&
+                 p.rope_T > 0 && p.rope_cols % 64 == 0 && (reinterpret_cast<uintptr_t>(p.rope) & 15) == 0,
+             "linear: a rotary epilogue needs the token-major kernel, a 16-bit 16-byte aligned output and N %% 32 == 0");
+  }
 
   if (p.impl == MT_GEMM_SIMT || g_force_simt) {
     if (p.out_splits) { *p.out_splits = 1; ep.partial = p.workspace; }

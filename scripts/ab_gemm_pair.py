@@ -68,7 +68,7 @@ def main():
     codec = MossAudioTokenizerModel.random_init(CodecConfig.released(), device=DEV, seed=99, workspace_bytes=24 << 30)
     codes = torch.randint(0, 1024, (32, 64, 125), device=DEV)
     res = {}
-    for mode in (6, 4, 1, 0, 6, 4, 1, 0):
+    for mode in (6, 4, 1, 0, 16, 6, 4, 1, 0, 16):
         L.lib().mt_gemm_debug_set_pair(mode)
         for _ in range(2):
             codec.decode(codes)
@@ -78,7 +78,7 @@ def main():
             e0.record(); codec.decode(codes); e1.record(); torch.cuda.synchronize()
             ts.append(e0.elapsed_time(e1))
         ts.sort()
-        res.setdefault({4: "one_sm", 1: "pair", 6: "one_sm_direct_epilogue", 0: "product_choice"}[mode], []).append(round(ts[2], 2))
+        res.setdefault({4: "one_sm", 1: "pair", 6: "one_sm_direct_epilogue", 0: "product_choice", 16: "product_with_rotary_prepass"}[mode], []).append(round(ts[2], 2))
     L.lib().mt_gemm_debug_set_pair(0)
     print(json.dumps({"codec_decode_ms_64x125": res}))
 
