@@ -186,3 +186,28 @@ def test_streaming_encode_pushes_match_reference_streaming():
         e = model._encode_frame(wav[..., : 4 * D])
         d = model._decode_frame(e.audio_codes)
         assert d.audio.shape == (B, 1, 4 * D) and torch.isfinite(d.audio).all()
+
+
+def test_stream_push_entry_points_refuse_the_wrong_half(enc):
+    """mt_codec_stream_push on an encoder stream / mt_codec_stream_push_encode on a decoder stream fail loudly (C ABI)."""
+    import ctypes as C
+    from moss_tts_b200 import _lib as L
+    g, cfg, model, oracle = enc
+    B, D = 1, cfg.downsample_rate
+    wav = torch.zeros(B, 2 * D, device=DEV)
+    codes = torch.zeros(cfg.num_quantizers, B, 2, dtype=torch.int64, device=DEV)
+    hidden = torch.empty(B, 2, cfg.code_dim, device=DEV)
+    out_wav = torch.empty(B, 2 * D, device=DEV)
+    ws = torch.empty(64 << 20, dtype=torch.uint8, device=DEV)
+    with model.streaming(B):
+        rc = L.lib().mt_codec_stream_push(model._enc_stream, L.ptr(codes), cfg.num_quantizers, 2, L.ptr(out_wav), L.ptr(ws),
+                                          C.c_longlong(ws.numel()), L.stream_ptr(DEV))
+        assert rc != 0 and b"encoder" in L.lib().mt_last_error()
+        rc = L.lib().mt_codec_stream_push_encode(model._stream, L.ptr(wav), 2, None, cfg.num_quantizers, L.ptr(codes), L.ptr(hidden),
+                                                 L.ptr(ws), C.c_longlong(ws.numel()), L.stream_ptr(DEV))
+        assert rc != 0 and b"decoder" in L.lib().mt_last_error()
+        rc = L.lib().mt_codec_stream_push_encode(model._enc_stream, L.ptr(wav), 0, None, cfg.num_quantizers, L.ptr(codes), L.ptr(hidden),
+                                                 L.ptr(ws), C.c_longlong(ws.numel()), L.stream_ptr(DEV))
+        assert rc != 0 and b"empty" in L.lib().mt_last_error()
+        out = model._encode_frame(wav.unsqueeze(1))          # the stream is still usable after the refused calls
+        assert out.audio_codes.shape == (cfg.num_quantizers, B, 2)
