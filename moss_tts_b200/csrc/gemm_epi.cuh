@@ -80,7 +80,18 @@ __device__ __forceinline__ void epi_chunk32(const Epi& ep, int m, int n0, int N,
     }
   } else if (ep.out_f32 == 2) {
     __half* dst = reinterpret_cast<__half*>(ep.out) + static_cast<long long>(m) * ep.ldo + n0;
-    if (full_chunk && (ep.ldo & 7) == 0) {
+    if (full_chunk && (ep.ldo & 15) == 0 && (reinterpret_cast<uintptr_t>(ep.out) & 31) == 0) {
+      // 32-byte stores (sm_100): every store writes a whole sector of this lane's row
+#pragma unroll
+      for (int j = 0; j < 32; j += 16) {
+        uint32_t pk[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) pk[e] = pack_f16(v[j + 2 * e], v[j + 2 * e + 1]);
+        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + j), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]),
+                     "r"(pk[3]), "r"(pk[4]), "r"(pk[5]), "r"(pk[6]), "r"(pk[7])
+                     : "memory");
+      }
+    } else if (full_chunk && (ep.ldo & 7) == 0) {
 #pragma unroll
       for (int j = 0; j < 32; j += 8) {
         uint4 pk;
