@@ -123,7 +123,7 @@ __device__ __forceinline__ void epi_chunk32(const Epi& ep, int m, int n0, int N,
 // so the direct form above touches 32 different rows with every 16-byte load / store.  Here the warp transposes its
 // 32 x 32 chunk through a swizzled shared-memory tile and then walks it in row-major order: every global access of the
 // warp covers whole 128-byte (fp32) / 64-byte (16-bit) row segments, the residual is read the same way, and its loads are
-// issued before the transposition so their latency is hidden.  Arithmetic per element is the direct form's, in the same
+// issued a chunk ahead (EpiRes) so their latency is hidden.  Arithmetic per element is the direct form's, in the same
 // order (bit-identical results).  Needs n0 + 32 <= N and 16-byte aligned rows (epi_coalesced_ok).
 // ---------------------------------------------------------------------------------------------------------------------
 constexpr int kEpiTileFloats = 32 * 32;       // 32 rows x 8 sixteen-byte chunks, chunk index XOR (row & 7): conflict-free both ways
