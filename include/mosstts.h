@@ -85,7 +85,8 @@ int mt_codec_debug_set_attention(int mode);
 /* Token-major GEMM kernels (M > 256: prefill, every codec Linear).  mode 0 (default) = chosen by shape: CTA pairs (256 x 256
  * tiles on tcgen05.mma.cta_group::2, gemm_pair.cu) for K >= 2048, the one-SM 128 x 256 kernel (gemm_big.cu) for the codec's
  * short-K Linears; 1 = pairs wherever M >= 256; 4 = never pairs; + 2 = the per-lane row-store epilogue in place of the
- * warp-transposed (coalesced) one; + 16 = the codec rotates q and k in a separate pass instead of the in_proj epilogue.  The
+ * warp-transposed (coalesced) one; + 16 = the codec rotates q and k in a separate pass instead of the in_proj epilogue;
+ * + 32 = 8 instead of 16 epilogue warps for the GELU epilogue.  The
  * GEMM kernels and epilogue forms give bit-identical results.  For A/B measurements and cross-checks;
  * process-wide. */
 int mt_gemm_debug_set_pair(int mode);

@@ -19,7 +19,7 @@ namespace mt {
 namespace {
 
 constexpr int kBM = 128, kBN = 256, kKBytes = 128, kStages = 4;
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 8;                  // warps that own a transposition tile (the EW = 8 form)
 constexpr int kThreads = 64 + 32 * kEpiWarps;
 constexpr int kABytes = kBM * kKBytes, kBBytes = kBN * kKBytes, kStageBytes = kABytes + kBBytes;
 constexpr int kBarOffset = kStages * kStageBytes;
@@ -27,8 +27,11 @@ constexpr int kEpiOffset = kBarOffset + (2 * kStages + 4) * 8 + 32;     // 8 war
 constexpr int kSmemTotal = kEpiOffset + kEpiWarps * kEpiTileFloats * 4 + 1024;
 static_assert(kSmemTotal <= 232448, "shared memory budget");
 
-template <int KIND /*1 bf16, 2 tf32, 3 fp16*/>
-__global__ void __launch_bounds__(kThreads, 1)
+// EW = epilogue warps: 8 (lane quarter x column half, warp-transposed stores) or 16 (lane quarter x column quarter, per-lane
+// stores): at the codec's short K the tile time is the epilogue's per-warp latency, and an ALU-heavy epilogue (GELU) halves it
+// with twice the warps.
+template <int KIND /*1 bf16, 2 tf32, 3 fp16*/, int EW = 8>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, Epi ep, int M, int N,
                 int k_blocks, int m_tiles, int n_tiles, int w_early, int w_tiled) {
   extern __shared__ uint8_t smem_raw[];
@@ -66,7 +69,7 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tmem_full[i], 1);
-      ptx::mbar_init(&tmem_empty[i], kEpiWarps);
+      ptx::mbar_init(&tmem_empty[i], EW);
     }
     ptx::fence_barrier_init();
   }
@@ -151,21 +154,22 @@ gemm_big_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
   } else {
     // ===== epilogue =====
     const int q = warp & 3;                    // TMEM lane quarter this warp may access
-    const int half = (warp - 2) >> 2;          // column half
-    float* tile = reinterpret_cast<float*>(smem + kEpiOffset) + (warp - 2) * kEpiTileFloats;
-    const bool coalesced = epi_coalesced_ok(ep);
+    constexpr int kCols = kBN / (EW / 4);      // columns per warp: a half (EW = 8) or a quarter (EW = 16) of the tile
+    const int half = (warp - 2) >> 2;          // which of them
+    float* tile = reinterpret_cast<float*>(smem + kEpiOffset) + ((warp - 2) % kEpiWarps) * kEpiTileFloats;
+    const bool coalesced = EW == 8 && epi_coalesced_ok(ep);
     pdl_wait();                                // residual reads / output writes follow the previous kernel
     int mt = 0, nt = 0;
     for (int i = 0; tile_of(i, mt, nt); ++i) {
       const int buf = i & 1;
       const int m0 = mt * kBM + q * 32;
-      const int n_base = nt * kBN + half * (kBN / 2);
+      const int n_base = nt * kBN + half * kCols;
       EpiRes res;
       if (coalesced && n_base + 32 <= N && m0 < M) epi_res_load(ep, m0, n_base, M, lane, res);   // lands behind the wait
       ptx::mbar_wait(&tmem_full[buf], (i >> 1) & 1);
       ptx::tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBN + half * (kBN / 2);
-      epi_tile_warp<kBN / 2>(ep, coalesced, m0, n_base, M, N, taddr, tile, lane, res);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * kBN + half * kCols;
+      epi_tile_warp<kCols>(ep, coalesced, m0, n_base, M, N, taddr, tile, lane, res);
       // this warp is done reading the accumulator: hand it back to the MMA warp
       ptx::tc_fence_before();
       __syncwarp();
@@ -196,24 +200,25 @@ int linear_big(const LinearPlan& p, const Epi& ep, cudaStream_t s) {
   const int m_tiles = cdiv(p.M, kBM), n_tiles = cdiv(p.N, kBN);
   const int total = m_tiles * n_tiles;
   const int grid = total < kNumSMs ? total : kNumSMs;
-  static bool attr_set[4] = {false, false, false, false};
   const int kind = mma_kind(p.dtype_in);
-  if (!attr_set[kind]) {
-    if (kind == 1) MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    else if (kind == 2) MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    else MT_CUDA(cudaFuncSetAttribute(gemm_big_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
-    attr_set[kind] = true;
-  }
   const int w_early = p.w_static ? 1 : 0, w_tiled = p.w_tiled ? 1 : 0;
-  if (kind == 1)
-    MT_CUDA(launch(gemm_big_kernel<1>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
-                   n_tiles, w_early, w_tiled));
-  else if (kind == 2)
-    MT_CUDA(launch(gemm_big_kernel<2>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
-                   n_tiles, w_early, w_tiled));
-  else
-    MT_CUDA(launch(gemm_big_kernel<3>, dim3(grid), dim3(kThreads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles,
-                   n_tiles, w_early, w_tiled));
+  // 16 epilogue warps for the GELU epilogue (fp16 operands: the codec's linear1); mt_gemm_debug_set_pair(+32) keeps 8
+  const bool ew16 = kind == 3 && ep.act == 1 && !(g_gemm_pair_mode & 32);
+  static bool attr_set[4] = {false, false, false, false};
+  auto go = [&](auto kern, int threads) -> int {
+    bool& done = attr_set[ew16 ? 0 : kind];
+    if (!done) {
+      MT_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+      done = true;
+    }
+    MT_CUDA(launch(kern, dim3(grid), dim3(threads), kSmemTotal, s, tmA, tmB, ep, p.M, p.N, k_blocks, m_tiles, n_tiles, w_early,
+                   w_tiled));
+    return MT_OK;
+  };
+  if (ew16) MT_TRY(go(gemm_big_kernel<3, 16>, 64 + 32 * 16));
+  else if (kind == 1) MT_TRY(go(gemm_big_kernel<1, 8>, kThreads));
+  else if (kind == 2) MT_TRY(go(gemm_big_kernel<2, 8>, kThreads));
+  else MT_TRY(go(gemm_big_kernel<3, 8>, kThreads));
   count_launch();
   return MT_OK;
 }

@@ -29,7 +29,7 @@ def time_gemm(M, N, K, dt, out_dt, act=0, residual=False, iters=20):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
     s = L.stream_ptr(DEV)
     out_ms = {}
-    for mode in (1, 4, 6):
+    for mode in (1, 4, 6, 36):
         L.lib().mt_gemm_debug_set_pair(mode)
         for _ in range(3):
             L.check(L.lib().mt_gemm(C.byref(a), s), "mt_gemm")
@@ -41,11 +41,11 @@ def time_gemm(M, N, K, dt, out_dt, act=0, residual=False, iters=20):
             torch.cuda.synchronize()
             ts.append(e0.elapsed_time(e1))
         ts.sort()
-        out_ms[{4: "one_sm", 1: "pair", 6: "direct"}[mode]] = ts[len(ts) // 2]
+        out_ms[{4: "one_sm", 1: "pair", 6: "direct", 36: "ew8"}[mode]] = ts[len(ts) // 2]
     L.lib().mt_gemm_debug_set_pair(0)
     fl = 2.0 * M * N * K
     return {"M": M, "N": N, "K": K, "dtype": str(dt).split(".")[-1], "epilogue": "gelu->half" if act else ("scale+residual fp32" if residual else "plain"),
-            "one_sm_us": round(out_ms["one_sm"] * 1e3, 1), "pair_us": round(out_ms["pair"] * 1e3, 1), "one_sm_direct_epilogue_us": round(out_ms["direct"] * 1e3, 1),
+            "one_sm_us": round(out_ms["one_sm"] * 1e3, 1), "pair_us": round(out_ms["pair"] * 1e3, 1), "one_sm_direct_epilogue_us": round(out_ms["direct"] * 1e3, 1), "one_sm_8_epilogue_warps_us": round(out_ms["ew8"] * 1e3, 1),
             "one_sm_tflops": round(fl / out_ms["one_sm"] / 1e9, 1), "pair_tflops": round(fl / out_ms["pair"] / 1e9, 1)}
 
 
